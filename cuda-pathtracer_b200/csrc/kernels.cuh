@@ -1,0 +1,79 @@
+// kernels.cuh -- launch interface of the sm_100a wavefront kernels (kernels.cu).
+//
+// Pipeline (replaces the one-thread-per-pixel megakernel `render`, rendering/integrator.h:371-408):
+//
+//   rng_init     once per film      XORWOW state per pixel == curand_init(seed+pix, pix, 0)   (render_init, :274-280)
+//   raygen       once per frame     first camera ray of every slot, queue = identity
+//   extend       per iteration      closest hit of every live slot's ray through the BVH8      (Scene::intersect)
+//   shade        per iteration      emission -> film, Russian roulette, albedo, cosine sample; a path that
+//                                   ends is REGENERATED in place with the pixel's next sample (so warps stay full);
+//                                   a slot whose pixel has no samples left is marked dead
+//   compact      when worthwhile    stable, warp-aggregated compaction of the live-slot queue
+//   resolve      once per frame     mean, Reinhard, gamma, RGB8                                 (:393-407)
+//
+// Path state is SoA, three 16-byte records per slot so every access is one coalesced 128-bit
+// load/store per lane:
+//   A = { o.x, o.y, o.z, d.x }   B = { d.y, d.z, depth|flags, beta.r }   C = { beta.g, beta.b, hit_t, hit_prim }
+#pragma once
+#include <cuda_runtime.h>
+
+#include "layout.h"
+#include "shade.h"
+
+namespace ptx {
+
+constexpr uint32_t kDeadFlag = 0x80000000u;
+
+struct WaveState {
+    float4* A;
+    float4* B;
+    float4* C;
+    uint2* D;                 // philox mode: { pixel, sample index }; compat mode: { pixel, samples done }
+    uint32_t* queue[2];       // live slot indices (ping-pong for compaction)
+    uint32_t* slot_pixel;     // slot -> pixel for the pixels this rank owns
+    // device counters (one 64-byte block): see CounterBlock
+    unsigned long long* counters;
+    uint32_t capacity;        // slots allocated
+};
+
+// indices into WaveState::counters
+enum { CTR_SEGMENTS = 0, CTR_PATHS = 1, CTR_LIVE = 2, CTR_QLEN = 3, CTR_NEXT_PATH = 4, CTR_NODE_VISITS = 5, CTR_TRI_TESTS = 6, CTR_COUNT = 8 };
+
+struct FilmView {
+    float4* accum;            // per pixel: sum r, g, b, (unused)
+    uint4* rngA;              // per pixel: v0..v3
+    uint2* rngB;              // per pixel: v4, d
+    int width, height;
+};
+
+struct RenderParams {
+    ShadeParams shade;
+    int spp;
+    uint32_t n_slots;         // owned pixels (compat) / pool size (philox)
+    uint32_t n_owned;         // pixels owned by this rank
+    unsigned long long total_paths;   // philox: n_owned * spp
+    uint32_t sample_begin;    // philox sample-range sharding: first global sample index
+    unsigned long long seed;
+};
+
+void launch_rng_init(cudaStream_t st, const FilmView& film, unsigned long long seed_base, const uint32_t* jump_tables);
+void launch_raygen(cudaStream_t st, int rng_mode, const WaveState& ws, const FilmView& film, const CameraView& cam,
+                   const RenderParams& rp);
+void launch_extend(cudaStream_t st, const WaveState& ws, const SceneView& scene, int q, uint32_t qlen_bound, bool count);
+void launch_shade(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FilmView& film,
+                  const CameraView& cam, const RenderParams& rp, int q, uint32_t qlen_bound);
+void launch_bounce(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FilmView& film,
+                   const CameraView& cam, const RenderParams& rp, int q, uint32_t qlen_bound);
+// compacts queue[q] -> queue[q^1]; scratch holds per-block counts (>= ceil(qlen_bound/1024)+1 words)
+void launch_compact(cudaStream_t st, const WaveState& ws, int q, uint32_t qlen_bound, uint32_t* scratch);
+void launch_resolve(cudaStream_t st, const FilmView& film, float inv_spp, uint8_t* rgb8, int flip_y);
+void launch_film_scale(cudaStream_t st, const FilmView& film, float inv_spp, float* linear_rgb);
+void launch_primary_ids(cudaStream_t st, const SceneView& scene, const CameraView& cam, int w, int h, int32_t* prim, float* t);
+void launch_trace_rays(cudaStream_t st, const SceneView& scene, const float* rays, size_t n, float t_min, int32_t* prim, float* t);
+void launch_slot_pixels(cudaStream_t st, uint32_t* slot_pixel, int w, int h, int shard_mode, int rank, int world, uint32_t n_owned);
+
+// pixels owned by `rank` under tile sharding: rows are dealt in bands of kBandRows
+constexpr int kBandRows = 4;
+uint32_t owned_pixel_count(int w, int h, int shard_mode, int rank, int world);
+
+}  // namespace ptx

@@ -1,0 +1,153 @@
+// traverse.h -- closest-hit traversal of the compressed BVH8 and the triangle test.
+//
+// Replaces Scene::intersect -> intersect_bvh_optimized (rendering/scene.h:39-110) and
+// Triangle::intersect / Quad::intersect (rendering/triangle.h:64-96, rendering/quad.h:49-132).
+// Acceptance rule kept from the reference: a candidate replaces the current hit iff
+// t > 1e-8, t >= t_min and t < closest (strict, scene.h:89-90); |det| < 1e-8 rejects; u in [0,1],
+// v >= 0, u+v <= 1 inclusive (triangle.h:71-80).
+//
+// Written __host__ __device__ so tests can compile the very same source for the CPU and compare
+// it with the oracle without a GPU; the product only ever calls it from CUDA kernels.
+#pragma once
+#include "layout.h"
+
+namespace ptx {
+
+PTX_HD uint32_t hi_bit(uint32_t x) {   // index of the highest set bit, x != 0
+#if defined(__CUDA_ARCH__)
+    return 31u - (uint32_t)__clz((int)x);
+#else
+    return 31u - (uint32_t)__builtin_clz(x);
+#endif
+}
+PTX_HD uint32_t popc32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return (uint32_t)__popc(x);
+#else
+    return (uint32_t)__builtin_popcount(x);
+#endif
+}
+PTX_HD uint32_t byte_of(uint32_t w, int i) { return (w >> (8 * i)) & 0xFFu; }
+// per byte: 0x80 -> 0xFF, 0x00 -> 0x00
+PTX_HD uint32_t sign_extend_s8x4(uint32_t x) { return ((x >> 7) & 0x01010101u) * 0xFFu; }
+
+struct TraceCounters {
+    uint32_t nodes, tris;
+};
+
+// Moeller-Trumbore on a precomputed edge record.  Returns true and updates (closest, u, v) on accept.
+PTX_HD bool intersect_tri(vec3 v0, vec3 e1, vec3 e2, vec3 o, vec3 d, float t_min, float& closest) {
+    const float EPSILON = 1e-8f;
+    vec3 h = cross(d, e2);
+    float a = dot(e1, h);
+    if (fabsf(a) < EPSILON) return false;
+    float f = 1.0f / a;
+    vec3 s = o - v0;
+    float u = f * dot(s, h);
+    if (u < 0.0f || u > 1.0f) return false;
+    vec3 q = cross(s, e1);
+    float v = f * dot(d, q);
+    if (v < 0.0f || u + v > 1.0f) return false;
+    float t = f * dot(e2, q);
+    if (t > EPSILON && t >= t_min && t < closest) { closest = t; return true; }
+    return false;
+}
+
+// Closest hit along (o, d) in [t_min, t_max).  Returns the triangle slot (index into tris) or kMiss;
+// t_hit receives the distance.  STACK entries of 8 bytes live in registers/local memory.
+template <int STACK, bool COUNT>
+PTX_HD uint32_t trace_closest(const SceneView& s, vec3 o, vec3 d, float t_min, float t_max, float& t_hit,
+                              TraceCounters* ctr) {
+    uint32_t stack_x[STACK], stack_y[STACK];
+    int sp = 0;
+    float closest = t_max;
+    uint32_t best = kMiss;
+
+    const float ooeps = 8.271806e-25f;   // 2^-80: keeps 1/d finite for axis-parallel rays
+    float idx = 1.0f / (fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
+    float idy = 1.0f / (fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
+    float idz = 1.0f / (fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
+    // octant: bit set where the direction is negative; slot priority = slot ^ octinv
+    uint32_t oct = (d.x < 0.0f ? 4u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 1u : 0u);
+    uint32_t octinv = 7u - oct;
+    uint32_t octinv4 = octinv * 0x01010101u;
+
+    uint32_t ng_x = 0, ng_y = 0x80000000u;   // node group: base index, (hit bits 31..24 | imask 7..0)
+    uint32_t tg_x = 0, tg_y = 0;             // triangle group: base index, hit bits 23..0
+
+    for (;;) {
+        if (ng_y > 0x00FFFFFFu) {
+            uint32_t imask = ng_y & 0xFFu;
+            uint32_t bit = hi_bit(ng_y);
+            ng_y &= ~(1u << bit);
+            if (ng_y > 0x00FFFFFFu) { stack_x[sp] = ng_x; stack_y[sp] = ng_y; sp++; }
+            uint32_t slot = (bit - 24u) ^ octinv;
+            uint32_t rel = popc32(imask & ~(0xFFFFFFFFu << slot));
+            const u32x4* np = s.nodes + (size_t)(ng_x + rel) * kNodeQuads;
+            u32x4 n0 = ldq(np + 0), n1 = ldq(np + 1), n2 = ldq(np + 2), n3 = ldq(np + 3), n4 = ldq(np + 4);
+            if (COUNT) ctr->nodes++;
+
+            float px = u2f(n0.x), py = u2f(n0.y), pz = u2f(n0.z);
+            uint32_t ex = n0.w & 0xFFu, ey = (n0.w >> 8) & 0xFFu, ez = (n0.w >> 16) & 0xFFu;
+            ng_x = n1.x; tg_x = n1.y;
+            float sx = u2f(ex << 23) * idx, sy = u2f(ey << 23) * idy, sz = u2f(ez << 23) * idz;
+            float ox = (px - o.x) * idx, oy = (py - o.y) * idy, oz = (pz - o.z) * idz;
+
+            uint32_t hitmask = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (int half = 0; half < 2; half++) {
+                uint32_t meta4 = half ? n1.w : n1.z;
+                uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+                uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
+                uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
+                uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+                uint32_t qlox = half ? n2.y : n2.x, qloy = half ? n2.w : n2.z, qloz = half ? n3.y : n3.x;
+                uint32_t qhix = half ? n3.w : n3.z, qhiy = half ? n4.y : n4.x, qhiz = half ? n4.w : n4.z;
+                uint32_t nearx = d.x < 0.0f ? qhix : qlox, farx = d.x < 0.0f ? qlox : qhix;
+                uint32_t neary = d.y < 0.0f ? qhiy : qloy, fary = d.y < 0.0f ? qloy : qhiy;
+                uint32_t nearz = d.z < 0.0f ? qhiz : qloz, farz = d.z < 0.0f ? qloz : qhiz;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+                for (int j = 0; j < 4; j++) {
+                    float tminx = (float)byte_of(nearx, j) * sx + ox;
+                    float tminy = (float)byte_of(neary, j) * sy + oy;
+                    float tminz = (float)byte_of(nearz, j) * sz + oz;
+                    float tmaxx = (float)byte_of(farx, j) * sx + ox;
+                    float tmaxy = (float)byte_of(fary, j) * sy + oy;
+                    float tmaxz = (float)byte_of(farz, j) * sz + oz;
+                    float cmin = fmaxf(fmaxf(tminx, tminy), fmaxf(tminz, t_min));
+                    float cmax = fminf(fminf(tmaxx, tmaxy), fminf(tmaxz, closest));
+                    if (cmin <= cmax) hitmask |= byte_of(child_bits4, j) << byte_of(bit_index4, j);
+                }
+            }
+            ng_y = (hitmask & 0xFF000000u) | (n0.w >> 24);
+            tg_y = hitmask & 0x00FFFFFFu;
+        } else {
+            tg_x = ng_x; tg_y = ng_y;
+            ng_x = 0; ng_y = 0;
+        }
+
+        while (tg_y != 0) {
+            uint32_t bit = hi_bit(tg_y);
+            tg_y &= ~(1u << bit);
+            uint32_t ti = tg_x + bit;
+            const f32x4* tp = s.tris + (size_t)ti * kTriQuads;
+            f32x4 a = ldq(tp + 0), b = ldq(tp + 1), c = ldq(tp + 2);
+            if (COUNT) ctr->tris++;
+            if (intersect_tri(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), o, d, t_min, closest)) best = ti;
+        }
+
+        if (ng_y <= 0x00FFFFFFu) {
+            if (sp == 0) break;
+            sp--;
+            ng_x = stack_x[sp]; ng_y = stack_y[sp];
+        }
+    }
+    t_hit = closest;
+    return best;
+}
+
+}  // namespace ptx

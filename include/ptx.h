@@ -1,0 +1,188 @@
+/* include/ptx.h -- C ABI of the B200-native path-tracing core ("ptx" = path-tracer core, the
+ * prefix proposed in SURVEY.md section 8(b); nothing to do with NVIDIA's PTX ISA).
+ *
+ * Drop-in boundary for the render loop of USharma002/CUDA-PathTracer.  The reference has no FFI
+ * layer; its "API" is the set of C++ structs and free functions that SceneState::loadScene,
+ * RenderState::allocateBuffers and renderFrame call directly.  Each entry point below names the
+ * reference call (file:line under /root/reference) it replaces.  Conventions:
+ *   - plain C, opaque handles, plain pointers and sizes; no C++/torch types cross this boundary;
+ *   - every function returns 0 on success or a negative ptx_status; nothing throws;
+ *     ptx_last_error() gives the text (the reference prints to stderr and carries on,
+ *     application_state.h:394-397; cudaMallocSafe throws, utils/cuda_utils.h:53-60);
+ *   - a ptx_ctx is one CUDA device + one stream; calls on one ctx are not thread-safe;
+ *   - all compute runs in hand-written sm_100a CUDA kernels; there is NO CPU fallback: without a
+ *     usable CUDA device ptx_ctx_create fails with PTX_ERR_NO_DEVICE.
+ */
+#ifndef PTX_H
+#define PTX_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    PTX_OK = 0,
+    PTX_ERR_INVALID = -1,     /* bad argument */
+    PTX_ERR_IO = -2,          /* file missing / unreadable / no primitives (loadOBJ returns false) */
+    PTX_ERR_CUDA = -3,        /* CUDA runtime error; text in ptx_last_error */
+    PTX_ERR_NO_DEVICE = -4,   /* no CUDA device: the product has no CPU path */
+    PTX_ERR_UNSUPPORTED = -5, /* e.g. sampling modes that need the (out-of-scope) radiosity solver */
+    PTX_ERR_NOMEM = -6
+} ptx_status;
+
+typedef struct ptx_ctx ptx_ctx;
+typedef struct ptx_scene ptx_scene;
+typedef struct ptx_film ptx_film;
+
+/* ---- context ------------------------------------------------------------------------------- */
+int ptx_ctx_create(int device, ptx_ctx** out);
+void ptx_ctx_destroy(ptx_ctx* ctx);
+const char* ptx_last_error(const ptx_ctx* ctx);           /* ctx may be NULL: last error of this thread */
+int ptx_sync(ptx_ctx* ctx);                                /* cudaDeviceSynchronize, application.h:199 */
+int ptx_ctx_device_info(const ptx_ctx* ctx, int* sm_count, int* cc_major, int* cc_minor, size_t* total_mem);
+const char* ptx_version(void);
+
+/* ---- scene --------------------------------------------------------------------------------- */
+/* One reference `Primitive` minus its radiosity payload (rendering/primitive.h:21-29,
+ * triangle.h:98-105, quad.h:134-140).  type 0: v[0..2] = v0 v1 v2; type 1: v00 v10 v11 v01. */
+typedef struct {
+    int32_t type;
+    float v[4][3];
+    float normal[3];
+    float bsdf[3];
+    float Le[3];
+    int32_t material_type;    /* 0 = Lambertian (all the reference has); 1 = perfect mirror (extension) */
+} ptx_primitive;
+
+typedef struct {
+    float bsdf[3];            /* Kd (or Kr for mirrors) */
+    float Le[3];              /* Ke */
+    int32_t type;             /* 0 diffuse, 1 mirror */
+    int32_t reserved;
+} ptx_material;
+
+typedef struct {
+    int32_t convert_quads;    /* AppConfig::convert_quads_to_triangles (application_state.h:271) */
+    int32_t subdivision;      /* AppConfig::subdivision_step: 1->4 splits per level (form_factors.h:520-574) */
+    int64_t triangle_cap;     /* .pbrt only: 0 = no cap (the reference substitutes a box above 2 M, pbrt_loader.h:205) */
+    int32_t mirror_from_mtl;  /* extension: MTL `illum 3|5` => mirror with Kr = Ks.  0 keeps reference semantics */
+    int32_t reserved;
+} ptx_load_opts;
+
+typedef struct {
+    int32_t builder;          /* 0 = GPU binned-SAH (default); 1 = host binned-SAH (cross-check) */
+    int32_t sah_bins;         /* 0 = default (16) */
+    int32_t max_leaf;         /* triangles per BVH8 leaf slot, 1..3; 0 = default (3) */
+    int32_t reserved;
+} ptx_build_opts;
+
+typedef struct {
+    int64_t n_primitives;     /* reference numbering: one per OBJ face / PBRT triangle */
+    int64_t n_triangles;      /* quads contribute two */
+    int64_t n_nodes;          /* BVH8 nodes (80 B each) */
+    int64_t n_materials;
+    int64_t node_bytes, triangle_bytes, shading_bytes;
+    float bounds_min[3], bounds_max[3];
+    float sah_cost;           /* SAH cost of the BVH8, root area normalised */
+    float build_ms;           /* device time of the last build */
+    int32_t builder;
+    int32_t max_depth;
+} ptx_scene_stats;
+
+/* replaces loadScene/loadOBJ/loadPBRT + RayTracingManager::buildAccelStructure + Scene(...)
+ * (utils/file_manager.h:93, 291-315; utils/pbrt_loader.h:178; ray_tracing_backend.h:81-129;
+ * scene.h:23-27; driver application_state.h:367-464).  Builds the acceleration structure. */
+int ptx_scene_load(ptx_ctx* ctx, const char* path, const ptx_load_opts* opts, ptx_scene** out);
+/* host-side parse only (no device work): what loadOBJ returns, in the reference's numbering */
+int ptx_parse_scene_file(const char* path, const ptx_load_opts* opts, ptx_primitive** prims_out, int64_t* n_out);
+void ptx_free_primitives(ptx_primitive* prims);
+/* scene from an in-memory primitive list (what a caller holding the reference's Primitive[] passes) */
+int ptx_scene_from_primitives(ptx_ctx* ctx, const ptx_primitive* prims, int64_t n, const ptx_build_opts* bopts,
+                              ptx_scene** out);
+/* packed triangle soup: v = 9 floats per triangle; normals NULL => geometric; mat_id indexes mats */
+int ptx_scene_from_triangles(ptx_ctx* ctx, const float* v, const float* normals, const uint32_t* mat_id,
+                             const ptx_material* mats, size_t n_tri, size_t n_mat, const ptx_build_opts* bopts,
+                             ptx_scene** out);
+int ptx_scene_build_accel(ptx_scene* scene, const ptx_build_opts* opts);     /* rebuild with other options */
+int ptx_scene_stats_get(const ptx_scene* scene, ptx_scene_stats* out);
+int ptx_scene_get_primitives(const ptx_scene* scene, ptx_primitive* out, int64_t capacity);
+void ptx_scene_destroy(ptx_scene* scene);
+
+/* ---- camera: the reference's Sensor (rendering/sensor.h:14-101), same field names ------------ */
+typedef struct {
+    float radius, yaw, pitch;
+    float vup[3], lookat[3];
+    float origin[3], lower_left_corner[3], horizontal[3], vertical[3];
+    float vfov, aspect;
+    int32_t image_width, image_height;
+} ptx_camera;
+
+int ptx_camera_set(ptx_camera* cam, const float eye[3], const float at[3], const float up[3], float vfov_deg,
+                   float aspect);                                           /* Sensor ctor, sensor.h:16-29 */
+int ptx_camera_update(ptx_camera* cam);                                     /* updateCamera, sensor.h:38-51 */
+int ptx_camera_orbit(ptx_camera* cam);                                      /* updateCameraOrbit, sensor.h:56-67 */
+/* RenderState default camera + allocateBuffers aspect + renderFrame's orbit update
+ * (application_state.h:88, 106-109; application.h:161-162) */
+int ptx_camera_default(ptx_camera* cam, int width, int height);
+
+/* ---- film: RenderState::allocateBuffers (application_state.h:91-123) ------------------------- */
+int ptx_film_create(ptx_ctx* ctx, int width, int height, ptx_film** out);   /* also runs render_init */
+int ptx_film_reset(ptx_film* film, uint64_t seed_base);                     /* re-seed (reference: 2023) + clear */
+int ptx_film_clear(ptx_film* film);                                         /* clear accumulation only */
+/* Reinhard + gamma 1/2.2 + 255.99 quantisation of integrator.h:393-407; row 0 = bottom unless flip_y */
+int ptx_film_resolve_rgb8(ptx_film* film, uint8_t* dst, int dst_is_device, int flip_y);
+int ptx_film_read_linear(ptx_film* film, float* rgb_host);                  /* w*h*3 pre-tonemap means */
+int ptx_film_write(ptx_film* film, const char* path);                        /* .ppm (RGB8, top row first) or .pfm */
+/* raw accumulation buffer (float4 per pixel: sum r,g,b + sample count) for NCCL film combine */
+int ptx_film_device_buffer(ptx_film* film, void** dev_ptr, size_t* bytes);
+int ptx_film_set_sample_count(ptx_film* film, float spp_total);             /* after an external reduce */
+void ptx_film_destroy(ptx_film* film);
+
+/* ---- render: renderFrame (application.h:157-216) -> render<<<>>> (integrator.h:371-408) ------- */
+enum { PTX_RNG_XORWOW_COMPAT = 0, PTX_RNG_PHILOX = 1 };
+enum { PTX_SAMPLING_BSDF = 0 };             /* SamplingMode::SAMPLING_BSDF; grid/MIS modes need the radiosity solver */
+enum { PTX_SHARD_NONE = 0, PTX_SHARD_TILES = 1, PTX_SHARD_SAMPLES = 2 };
+
+typedef struct {
+    int32_t spp;              /* AppConfig::spp */
+    int32_t max_depth;        /* reference hard-codes 5 (integrator.h:389); 0 => 5 */
+    int32_t rng_mode;         /* PTX_RNG_* ; compat reproduces curand_init(2023+pix, pix, 0) streams */
+    int32_t sampling_mode;    /* PTX_SAMPLING_BSDF only */
+    int32_t accumulate;       /* 0: each call is an independent frame like the reference; 1: progressive */
+    int32_t shard_mode;       /* PTX_SHARD_* */
+    int32_t shard_rank, shard_world;
+    int32_t rr_start_depth;   /* 0 => 3  (depth > 2, integrator.h:207) */
+    float rr_cap;             /* 0 => 0.95 */
+    int32_t pipeline;         /* 0 = wavefront (raygen/extend/shade/compact); 1 = fused bounce kernel */
+    int32_t reserved[5];
+} ptx_render_opts;
+
+typedef struct {
+    uint64_t segments;        /* Scene::intersect-equivalent calls (path segments) of the last render */
+    uint64_t paths;
+    uint64_t iterations;      /* wavefront iterations */
+    uint64_t kernel_launches; /* kernels launched by the last ptx_render */
+    uint64_t compactions;
+    float render_ms;          /* CUDA-event time of the last ptx_render on the ctx stream */
+    float extend_ms, shade_ms, other_ms;   /* filled when opts.reserved[0] & 1 (per-stage timing) */
+} ptx_render_stats;
+
+int ptx_render(ptx_ctx* ctx, const ptx_scene* scene, const ptx_camera* cam, ptx_film* film,
+               const ptx_render_opts* opts);
+int ptx_render_stats_get(const ptx_ctx* ctx, ptx_render_stats* out);
+
+/* ---- queries used by parity tests (spec: pick_primitive_kernel, ui/callbacks.h:22-48) --------- */
+/* pixel-centre primary rays, u=(x+0.5)/w, v=(y+0.5)/h; prim_id in the reference's numbering, -1 = miss */
+int ptx_trace_primary_ids(ptx_ctx* ctx, const ptx_scene* scene, const ptx_camera* cam, int width, int height,
+                          int32_t* prim_id_host, float* t_host);
+/* closest hit for n host rays (6 floats: o, d; d normalised like the Ray ctor, core/ray.h:9-12) */
+int ptx_trace_rays(ptx_ctx* ctx, const ptx_scene* scene, const float* rays_host, size_t n, float t_min,
+                   int32_t* prim_id_host, float* t_host);
+/* XORWOW state after render_init for pixels [first, first+n): 6 words each (v[0..4], d) */
+int ptx_film_rng_state(ptx_film* film, int64_t first, int64_t n, uint32_t* out_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTX_H */

@@ -1,0 +1,139 @@
+// tests/host_emu.cpp -- TEST-ONLY: compiles the product's __host__ __device__ kernel cores
+// (traverse.h, shade.h, rng.h) and host builders for the CPU so that `-m "not gpu"` tests can check
+// BVH8 construction, traversal, RNG and shading logic against the oracle without a GPU.
+// It is never linked into libptx.so; the product path always runs CUDA kernels.
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../cuda-pathtracer_b200/csrc/bvh_host.h"
+#include "../cuda-pathtracer_b200/csrc/loader.h"
+#include "../cuda-pathtracer_b200/csrc/rng.h"
+#include "../cuda-pathtracer_b200/csrc/scene_pack.h"
+#include "../cuda-pathtracer_b200/csrc/shade.h"
+#include "../cuda-pathtracer_b200/csrc/traverse.h"
+
+using namespace ptx;
+
+struct EmuScene {
+    PackedScene packed;
+    Bvh8Result bvh;
+    SceneView view;
+};
+
+static void finish(EmuScene* s, int max_leaf) {
+    Bvh2 b2;
+    build_bvh2_sah(s->packed.tris.data(), s->packed.tris.size(), 16, max_leaf, b2);
+    collapse_bvh8(b2, s->packed.tris.data(), s->packed.tris.size(), s->bvh);
+    s->view.nodes = s->bvh.nodes.data();
+    s->view.tris = s->bvh.tris.data();
+    s->view.prim_shade = s->packed.prim_shade.data();
+    s->view.materials = s->packed.materials.data();
+    s->view.n_nodes = (uint32_t)(s->bvh.nodes.size() / kNodeQuads);
+    s->view.n_tris = (uint32_t)s->bvh.tri_src.size();
+    s->view.n_prims = (uint32_t)s->packed.prim_shade.size();
+    s->view.n_mats = (uint32_t)(s->packed.materials.size() / 2);
+}
+
+extern "C" {
+
+EmuScene* emu_scene_from_prims(const ptx_primitive* prims, int64_t n, int max_leaf) {
+    EmuScene* s = new EmuScene();
+    pack_primitives(prims, (size_t)n, s->packed);
+    finish(s, max_leaf);
+    return s;
+}
+EmuScene* emu_scene_load(const char* path, int convert_quads, int subdiv, int max_leaf) {
+    std::vector<ptx_primitive> prims; std::string err;
+    if (!load_obj(path, false, prims, err)) return nullptr;
+    if (convert_quads) split_quads(prims);
+    if (subdiv > 0) subdivide(prims, subdiv);
+    return emu_scene_from_prims(prims.data(), (int64_t)prims.size(), max_leaf);
+}
+void emu_scene_free(EmuScene* s) { delete s; }
+int64_t emu_scene_counts(const EmuScene* s, int64_t* n_tris, int64_t* n_nodes, int* depth, float* sah) {
+    *n_tris = s->view.n_tris; *n_nodes = s->view.n_nodes; *depth = s->bvh.max_depth; *sah = s->bvh.sah_cost;
+    return s->view.n_prims;
+}
+int64_t emu_parse_obj(const char* path, int convert_quads, int subdiv, ptx_primitive* out, int64_t cap) {
+    std::vector<ptx_primitive> prims; std::string err;
+    if (!load_obj(path, false, prims, err)) return -1;
+    if (convert_quads) split_quads(prims);
+    if (subdiv > 0) subdivide(prims, subdiv);
+    for (size_t i = 0; i < prims.size() && (int64_t)i < cap; i++) out[i] = prims[i];
+    return (int64_t)prims.size();
+}
+
+// closest hits for n rays (6 floats each; d normalised here like the Ray ctor)
+void emu_trace(const EmuScene* s, const float* rays, int64_t n, float t_min, int32_t* prim, float* t, uint64_t* ctr) {
+    for (int64_t i = 0; i < n; i++) {
+        vec3 o = ld3(rays + 6 * i), d = unit(ld3(rays + 6 * i + 3));
+        float th; TraceCounters c = {0, 0};
+        uint32_t tri = trace_closest<32, true>(s->view, o, d, t_min, FLT_MAX, th, &c);
+        prim[i] = tri == kMiss ? -1 : (int32_t)f2u(s->view.tris[(size_t)tri * kTriQuads].w);
+        t[i] = tri == kMiss ? -1.0f : th;
+        if (ctr) { ctr[0] += c.nodes; ctr[1] += c.tris; }
+    }
+}
+
+void emu_primary_ids(const EmuScene* s, const CameraView* cam, int32_t* prim, float* t) {
+    for (int y = 0; y < cam->height; y++)
+        for (int x = 0; x < cam->width; x++) {
+            float u = (x + 0.5f) / (float)cam->width, v = (y + 0.5f) / (float)cam->height;
+            vec3 o, d; camera_ray(*cam, u, v, o, d);
+            float th;
+            uint32_t tri = trace_closest<32, false>(s->view, o, d, 1e-4f, FLT_MAX, th, nullptr);
+            prim[y * cam->width + x] = tri == kMiss ? -1 : (int32_t)f2u(s->view.tris[(size_t)tri * kTriQuads].w);
+            t[y * cam->width + x] = tri == kMiss ? -1.0f : th;
+        }
+}
+
+void emu_jump_tables(uint32_t* out) { xorwow_build_jump_tables(out); }
+void emu_xorwow_init(uint64_t seed, uint64_t subsequence, const uint32_t* tables, uint32_t* out6) {
+    Xorwow s = xorwow_seed(seed);
+    for (int b = 0; b < kXorwowJumps; b++)
+        if ((subsequence >> b) & 1ull) xorwow_apply(s, tables + (size_t)b * kXorwowJumpWords);
+    out6[0] = s.v0; out6[1] = s.v1; out6[2] = s.v2; out6[3] = s.v3; out6[4] = s.v4; out6[5] = s.d;
+}
+void emu_philox(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out4) {
+    Philox4 p = philox4x32_10(c0, c1, c2, c3, k0, k1);
+    out4[0] = p.x; out4[1] = p.y; out4[2] = p.z; out4[3] = p.w;
+}
+
+// the render loop of integrator.h:371-408 driven through shade.h / traverse.h (compat RNG), serial
+void emu_render(const EmuScene* s, const CameraView* cam, int spp, int max_depth, uint64_t seed_base, float* linear,
+                uint8_t* rgb8, uint64_t* segments) {
+    std::vector<uint32_t> tables((size_t)kXorwowJumps * kXorwowJumpWords);
+    xorwow_build_jump_tables(tables.data());
+    ShadeParams sp = {max_depth, 3, 0.95f};
+    uint64_t seg = 0;
+    for (int y = 0; y < cam->height; y++)
+        for (int x = 0; x < cam->width; x++) {
+            int pix = y * cam->width + x;
+            uint32_t st6[6];
+            emu_xorwow_init(seed_base + (uint64_t)pix, (uint64_t)pix, tables.data(), st6);
+            XorwowRng rng; rng.st = Xorwow{st6[0], st6[1], st6[2], st6[3], st6[4], st6[5]};
+            vec3 color = mk3(0, 0, 0);
+            for (int k = 0; k < spp; k++) {
+                float u = (x + rng.next()) / (float)cam->width;
+                float v = (y + rng.next()) / (float)cam->height;
+                PathVertex pv; camera_ray(*cam, u, v, pv.o, pv.d);
+                pv.beta = mk3(1, 1, 1); pv.depth = 0;
+                vec3 L = mk3(0, 0, 0);
+                for (;;) {
+                    float th; seg++;
+                    uint32_t tri = trace_closest<32, false>(s->view, pv.o, pv.d, 1e-4f, FLT_MAX, th, nullptr);
+                    uint32_t prim = tri == kMiss ? kMiss : f2u(s->view.tris[(size_t)tri * kTriQuads].w);
+                    if (!shade_bounce(s->view, sp, pv, prim, th, rng, L)) break;
+                }
+                color = color + L;
+            }
+            color = div_scalar(color, (float)spp);
+            if (linear) st3(linear + 3 * pix, color);
+            if (rgb8) { rgb8[3 * pix] = tonemap_channel(color.x); rgb8[3 * pix + 1] = tonemap_channel(color.y); rgb8[3 * pix + 2] = tonemap_channel(color.z); }
+        }
+    if (segments) *segments = seg;
+}
+
+}  // extern "C"
