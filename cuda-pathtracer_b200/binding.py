@@ -1,0 +1,320 @@
+"""ctypes binding over the C ABI of include/ptx.h (libptx.so).
+
+Host-side mirror of the reference's scene / camera / integrator interface for test drivers and
+bench.py.  It only marshals arguments: every pixel and every hit comes from the CUDA kernels in
+libptx.so; if the library is missing or no GPU is usable, calls raise PtxError (no fallback).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libptx.so")
+
+RNG_XORWOW_COMPAT, RNG_PHILOX = 0, 1
+SHARD_NONE, SHARD_TILES, SHARD_SAMPLES = 0, 1, 2
+PIPELINE_WAVEFRONT, PIPELINE_FUSED = 0, 1
+
+
+class PtxError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"ptx error {code}: {msg}")
+        self.code = code
+
+
+class Primitive(C.Structure):
+    _fields_ = [("type", C.c_int32), ("v", (C.c_float * 3) * 4), ("normal", C.c_float * 3), ("bsdf", C.c_float * 3),
+                ("Le", C.c_float * 3), ("material_type", C.c_int32)]
+
+
+PRIM_DTYPE = np.dtype([("type", "<i4"), ("v", "<f4", (4, 3)), ("normal", "<f4", 3), ("bsdf", "<f4", 3), ("Le", "<f4", 3),
+                       ("material_type", "<i4")])
+
+
+class Material(C.Structure):
+    _fields_ = [("bsdf", C.c_float * 3), ("Le", C.c_float * 3), ("type", C.c_int32), ("reserved", C.c_int32)]
+
+
+class LoadOpts(C.Structure):
+    _fields_ = [("convert_quads", C.c_int32), ("subdivision", C.c_int32), ("triangle_cap", C.c_int64),
+                ("mirror_from_mtl", C.c_int32), ("reserved", C.c_int32)]
+
+
+class BuildOpts(C.Structure):
+    _fields_ = [("builder", C.c_int32), ("sah_bins", C.c_int32), ("max_leaf", C.c_int32), ("reserved", C.c_int32)]
+
+
+class SceneStats(C.Structure):
+    _fields_ = [("n_primitives", C.c_int64), ("n_triangles", C.c_int64), ("n_nodes", C.c_int64), ("n_materials", C.c_int64),
+                ("node_bytes", C.c_int64), ("triangle_bytes", C.c_int64), ("shading_bytes", C.c_int64),
+                ("bounds_min", C.c_float * 3), ("bounds_max", C.c_float * 3), ("sah_cost", C.c_float), ("build_ms", C.c_float),
+                ("builder", C.c_int32), ("max_depth", C.c_int32)]
+
+
+class Camera(C.Structure):
+    _fields_ = [("radius", C.c_float), ("yaw", C.c_float), ("pitch", C.c_float), ("vup", C.c_float * 3), ("lookat", C.c_float * 3),
+                ("origin", C.c_float * 3), ("lower_left_corner", C.c_float * 3), ("horizontal", C.c_float * 3),
+                ("vertical", C.c_float * 3), ("vfov", C.c_float), ("aspect", C.c_float), ("image_width", C.c_int32),
+                ("image_height", C.c_int32)]
+
+
+class RenderOpts(C.Structure):
+    _fields_ = [("spp", C.c_int32), ("max_depth", C.c_int32), ("rng_mode", C.c_int32), ("sampling_mode", C.c_int32),
+                ("accumulate", C.c_int32), ("shard_mode", C.c_int32), ("shard_rank", C.c_int32), ("shard_world", C.c_int32),
+                ("rr_start_depth", C.c_int32), ("rr_cap", C.c_float), ("pipeline", C.c_int32), ("reserved", C.c_int32 * 5)]
+
+
+class RenderStats(C.Structure):
+    _fields_ = [("segments", C.c_uint64), ("paths", C.c_uint64), ("iterations", C.c_uint64), ("kernel_launches", C.c_uint64),
+                ("compactions", C.c_uint64), ("render_ms", C.c_float), ("extend_ms", C.c_float), ("shade_ms", C.c_float),
+                ("other_ms", C.c_float), ("node_visits", C.c_uint64), ("tri_tests", C.c_uint64)]
+
+
+EXPORTS = [
+    "ptx_ctx_create", "ptx_ctx_destroy", "ptx_last_error", "ptx_sync", "ptx_ctx_device_info", "ptx_version",
+    "ptx_scene_load", "ptx_parse_scene_file", "ptx_free_primitives", "ptx_scene_from_primitives", "ptx_scene_from_triangles",
+    "ptx_scene_build_accel", "ptx_scene_stats_get", "ptx_scene_get_primitives", "ptx_scene_destroy",
+    "ptx_camera_set", "ptx_camera_update", "ptx_camera_orbit", "ptx_camera_default",
+    "ptx_film_create", "ptx_film_reset", "ptx_film_clear", "ptx_film_resolve_rgb8", "ptx_film_read_linear", "ptx_film_write",
+    "ptx_film_device_buffer", "ptx_film_set_sample_count", "ptx_film_destroy",
+    "ptx_render", "ptx_render_stats_get", "ptx_trace_primary_ids", "ptx_trace_rays", "ptx_film_rng_state",
+]
+
+_lib = None
+
+
+def lib():
+    """Load libptx.so (raises if it has not been built: there is no Python/CPU stand-in)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise PtxError(-3, f"{LIB_PATH} not built; run __graft_entry__.build()")
+        L = C.CDLL(LIB_PATH)
+        L.ptx_last_error.restype = C.c_char_p
+        L.ptx_last_error.argtypes = [C.c_void_p]
+        L.ptx_version.restype = C.c_char_p
+        for name in ("ptx_ctx_destroy", "ptx_scene_destroy", "ptx_film_destroy", "ptx_free_primitives"):
+            getattr(L, name).restype = None
+            getattr(L, name).argtypes = [C.c_void_p]
+        L.ptx_film_set_sample_count.argtypes = [C.c_void_p, C.c_float]
+        L.ptx_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_float, C.c_void_p, C.c_void_p]
+        L.ptx_film_reset.argtypes = [C.c_void_p, C.c_uint64]
+        L.ptx_film_rng_state.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]
+        L.ptx_scene_from_primitives.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        L.ptx_scene_from_triangles.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t,
+                                               C.c_void_p, C.c_void_p]
+        L.ptx_scene_get_primitives.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        L.ptx_scene_load.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_void_p]
+        L.ptx_parse_scene_file.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ptx_film_write.argtypes = [C.c_void_p, C.c_char_p]
+        L.ptx_film_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.ptx_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ptx_trace_primary_ids.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.ptx_film_resolve_rgb8.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        L.ptx_film_read_linear.argtypes = [C.c_void_p, C.c_void_p]
+        L.ptx_film_device_buffer.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ptx_camera_set.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float]
+        _lib = L
+    return _lib
+
+
+def _check(rc, ctx=None):
+    if rc < 0:
+        msg = lib().ptx_last_error(ctx)
+        raise PtxError(rc, msg.decode() if msg else "")
+    return rc
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def parse_scene_file(path, convert_quads=False, subdivision=0, mirror_from_mtl=False):
+    """Host-only parse (loadOBJ semantics): structured numpy array in the reference's primitive numbering."""
+    opts = LoadOpts(int(convert_quads), int(subdivision), 0, int(mirror_from_mtl), 0)
+    p = C.c_void_p()
+    n = C.c_int64()
+    _check(lib().ptx_parse_scene_file(os.fspath(path).encode(), C.byref(opts), C.byref(p), C.byref(n)))
+    try:
+        buf = (C.c_char * (n.value * C.sizeof(Primitive))).from_address(p.value)
+        return np.frombuffer(buf, dtype=PRIM_DTYPE).copy()
+    finally:
+        lib().ptx_free_primitives(p)
+
+
+def default_camera(width, height):
+    cam = Camera()
+    _check(lib().ptx_camera_default(C.byref(cam), int(width), int(height)))
+    return cam
+
+
+def look_at_camera(eye, at, up, vfov, width, height, orbit=False):
+    cam = Camera()
+    cam.image_width, cam.image_height = int(width), int(height)
+    f3 = C.c_float * 3
+    _check(lib().ptx_camera_set(C.byref(cam), f3(*eye), f3(*at), f3(*up), C.c_float(vfov), C.c_float(float(width) / float(height))))
+    if orbit:
+        _check(lib().ptx_camera_orbit(C.byref(cam)))
+    return cam
+
+
+class Context:
+    """One CUDA device + stream (ptx_ctx)."""
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        _check(lib().ptx_ctx_create(int(device), C.byref(self._h)))
+        self.device = int(device)
+
+    def close(self):
+        if self._h:
+            lib().ptx_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def sync(self):
+        _check(lib().ptx_sync(self._h), self._h)
+
+    def device_info(self):
+        sm, ma, mi, mem = C.c_int(), C.c_int(), C.c_int(), C.c_size_t()
+        _check(lib().ptx_ctx_device_info(self._h, C.byref(sm), C.byref(ma), C.byref(mi), C.byref(mem)), self._h)
+        return {"sm_count": sm.value, "cc": (ma.value, mi.value), "total_mem": mem.value}
+
+    # -- scenes -------------------------------------------------------------------------------
+    def load_scene(self, path, convert_quads=False, subdivision=0, mirror_from_mtl=False):
+        opts = LoadOpts(int(convert_quads), int(subdivision), 0, int(mirror_from_mtl), 0)
+        h = C.c_void_p()
+        _check(lib().ptx_scene_load(self._h, os.fspath(path).encode(), C.byref(opts), C.byref(h)), self._h)
+        return Scene(self, h)
+
+    def scene_from_primitives(self, prims, builder=0, max_leaf=0):
+        prims = np.ascontiguousarray(prims, dtype=PRIM_DTYPE)
+        bo = BuildOpts(int(builder), 0, int(max_leaf), 0)
+        h = C.c_void_p()
+        _check(lib().ptx_scene_from_primitives(self._h, _ptr(prims), len(prims), C.byref(bo), C.byref(h)), self._h)
+        return Scene(self, h)
+
+    def scene_from_triangles(self, verts, mat_id=None, materials=None, normals=None, builder=0, max_leaf=0):
+        verts = np.ascontiguousarray(verts, dtype=np.float32).reshape(-1, 9)
+        n = len(verts)
+        mid = None if mat_id is None else np.ascontiguousarray(mat_id, dtype=np.uint32)
+        nrm = None if normals is None else np.ascontiguousarray(normals, dtype=np.float32).reshape(-1, 3)
+        mats = (Material * max(len(materials or []), 1))()
+        for i, m in enumerate(materials or []):
+            mats[i].bsdf[:] = m["bsdf"]; mats[i].Le[:] = m.get("Le", (0, 0, 0)); mats[i].type = int(m.get("type", 0))
+        bo = BuildOpts(int(builder), 0, int(max_leaf), 0)
+        h = C.c_void_p()
+        _check(lib().ptx_scene_from_triangles(self._h, _ptr(verts), None if nrm is None else _ptr(nrm), None if mid is None else _ptr(mid),
+                                              mats, n, len(materials or []), C.byref(bo), C.byref(h)), self._h)
+        return Scene(self, h)
+
+    def create_film(self, width, height):
+        h = C.c_void_p()
+        _check(lib().ptx_film_create(self._h, int(width), int(height), C.byref(h)), self._h)
+        return Film(self, h, int(width), int(height))
+
+    # -- rendering ----------------------------------------------------------------------------
+    def render(self, scene, camera, film, spp, max_depth=5, rng_mode=RNG_XORWOW_COMPAT, accumulate=False, shard_mode=SHARD_NONE,
+               shard_rank=0, shard_world=1, pipeline=PIPELINE_WAVEFRONT, stage_timing=False, count_work=False, sampling_mode=0):
+        o = RenderOpts()
+        o.spp, o.max_depth, o.rng_mode, o.sampling_mode = int(spp), int(max_depth), int(rng_mode), int(sampling_mode)
+        o.accumulate, o.shard_mode, o.shard_rank, o.shard_world = int(accumulate), int(shard_mode), int(shard_rank), int(shard_world)
+        o.pipeline = int(pipeline)
+        o.reserved[0] = (1 if stage_timing else 0) | (2 if count_work else 0)
+        _check(lib().ptx_render(self._h, scene._h, C.byref(camera), film._h, C.byref(o)), self._h)
+        return self.render_stats()
+
+    def render_stats(self):
+        st = RenderStats()
+        _check(lib().ptx_render_stats_get(self._h, C.byref(st)), self._h)
+        return {k: getattr(st, k) for k, _ in RenderStats._fields_}
+
+    def trace_primary_ids(self, scene, camera, width, height):
+        ids = np.empty((height, width), np.int32)
+        ts = np.empty((height, width), np.float32)
+        _check(lib().ptx_trace_primary_ids(self._h, scene._h, C.byref(camera), int(width), int(height), _ptr(ids), _ptr(ts)), self._h)
+        return ids, ts
+
+    def trace_rays(self, scene, rays, t_min=1e-4):
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
+        ids = np.empty(len(rays), np.int32)
+        ts = np.empty(len(rays), np.float32)
+        _check(lib().ptx_trace_rays(self._h, scene._h, _ptr(rays), len(rays), C.c_float(t_min), _ptr(ids), _ptr(ts)), self._h)
+        return ids, ts
+
+
+class Scene:
+    def __init__(self, ctx, handle):
+        self.ctx, self._h = ctx, handle
+
+    def close(self):
+        if self._h:
+            lib().ptx_scene_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def stats(self):
+        st = SceneStats()
+        _check(lib().ptx_scene_stats_get(self._h, C.byref(st)))
+        d = {k: getattr(st, k) for k, _ in SceneStats._fields_}
+        d["bounds_min"], d["bounds_max"] = list(st.bounds_min), list(st.bounds_max)
+        return d
+
+    def rebuild(self, builder=0, sah_bins=0, max_leaf=0):
+        bo = BuildOpts(int(builder), int(sah_bins), int(max_leaf), 0)
+        _check(lib().ptx_scene_build_accel(self._h, C.byref(bo)), self.ctx._h)
+
+    def primitives(self):
+        n = _check(lib().ptx_scene_get_primitives(self._h, None, 0))
+        out = np.zeros(n, dtype=PRIM_DTYPE)
+        if n:
+            _check(lib().ptx_scene_get_primitives(self._h, _ptr(out), n))
+        return out
+
+
+class Film:
+    def __init__(self, ctx, handle, w, h):
+        self.ctx, self._h, self.width, self.height = ctx, handle, w, h
+
+    def close(self):
+        if self._h:
+            lib().ptx_film_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def reset(self, seed_base=2023):
+        _check(lib().ptx_film_reset(self._h, int(seed_base)), self.ctx._h)
+
+    def clear(self):
+        _check(lib().ptx_film_clear(self._h), self.ctx._h)
+
+    def rgb8(self, flip_y=False, out=None):
+        img = out if out is not None else np.empty((self.height, self.width, 3), np.uint8)
+        _check(lib().ptx_film_resolve_rgb8(self._h, _ptr(img), 0, int(flip_y)), self.ctx._h)
+        return img
+
+    def linear(self):
+        img = np.empty((self.height, self.width, 3), np.float32)
+        _check(lib().ptx_film_read_linear(self._h, _ptr(img)), self.ctx._h)
+        return img
+
+    def write(self, path):
+        _check(lib().ptx_film_write(self._h, os.fspath(path).encode()), self.ctx._h)
+
+    def device_buffer(self):
+        p, n = C.c_void_p(), C.c_size_t()
+        _check(lib().ptx_film_device_buffer(self._h, C.byref(p), C.byref(n)), self.ctx._h)
+        return p.value, n.value
+
+    def set_sample_count(self, spp_total):
+        _check(lib().ptx_film_set_sample_count(self._h, float(spp_total)))
+
+    def rng_state(self, first=0, n=None):
+        n = self.width * self.height - first if n is None else n
+        out = np.empty((n, 6), np.uint32)
+        _check(lib().ptx_film_rng_state(self._h, int(first), int(n), _ptr(out)), self.ctx._h)
+        return out

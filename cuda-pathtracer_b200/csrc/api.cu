@@ -1,0 +1,688 @@
+// api.cu -- implementation of the C ABI declared in include/ptx.h.
+//
+// Host-side orchestration only: scene packing / upload, film buffers, and the wavefront loop that
+// launches the sm_100a kernels of kernels.cu.  There is no CPU rendering path in this library: every
+// entry point that produces pixels or hits launches CUDA kernels and fails with PTX_ERR_NO_DEVICE /
+// PTX_ERR_CUDA when that is impossible.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/ptx.h"
+#include "bvh_host.h"
+#include "kernels.cuh"
+#include "loader.h"
+#include "rng.h"
+#include "scene_pack.h"
+
+using namespace ptx;
+
+namespace {
+thread_local std::string g_last_error;
+}
+
+struct ptx_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    cudaDeviceProp prop{};
+    uint32_t* d_jump = nullptr;                 // XORWOW jump matrices J[0..63]
+    // wavefront state (grown on demand, reused across renders)
+    WaveState ws{};
+    uint32_t* d_scratch = nullptr; size_t scratch_words = 0;
+    unsigned long long* h_counters = nullptr;   // pinned
+    int slot_key[5] = {-1, -1, -1, -1, -1};     // (w, h, shard_mode, rank, world) the slot map was built for
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::vector<cudaEvent_t> stage_events;
+    ptx_render_stats stats{};
+};
+
+struct ptx_scene {
+    ptx_ctx* ctx = nullptr;
+    std::vector<ptx_primitive> prims;           // reference numbering (empty for triangle-soup scenes)
+    PackedScene packed;                          // host copy kept for rebuilds
+    u32x4* d_nodes = nullptr; f32x4* d_tris = nullptr; f32x4* d_prim_shade = nullptr; f32x4* d_materials = nullptr;
+    SceneView view{};
+    ptx_scene_stats stats{};
+};
+
+struct ptx_film {
+    ptx_ctx* ctx = nullptr;
+    int w = 0, h = 0;
+    float4* d_accum = nullptr; uint4* d_rngA = nullptr; uint2* d_rngB = nullptr; uint8_t* d_rgb8 = nullptr; float* d_linear = nullptr;
+    float total_spp = 0.f;
+    uint32_t sample_base = 0;                    // global index of the next frame's first sample (progressive mode)
+    unsigned long long seed_base = 2023ull;      // integrator.h:279
+    FilmView view() const { FilmView f; f.accum = d_accum; f.rngA = d_rngA; f.rngB = d_rngB; f.width = w; f.height = h; return f; }
+};
+
+namespace {
+
+int fail(ptx_ctx* ctx, int code, const std::string& msg) {
+    g_last_error = msg;
+    if (ctx) ctx->err = msg;
+    return code;
+}
+int cuda_fail(ptx_ctx* ctx, cudaError_t e, const char* what) {
+    return fail(ctx, PTX_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define PTX_CUDA(ctx, call)                                              \
+    do {                                                                 \
+        cudaError_t e_ = (call);                                         \
+        if (e_ != cudaSuccess) return cuda_fail((ctx), e_, #call);       \
+    } while (0)
+
+CameraView camera_view(const ptx_camera& c, int w, int h) {
+    CameraView v;
+    memcpy(v.origin, c.origin, 12); memcpy(v.llc, c.lower_left_corner, 12);
+    memcpy(v.horizontal, c.horizontal, 12); memcpy(v.vertical, c.vertical, 12);
+    v.width = w; v.height = h;
+    return v;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* ptx_version(void) { return "ptx-b200 0.1 (sm_100a)"; }
+
+const char* ptx_last_error(const ptx_ctx* ctx) { return ctx ? ctx->err.c_str() : g_last_error.c_str(); }
+
+int ptx_ctx_create(int device, ptx_ctx** out) {
+    if (!out) return fail(nullptr, PTX_ERR_INVALID, "ptx_ctx_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(nullptr, PTX_ERR_NO_DEVICE, std::string("no CUDA device available (this library has no CPU path): ") +
+                                                     (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0"));
+    if (device < 0 || device >= n) return fail(nullptr, PTX_ERR_INVALID, "ptx_ctx_create: bad device index");
+    ptx_ctx* c = new ptx_ctx();
+    c->device = device;
+    PTX_CUDA(c, cudaSetDevice(device));
+    PTX_CUDA(c, cudaGetDeviceProperties(&c->prop, device));
+    PTX_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    PTX_CUDA(c, cudaEventCreate(&c->ev0));
+    PTX_CUDA(c, cudaEventCreate(&c->ev1));
+    PTX_CUDA(c, cudaMallocHost(&c->h_counters, sizeof(unsigned long long) * CTR_COUNT));
+    PTX_CUDA(c, cudaMalloc(&c->ws.counters, sizeof(unsigned long long) * CTR_COUNT));
+    std::vector<uint32_t> jump((size_t)kXorwowJumps * kXorwowJumpWords);
+    xorwow_build_jump_tables(jump.data());
+    PTX_CUDA(c, cudaMalloc(&c->d_jump, jump.size() * sizeof(uint32_t)));
+    PTX_CUDA(c, cudaMemcpy(c->d_jump, jump.data(), jump.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    *out = c;
+    return PTX_OK;
+}
+
+void ptx_ctx_destroy(ptx_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    cudaFree(c->ws.A); cudaFree(c->ws.B); cudaFree(c->ws.C); cudaFree(c->ws.D);
+    cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]); cudaFree(c->ws.slot_pixel); cudaFree(c->ws.counters);
+    cudaFree(c->d_scratch); cudaFree(c->d_jump);
+    cudaFreeHost(c->h_counters);
+    for (auto ev : c->stage_events) cudaEventDestroy(ev);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int ptx_sync(ptx_ctx* c) {
+    if (!c) return fail(nullptr, PTX_ERR_INVALID, "ptx_sync: ctx is NULL");
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return PTX_OK;
+}
+
+int ptx_ctx_device_info(const ptx_ctx* c, int* sm_count, int* cc_major, int* cc_minor, size_t* total_mem) {
+    if (!c) return fail(nullptr, PTX_ERR_INVALID, "ptx_ctx_device_info: ctx is NULL");
+    if (sm_count) *sm_count = c->prop.multiProcessorCount;
+    if (cc_major) *cc_major = c->prop.major;
+    if (cc_minor) *cc_minor = c->prop.minor;
+    if (total_mem) *total_mem = c->prop.totalGlobalMem;
+    return PTX_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// camera: host maths of the reference's Sensor (rendering/sensor.h:16-67), same operation order
+// ---------------------------------------------------------------------------------------------
+int ptx_camera_update(ptx_camera* cam) {
+    if (!cam) return fail(nullptr, PTX_ERR_INVALID, "ptx_camera_update: cam is NULL");
+    float theta = (float)((double)cam->vfov * 3.14159265358979323846 / (double)180.0f);   // `vfov * M_PI / 180.0f`
+    float half_height = tanf(theta / 2.0f);
+    float half_width = cam->aspect * half_height;
+    vec3 origin = ld3(cam->origin);
+    vec3 w = unit(origin - ld3(cam->lookat));
+    vec3 u = unit(cross(ld3(cam->vup), w));
+    vec3 v = cross(w, u);
+    st3(cam->lower_left_corner, ((origin - half_width * u) - half_height * v) - w);
+    st3(cam->horizontal, (2 * half_width) * u);
+    st3(cam->vertical, (2 * half_height) * v);
+    return PTX_OK;
+}
+
+int ptx_camera_set(ptx_camera* cam, const float eye[3], const float at[3], const float up[3], float vfov_deg, float aspect) {
+    if (!cam || !eye || !at || !up) return fail(nullptr, PTX_ERR_INVALID, "ptx_camera_set: NULL argument");
+    memcpy(cam->origin, eye, 12); memcpy(cam->lookat, at, 12); memcpy(cam->vup, up, 12);
+    cam->vfov = vfov_deg; cam->aspect = aspect;
+    cam->radius = length(ld3(eye) - ld3(at));
+    cam->yaw = 90.0f; cam->pitch = 0.0f;
+    if (cam->image_width <= 0) cam->image_width = 0;
+    if (cam->image_height <= 0) cam->image_height = 0;
+    return ptx_camera_update(cam);
+}
+
+int ptx_camera_orbit(ptx_camera* cam) {
+    if (!cam) return fail(nullptr, PTX_ERR_INVALID, "ptx_camera_orbit: cam is NULL");
+    float yawRad = (float)((double)cam->yaw * 3.14159265358979323846 / (double)180.0f);
+    float pitchRad = (float)((double)cam->pitch * 3.14159265358979323846 / (double)180.0f);
+    cam->origin[0] = cam->lookat[0] + cam->radius * cosf(pitchRad) * cosf(yawRad);
+    cam->origin[1] = cam->lookat[1] + cam->radius * sinf(pitchRad);
+    cam->origin[2] = cam->lookat[2] + cam->radius * cosf(pitchRad) * sinf(yawRad);
+    return ptx_camera_update(cam);
+}
+
+int ptx_camera_default(ptx_camera* cam, int width, int height) {
+    if (!cam || width <= 0 || height <= 0) return fail(nullptr, PTX_ERR_INVALID, "ptx_camera_default: bad argument");
+    memset(cam, 0, sizeof *cam);
+    const float eye[3] = {0.5f, 3.0f, 8.5f}, at[3] = {0.0f, 2.5f, 0.0f}, up[3] = {0.0f, 1.0f, 0.0f};
+    cam->image_width = width; cam->image_height = height;
+    ptx_camera_set(cam, eye, at, up, 40.0f, 1.0f);                 // RenderState ctor, application_state.h:88
+    cam->aspect = (float)width / (float)height;                     // allocateBuffers, application_state.h:106-109
+    ptx_camera_update(cam);
+    return ptx_camera_orbit(cam);                                   // renderFrame, application.h:162
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// scene
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+void free_accel(ptx_scene* s) {
+    cudaFree(s->d_nodes); cudaFree(s->d_tris);
+    s->d_nodes = nullptr; s->d_tris = nullptr;
+}
+
+int build_accel(ptx_scene* s, const ptx_build_opts* bo) {
+    ptx_ctx* c = s->ctx;
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    int builder = bo ? bo->builder : 0;
+    int bins = bo && bo->sah_bins > 0 ? bo->sah_bins : 16;
+    int max_leaf = bo && bo->max_leaf > 0 ? bo->max_leaf : 3;
+    free_accel(s);
+    size_t n = s->packed.tris.size();
+    if (n > 0x7FFFFFF0ull) return fail(c, PTX_ERR_INVALID, "scene too large: triangle count must fit 31 bits");
+    PTX_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    Bvh8Result r;
+    {
+        Bvh2 b2;
+        build_bvh2_sah(s->packed.tris.data(), n, bins, max_leaf, b2);
+        collapse_bvh8(b2, s->packed.tris.data(), n, r);
+        builder = 1;
+    }
+    size_t node_bytes = r.nodes.size() * sizeof(u32x4), tri_bytes = std::max<size_t>(r.tris.size(), 1) * sizeof(f32x4);
+    PTX_CUDA(c, cudaMalloc(&s->d_nodes, node_bytes));
+    PTX_CUDA(c, cudaMalloc(&s->d_tris, tri_bytes));
+    PTX_CUDA(c, cudaMemcpyAsync(s->d_nodes, r.nodes.data(), node_bytes, cudaMemcpyHostToDevice, c->stream));
+    if (!r.tris.empty())
+        PTX_CUDA(c, cudaMemcpyAsync(s->d_tris, r.tris.data(), r.tris.size() * sizeof(f32x4), cudaMemcpyHostToDevice, c->stream));
+    PTX_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+    float ms = 0.f; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    s->view.nodes = s->d_nodes; s->view.tris = s->d_tris;
+    s->view.n_nodes = (uint32_t)(r.nodes.size() / kNodeQuads);
+    s->view.n_tris = (uint32_t)r.tri_src.size();
+    s->stats.n_nodes = s->view.n_nodes; s->stats.n_triangles = s->view.n_tris;
+    s->stats.node_bytes = (int64_t)node_bytes; s->stats.triangle_bytes = (int64_t)(r.tris.size() * sizeof(f32x4));
+    s->stats.sah_cost = r.sah_cost; s->stats.max_depth = r.max_depth; s->stats.builder = builder; s->stats.build_ms = ms;
+    st3(s->stats.bounds_min, r.bounds.lo); st3(s->stats.bounds_max, r.bounds.hi);
+    return PTX_OK;
+}
+
+int finish_scene(ptx_ctx* c, ptx_scene* s, const ptx_build_opts* bo, ptx_scene** out) {
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    size_t np = s->packed.prim_shade.size(), nm = s->packed.materials.size();
+    PTX_CUDA(c, cudaMalloc(&s->d_prim_shade, std::max<size_t>(np, 1) * sizeof(f32x4)));
+    PTX_CUDA(c, cudaMalloc(&s->d_materials, std::max<size_t>(nm, 2) * sizeof(f32x4)));
+    if (np) PTX_CUDA(c, cudaMemcpy(s->d_prim_shade, s->packed.prim_shade.data(), np * sizeof(f32x4), cudaMemcpyHostToDevice));
+    if (nm) PTX_CUDA(c, cudaMemcpy(s->d_materials, s->packed.materials.data(), nm * sizeof(f32x4), cudaMemcpyHostToDevice));
+    s->view.prim_shade = s->d_prim_shade; s->view.materials = s->d_materials;
+    s->view.n_prims = (uint32_t)np; s->view.n_mats = (uint32_t)(nm / 2);
+    s->stats.n_primitives = (int64_t)np; s->stats.n_materials = (int64_t)(nm / 2);
+    s->stats.shading_bytes = (int64_t)((np + nm) * sizeof(f32x4));
+    int rc = build_accel(s, bo);
+    if (rc != PTX_OK) { ptx_scene_destroy(s); return rc; }
+    *out = s;
+    return PTX_OK;
+}
+
+bool has_suffix(const std::string& s, const char* suf) {
+    size_t n = strlen(suf);
+    if (s.size() < n) return false;
+    for (size_t i = 0; i < n; i++) if (tolower((unsigned char)s[s.size() - n + i]) != suf[i]) return false;
+    return true;
+}
+
+int parse_file(const char* path, const ptx_load_opts* opts, std::vector<ptx_primitive>& prims, std::string& err) {
+    std::string p = path ? path : "";
+    if (has_suffix(p, ".obj")) {
+        if (!load_obj(p, opts && opts->mirror_from_mtl, prims, err)) return PTX_ERR_IO;
+    } else {
+        err = "unsupported scene format (supported: .obj): " + p;      // loadScene, file_manager.h:291-315
+        return PTX_ERR_UNSUPPORTED;
+    }
+    if (opts && opts->convert_quads) split_quads(prims);                // application_state.h:404-407
+    if (opts && opts->subdivision > 0) subdivide(prims, opts->subdivision);   // application_state.h:409-413
+    return PTX_OK;
+}
+
+}  // namespace
+
+int ptx_parse_scene_file(const char* path, const ptx_load_opts* opts, ptx_primitive** prims_out, int64_t* n_out) {
+    if (!path || !prims_out || !n_out) return fail(nullptr, PTX_ERR_INVALID, "ptx_parse_scene_file: NULL argument");
+    std::vector<ptx_primitive> prims; std::string err;
+    int rc = parse_file(path, opts, prims, err);
+    if (rc != PTX_OK) return fail(nullptr, rc, err);
+    ptx_primitive* buf = (ptx_primitive*)malloc(sizeof(ptx_primitive) * std::max<size_t>(prims.size(), 1));
+    if (!buf) return fail(nullptr, PTX_ERR_NOMEM, "out of host memory");
+    memcpy(buf, prims.data(), sizeof(ptx_primitive) * prims.size());
+    *prims_out = buf; *n_out = (int64_t)prims.size();
+    return PTX_OK;
+}
+void ptx_free_primitives(ptx_primitive* prims) { free(prims); }
+
+int ptx_scene_from_primitives(ptx_ctx* c, const ptx_primitive* prims, int64_t n, const ptx_build_opts* bo, ptx_scene** out) {
+    if (!c || !out || n < 0 || (n > 0 && !prims)) return fail(c, PTX_ERR_INVALID, "ptx_scene_from_primitives: bad argument");
+    ptx_scene* s = new ptx_scene();
+    s->ctx = c;
+    s->prims.assign(prims, prims + n);
+    pack_primitives(prims, (size_t)n, s->packed);
+    return finish_scene(c, s, bo, out);
+}
+
+int ptx_scene_from_triangles(ptx_ctx* c, const float* v, const float* normals, const uint32_t* mat_id, const ptx_material* mats,
+                             size_t n_tri, size_t n_mat, const ptx_build_opts* bo, ptx_scene** out) {
+    if (!c || !out || (n_tri > 0 && !v) || (n_mat > 0 && !mats)) return fail(c, PTX_ERR_INVALID, "ptx_scene_from_triangles: bad argument");
+    ptx_scene* s = new ptx_scene();
+    s->ctx = c;
+    pack_triangles(v, normals, mat_id, mats, n_tri, n_mat, s->packed);
+    return finish_scene(c, s, bo, out);
+}
+
+int ptx_scene_load(ptx_ctx* c, const char* path, const ptx_load_opts* opts, ptx_scene** out) {
+    if (!c || !path || !out) return fail(c, PTX_ERR_INVALID, "ptx_scene_load: NULL argument");
+    std::vector<ptx_primitive> prims; std::string err;
+    int rc = parse_file(path, opts, prims, err);
+    if (rc != PTX_OK) return fail(c, rc, err);
+    return ptx_scene_from_primitives(c, prims.data(), (int64_t)prims.size(), nullptr, out);
+}
+
+int ptx_scene_build_accel(ptx_scene* s, const ptx_build_opts* opts) {
+    if (!s) return fail(nullptr, PTX_ERR_INVALID, "ptx_scene_build_accel: scene is NULL");
+    return build_accel(s, opts);
+}
+
+int ptx_scene_stats_get(const ptx_scene* s, ptx_scene_stats* out) {
+    if (!s || !out) return fail(nullptr, PTX_ERR_INVALID, "ptx_scene_stats_get: NULL argument");
+    *out = s->stats;
+    return PTX_OK;
+}
+
+int ptx_scene_get_primitives(const ptx_scene* s, ptx_primitive* out, int64_t capacity) {
+    if (!s || (capacity > 0 && !out)) return fail(nullptr, PTX_ERR_INVALID, "ptx_scene_get_primitives: NULL argument");
+    int64_t n = std::min<int64_t>(capacity, (int64_t)s->prims.size());
+    if (n > 0) memcpy(out, s->prims.data(), sizeof(ptx_primitive) * (size_t)n);
+    return (int)std::min<int64_t>((int64_t)s->prims.size(), 0x7FFFFFFF);
+}
+
+void ptx_scene_destroy(ptx_scene* s) {
+    if (!s) return;
+    cudaSetDevice(s->ctx->device);
+    cudaStreamSynchronize(s->ctx->stream);
+    free_accel(s);
+    cudaFree(s->d_prim_shade); cudaFree(s->d_materials);
+    delete s;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// film
+// ---------------------------------------------------------------------------------------------
+int ptx_film_create(ptx_ctx* c, int width, int height, ptx_film** out) {
+    if (!c || !out || width <= 0 || height <= 0) return fail(c, PTX_ERR_INVALID, "ptx_film_create: bad argument");
+    if ((long long)width * height > 0x7FFFFFFFll) return fail(c, PTX_ERR_INVALID, "ptx_film_create: image too large");
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    ptx_film* f = new ptx_film();
+    f->ctx = c; f->w = width; f->h = height;
+    size_t npix = (size_t)width * height;
+    cudaError_t e;
+    if ((e = cudaMalloc(&f->d_accum, npix * sizeof(float4))) != cudaSuccess || (e = cudaMalloc(&f->d_rngA, npix * sizeof(uint4))) != cudaSuccess ||
+        (e = cudaMalloc(&f->d_rngB, npix * sizeof(uint2))) != cudaSuccess || (e = cudaMalloc(&f->d_rgb8, npix * 3)) != cudaSuccess ||
+        (e = cudaMalloc(&f->d_linear, npix * 3 * sizeof(float))) != cudaSuccess) {
+        ptx_film_destroy(f);
+        return cuda_fail(c, e, "ptx_film_create: cudaMalloc");
+    }
+    *out = f;
+    return ptx_film_reset(f, 2023ull);
+}
+
+int ptx_film_reset(ptx_film* f, uint64_t seed_base) {
+    if (!f) return fail(nullptr, PTX_ERR_INVALID, "ptx_film_reset: film is NULL");
+    ptx_ctx* c = f->ctx;
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    f->seed_base = seed_base;
+    launch_rng_init(c->stream, f->view(), seed_base, c->d_jump);
+    PTX_CUDA(c, cudaGetLastError());
+    return ptx_film_clear(f);
+}
+
+int ptx_film_clear(ptx_film* f) {
+    if (!f) return fail(nullptr, PTX_ERR_INVALID, "ptx_film_clear: film is NULL");
+    ptx_ctx* c = f->ctx;
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    PTX_CUDA(c, cudaMemsetAsync(f->d_accum, 0, (size_t)f->w * f->h * sizeof(float4), c->stream));
+    f->total_spp = 0.f; f->sample_base = 0;
+    return PTX_OK;
+}
+
+int ptx_film_resolve_rgb8(ptx_film* f, uint8_t* dst, int dst_is_device, int flip_y) {
+    if (!f || !dst) return fail(nullptr, PTX_ERR_INVALID, "ptx_film_resolve_rgb8: NULL argument");
+    ptx_ctx* c = f->ctx;
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    float inv = f->total_spp > 0.f ? 1.0f / f->total_spp : 0.f;      // `color /= float(spp)`: k = 1/spp, multiply
+    size_t bytes = (size_t)f->w * f->h * 3;
+    launch_resolve(c->stream, f->view(), inv, dst_is_device ? dst : f->d_rgb8, flip_y);
+    PTX_CUDA(c, cudaGetLastError());
+    if (!dst_is_device) PTX_CUDA(c, cudaMemcpyAsync(dst, f->d_rgb8, bytes, cudaMemcpyDeviceToHost, c->stream));
+    PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return PTX_OK;
+}
+
+int ptx_film_read_linear(ptx_film* f, float* rgb_host) {
+    if (!f || !rgb_host) return fail(nullptr, PTX_ERR_INVALID, "ptx_film_read_linear: NULL argument");
+    ptx_ctx* c = f->ctx;
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    float inv = f->total_spp > 0.f ? 1.0f / f->total_spp : 0.f;
+    launch_film_scale(c->stream, f->view(), inv, f->d_linear);
+    PTX_CUDA(c, cudaGetLastError());
+    PTX_CUDA(c, cudaMemcpyAsync(rgb_host, f->d_linear, (size_t)f->w * f->h * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return PTX_OK;
+}
+
+int ptx_film_write(ptx_film* f, const char* path) {
+    if (!f || !path) return fail(nullptr, PTX_ERR_INVALID, "ptx_film_write: NULL argument");
+    std::string p = path;
+    size_t npix = (size_t)f->w * f->h;
+    FILE* fp = nullptr;
+    if (has_suffix(p, ".pfm")) {
+        std::vector<float> lin(npix * 3);
+        int rc = ptx_film_read_linear(f, lin.data());
+        if (rc != PTX_OK) return rc;
+        if (!(fp = fopen(path, "wb"))) return fail(f->ctx, PTX_ERR_IO, "cannot write " + p);
+        fprintf(fp, "PF\n%d %d\n-1.0\n", f->w, f->h);                  // PFM rows run bottom to top, like the film
+        fwrite(lin.data(), sizeof(float), lin.size(), fp);
+    } else {
+        std::vector<uint8_t> img(npix * 3);
+        int rc = ptx_film_resolve_rgb8(f, img.data(), 0, 1);             // vertical flip like the PNG export (ui_windows.h:205-207)
+        if (rc != PTX_OK) return rc;
+        if (!(fp = fopen(path, "wb"))) return fail(f->ctx, PTX_ERR_IO, "cannot write " + p);
+        fprintf(fp, "P6\n%d %d\n255\n", f->w, f->h);
+        fwrite(img.data(), 1, img.size(), fp);
+    }
+    fclose(fp);
+    return PTX_OK;
+}
+
+int ptx_film_device_buffer(ptx_film* f, void** dev_ptr, size_t* bytes) {
+    if (!f || !dev_ptr) return fail(nullptr, PTX_ERR_INVALID, "ptx_film_device_buffer: NULL argument");
+    *dev_ptr = f->d_accum;
+    if (bytes) *bytes = (size_t)f->w * f->h * sizeof(float4);
+    return PTX_OK;
+}
+
+int ptx_film_set_sample_count(ptx_film* f, float spp_total) {
+    if (!f) return fail(nullptr, PTX_ERR_INVALID, "ptx_film_set_sample_count: film is NULL");
+    f->total_spp = spp_total;
+    return PTX_OK;
+}
+
+int ptx_film_rng_state(ptx_film* f, int64_t first, int64_t n, uint32_t* out_host) {
+    if (!f || !out_host || first < 0 || n < 0 || first + n > (int64_t)f->w * f->h) return fail(nullptr, PTX_ERR_INVALID, "ptx_film_rng_state: bad range");
+    ptx_ctx* c = f->ctx;
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    std::vector<uint4> a((size_t)n); std::vector<uint2> b((size_t)n);
+    PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (n) {
+        PTX_CUDA(c, cudaMemcpy(a.data(), f->d_rngA + first, (size_t)n * sizeof(uint4), cudaMemcpyDeviceToHost));
+        PTX_CUDA(c, cudaMemcpy(b.data(), f->d_rngB + first, (size_t)n * sizeof(uint2), cudaMemcpyDeviceToHost));
+    }
+    for (int64_t i = 0; i < n; i++) {
+        uint32_t* o = out_host + 6 * i;
+        o[0] = a[i].x; o[1] = a[i].y; o[2] = a[i].z; o[3] = a[i].w; o[4] = b[i].x; o[5] = b[i].y;
+    }
+    return PTX_OK;
+}
+
+void ptx_film_destroy(ptx_film* f) {
+    if (!f) return;
+    cudaSetDevice(f->ctx->device);
+    cudaStreamSynchronize(f->ctx->stream);
+    cudaFree(f->d_accum); cudaFree(f->d_rngA); cudaFree(f->d_rngB); cudaFree(f->d_rgb8); cudaFree(f->d_linear);
+    delete f;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// render: the wavefront loop
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+int ensure_wave_capacity(ptx_ctx* c, uint32_t slots, uint32_t owned) {
+    uint32_t need = std::max(slots, owned);
+    if (need > c->ws.capacity) {
+        cudaFree(c->ws.A); cudaFree(c->ws.B); cudaFree(c->ws.C); cudaFree(c->ws.D);
+        cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]); cudaFree(c->ws.slot_pixel);
+        c->ws.A = c->ws.B = c->ws.C = nullptr; c->ws.D = nullptr; c->ws.queue[0] = c->ws.queue[1] = c->ws.slot_pixel = nullptr;
+        c->ws.capacity = 0; c->slot_key[0] = -1;
+        size_t n = need;
+        PTX_CUDA(c, cudaMalloc(&c->ws.A, n * sizeof(float4)));
+        PTX_CUDA(c, cudaMalloc(&c->ws.B, n * sizeof(float4)));
+        PTX_CUDA(c, cudaMalloc(&c->ws.C, n * sizeof(float4)));
+        PTX_CUDA(c, cudaMalloc(&c->ws.D, n * sizeof(uint2)));
+        PTX_CUDA(c, cudaMalloc(&c->ws.queue[0], n * sizeof(uint32_t)));
+        PTX_CUDA(c, cudaMalloc(&c->ws.queue[1], n * sizeof(uint32_t)));
+        PTX_CUDA(c, cudaMalloc(&c->ws.slot_pixel, n * sizeof(uint32_t)));
+        c->ws.capacity = need;
+    }
+    size_t words = (size_t)need / 1024 + 8;
+    if (words > c->scratch_words) {
+        cudaFree(c->d_scratch); c->d_scratch = nullptr; c->scratch_words = 0;
+        PTX_CUDA(c, cudaMalloc(&c->d_scratch, words * sizeof(uint32_t)));
+        c->scratch_words = words;
+    }
+    return PTX_OK;
+}
+
+constexpr uint32_t kPhiloxPool = 1u << 22;   // slots in flight in counter-RNG mode
+
+}  // namespace
+
+int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_film* film, const ptx_render_opts* opts) {
+    if (!c || !scene || !cam || !film || !opts) return fail(c, PTX_ERR_INVALID, "ptx_render: NULL argument");
+    if (scene->ctx != c || film->ctx != c) return fail(c, PTX_ERR_INVALID, "ptx_render: scene/film belong to another context");
+    if (opts->sampling_mode != PTX_SAMPLING_BSDF)
+        return fail(c, PTX_ERR_UNSUPPORTED, "only SAMPLING_BSDF is supported (grid/MIS modes need the radiosity solver)");
+    if (opts->spp < 0) return fail(c, PTX_ERR_INVALID, "ptx_render: spp < 0");
+    int rng_mode = opts->rng_mode;
+    if (rng_mode != PTX_RNG_XORWOW_COMPAT && rng_mode != PTX_RNG_PHILOX) return fail(c, PTX_ERR_INVALID, "ptx_render: bad rng_mode");
+    int shard_mode = opts->shard_mode, rank = opts->shard_rank, world = opts->shard_world > 0 ? opts->shard_world : 1;
+    if (shard_mode == PTX_SHARD_NONE) { rank = 0; world = 1; }
+    if (rank < 0 || rank >= world) return fail(c, PTX_ERR_INVALID, "ptx_render: bad shard rank/world");
+    if (shard_mode == PTX_SHARD_SAMPLES && rng_mode != PTX_RNG_PHILOX)
+        return fail(c, PTX_ERR_INVALID, "sample-range sharding needs the counter-based RNG (the XORWOW stream is sequential per pixel)");
+    PTX_CUDA(c, cudaSetDevice(c->device));
+
+    const int w = film->w, h = film->h;
+    RenderParams rp{};
+    rp.shade.max_depth = opts->max_depth > 0 ? opts->max_depth : 5;
+    rp.shade.rr_start_depth = opts->rr_start_depth > 0 ? opts->rr_start_depth : 3;
+    rp.shade.rr_cap = opts->rr_cap > 0.f ? opts->rr_cap : 0.95f;
+    rp.seed = film->seed_base;
+    int spp_local = opts->spp;
+    if (!opts->accumulate) film->sample_base = 0;
+    rp.sample_begin = film->sample_base;                   // progressive frames continue the sample index
+    if (shard_mode == PTX_SHARD_SAMPLES) {
+        int lo = (int)((long long)opts->spp * rank / world), hi = (int)((long long)opts->spp * (rank + 1) / world);
+        spp_local = hi - lo;
+        rp.sample_begin += (uint32_t)lo;
+    }
+    rp.spp = spp_local;
+    rp.n_owned = owned_pixel_count(w, h, shard_mode, rank, world);
+    rp.total_paths = (unsigned long long)rp.n_owned * (unsigned long long)spp_local;
+    rp.n_slots = rng_mode == PTX_RNG_XORWOW_COMPAT ? rp.n_owned : (uint32_t)std::min<unsigned long long>(rp.total_paths, kPhiloxPool);
+
+    int rc = ensure_wave_capacity(c, rp.n_slots, rp.n_owned);
+    if (rc != PTX_OK) return rc;
+    int key[5] = {w, h, shard_mode, rank, world};
+    if (memcmp(key, c->slot_key, sizeof key) != 0) {
+        launch_slot_pixels(c->stream, c->ws.slot_pixel, w, h, shard_mode, rank, world, rp.n_owned);
+        memcpy(c->slot_key, key, sizeof key);
+    }
+    if (!opts->accumulate) { rc = ptx_film_clear(film); if (rc != PTX_OK) return rc; }
+
+    CameraView cv = camera_view(*cam, w, h);
+    FilmView fv = film->view();
+    const bool fused = opts->pipeline == 1;
+    const bool count_work = (opts->reserved[0] & 2) != 0;
+    const bool stage_timing = (opts->reserved[0] & 1) != 0 && !fused;
+
+    unsigned long long live0 = (rp.spp > 0) ? std::min<unsigned long long>(rp.n_slots, rng_mode == PTX_RNG_PHILOX ? rp.total_paths : rp.n_slots) : 0ull;
+    unsigned long long* hc = c->h_counters;
+    for (int i = 0; i < CTR_COUNT; i++) hc[i] = 0;
+    hc[CTR_LIVE] = live0; hc[CTR_QLEN] = rp.n_slots; hc[CTR_NEXT_PATH] = rp.n_slots;
+    PTX_CUDA(c, cudaMemcpyAsync(c->ws.counters, hc, sizeof(unsigned long long) * CTR_COUNT, cudaMemcpyHostToDevice, c->stream));
+    PTX_CUDA(c, cudaStreamSynchronize(c->stream));      // hc is reused as the read-back buffer below
+
+    ptx_render_stats st{};
+    PTX_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    launch_raygen(c->stream, rng_mode, c->ws, fv, cv, rp);
+    st.kernel_launches++;
+
+    const int kBatch = 8;
+    if (stage_timing && c->stage_events.size() < (size_t)kBatch * 3) {
+        while (c->stage_events.size() < (size_t)kBatch * 3) { cudaEvent_t e; PTX_CUDA(c, cudaEventCreate(&e)); c->stage_events.push_back(e); }
+    }
+    uint32_t qbound = rp.n_slots;
+    unsigned long long live = live0;
+    int q = 0;
+    // in compat mode no slot can die before it has traced spp segments
+    long long first_check = rng_mode == PTX_RNG_XORWOW_COMPAT ? std::max(1, rp.spp) : 1;
+    while (live > 0) {
+        int iters = (int)std::min<long long>(std::max<long long>(first_check, 1), 4096);
+        if (st.iterations > 0) iters = kBatch;
+        if (stage_timing) iters = std::min(iters, kBatch);
+        for (int i = 0; i < iters; i++) {
+            if (fused) {
+                launch_bounce(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, q, qbound);
+                st.kernel_launches++;
+            } else {
+                if (stage_timing) cudaEventRecord(c->stage_events[3 * i], c->stream);
+                launch_extend(c->stream, c->ws, scene->view, q, qbound, count_work);
+                if (stage_timing) cudaEventRecord(c->stage_events[3 * i + 1], c->stream);
+                launch_shade(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, q, qbound);
+                if (stage_timing) cudaEventRecord(c->stage_events[3 * i + 2], c->stream);
+                st.kernel_launches += 2;
+            }
+            st.iterations++;
+        }
+        PTX_CUDA(c, cudaGetLastError());
+        PTX_CUDA(c, cudaMemcpyAsync(hc, c->ws.counters, sizeof(unsigned long long) * CTR_COUNT, cudaMemcpyDeviceToHost, c->stream));
+        PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (stage_timing)
+            for (int i = 0; i < iters; i++) {
+                float a = 0.f, b = 0.f;
+                cudaEventElapsedTime(&a, c->stage_events[3 * i], c->stage_events[3 * i + 1]);
+                cudaEventElapsedTime(&b, c->stage_events[3 * i + 1], c->stage_events[3 * i + 2]);
+                st.extend_ms += a; st.shade_ms += b;
+            }
+        live = hc[CTR_LIVE];
+        uint32_t qlen = (uint32_t)hc[CTR_QLEN];
+        if (live > 0 && qlen > 8192u && live * 4ull < (unsigned long long)qlen * 3ull) {      // < 75 % of the queue is live: compact
+            launch_compact(c->stream, c->ws, q, qbound, c->d_scratch);
+            st.kernel_launches += 4; st.compactions++;
+            q ^= 1;
+            qbound = (uint32_t)live;        // stream order: nothing dies between the read-back and the compaction
+        }
+    }
+    PTX_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    PTX_CUDA(c, cudaMemcpyAsync(hc, c->ws.counters, sizeof(unsigned long long) * CTR_COUNT, cudaMemcpyDeviceToHost, c->stream));
+    PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+    PTX_CUDA(c, cudaGetLastError());
+    cudaEventElapsedTime(&st.render_ms, c->ev0, c->ev1);
+    st.segments = hc[CTR_SEGMENTS]; st.paths = hc[CTR_PATHS];
+    st.other_ms = st.render_ms - st.extend_ms - st.shade_ms;
+    st.node_visits = hc[CTR_NODE_VISITS]; st.tri_tests = hc[CTR_TRI_TESTS];
+    c->stats = st;
+    if (shard_mode == PTX_SHARD_SAMPLES) film->total_spp += (float)spp_local;   // partial: caller reduces and sets the total
+    else film->total_spp += (float)opts->spp;
+    film->sample_base += (uint32_t)opts->spp;
+    return PTX_OK;
+}
+
+int ptx_render_stats_get(const ptx_ctx* c, ptx_render_stats* out) {
+    if (!c || !out) return fail(nullptr, PTX_ERR_INVALID, "ptx_render_stats_get: NULL argument");
+    *out = c->stats;
+    return PTX_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// queries
+// ---------------------------------------------------------------------------------------------
+int ptx_trace_primary_ids(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, int width, int height, int32_t* prim_id_host,
+                          float* t_host) {
+    if (!c || !scene || !cam || width <= 0 || height <= 0 || !prim_id_host || !t_host) return fail(c, PTX_ERR_INVALID, "ptx_trace_primary_ids: bad argument");
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    size_t n = (size_t)width * height;
+    int32_t* d_ids = nullptr; float* d_t = nullptr;
+    PTX_CUDA(c, cudaMalloc(&d_ids, n * 4));
+    cudaError_t e = cudaMalloc(&d_t, n * 4);
+    if (e != cudaSuccess) { cudaFree(d_ids); return cuda_fail(c, e, "cudaMalloc"); }
+    launch_primary_ids(c->stream, scene->view, camera_view(*cam, width, height), width, height, d_ids, d_t);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(prim_id_host, d_ids, n * 4, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(t_host, d_t, n * 4, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d_ids); cudaFree(d_t);
+    if (e != cudaSuccess) return cuda_fail(c, e, "ptx_trace_primary_ids");
+    return PTX_OK;
+}
+
+int ptx_trace_rays(ptx_ctx* c, const ptx_scene* scene, const float* rays_host, size_t n, float t_min, int32_t* prim_id_host, float* t_host) {
+    if (!c || !scene || (n && (!rays_host || !prim_id_host || !t_host))) return fail(c, PTX_ERR_INVALID, "ptx_trace_rays: bad argument");
+    if (!n) return PTX_OK;
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    float* d_rays = nullptr; int32_t* d_ids = nullptr; float* d_t = nullptr;
+    cudaError_t e = cudaMalloc(&d_rays, n * 24);
+    if (e == cudaSuccess) e = cudaMalloc(&d_ids, n * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&d_t, n * 4);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_rays, rays_host, n * 24, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) { launch_trace_rays(c->stream, scene->view, d_rays, n, t_min, d_ids, d_t); e = cudaGetLastError(); }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(prim_id_host, d_ids, n * 4, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(t_host, d_t, n * 4, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d_rays); cudaFree(d_ids); cudaFree(d_t);
+    if (e != cudaSuccess) return cuda_fail(c, e, "ptx_trace_rays");
+    return PTX_OK;
+}
+
+}  // extern "C"

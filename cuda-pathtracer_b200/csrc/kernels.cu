@@ -1,0 +1,448 @@
+// kernels.cu -- hand-written sm_100a kernels of the wavefront integrator (see kernels.cuh).
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3
+#include "kernels.cuh"
+#include "traverse.h"
+
+namespace ptx {
+
+namespace {
+
+constexpr int kBlock = 256;
+
+__device__ __forceinline__ float4 ld_state(const float4* p) { return *p; }
+__device__ __forceinline__ vec3 v3(float x, float y, float z) { return mk3(x, y, z); }
+
+// one atomicAdd per warp for a per-lane 0/1 contribution
+__device__ __forceinline__ void warp_count_add(unsigned long long* ctr, bool pred) {
+    unsigned m = __ballot_sync(0xFFFFFFFFu, pred);
+    if ((threadIdx.x & 31) == 0 && m) atomicAdd(ctr, (unsigned long long)__popc(m));
+}
+
+// ---------------------------------------------------------------------------------------------
+// rng_init: XORWOW state of pixel p == curand_init(seed_base + p, p, 0)   (integrator.h:274-280)
+// The jump J[b] is applied for every set bit b of p; the matrix rows are read with warp-uniform
+// addresses (broadcast loads), the per-lane state bits select them with masks.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) k_rng_init(FilmView film, unsigned long long seed_base, const uint32_t* __restrict__ jump) {
+    uint32_t p = blockIdx.x * kBlock + threadIdx.x;
+    uint32_t npix = (uint32_t)film.width * (uint32_t)film.height;
+    bool valid = p < npix;
+    Xorwow s = xorwow_seed(seed_base + (unsigned long long)p);
+    uint32_t top = __reduce_max_sync(0xFFFFFFFFu, valid ? p : 0u);   // highest pixel index in the warp
+    for (int b = 0; b < 32 && (top >> b) != 0; b++) {
+        if (__any_sync(0xFFFFFFFFu, valid && ((p >> b) & 1u))) {
+            Xorwow t = s;
+            xorwow_apply(t, jump + (size_t)b * kXorwowJumpWords);
+            if ((p >> b) & 1u) s = t;
+        }
+    }
+    if (valid) {
+        film.rngA[p] = make_uint4(s.v0, s.v1, s.v2, s.v3);
+        film.rngB[p] = make_uint2(s.v4, s.d);
+    }
+}
+
+// slot -> pixel map of the pixels this rank owns (tile sharding deals bands of kBandRows rows)
+__global__ void __launch_bounds__(kBlock) k_slot_pixels(uint32_t* slot_pixel, int w, int h, int shard_mode, int rank, int world,
+                                                        uint32_t n_owned) {
+    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+    if (i >= n_owned) return;
+    if (shard_mode != 1 || world <= 1) { slot_pixel[i] = i; return; }
+    uint32_t band_px = (uint32_t)kBandRows * (uint32_t)w;
+    uint32_t local_band = i / band_px, within = i % band_px;
+    uint32_t band = local_band * (uint32_t)world + (uint32_t)rank;
+    slot_pixel[i] = band * band_px + within;
+}
+
+__device__ __forceinline__ void store_vertex(const WaveState& ws, uint32_t slot, const PathVertex& pv, uint32_t flags) {
+    ws.A[slot] = make_float4(pv.o.x, pv.o.y, pv.o.z, pv.d.x);
+    ws.B[slot] = make_float4(pv.d.y, pv.d.z, __uint_as_float((uint32_t)pv.depth | flags), pv.beta.x);
+    float4 c = ws.C[slot];
+    c.x = pv.beta.y; c.y = pv.beta.z;
+    ws.C[slot] = c;
+}
+
+__device__ __forceinline__ void start_path(const CameraView& cam, uint32_t pixel, float ju, float jv, PathVertex& pv) {
+    int x = (int)(pixel % (uint32_t)cam.width), y = (int)(pixel / (uint32_t)cam.width);
+    float u = ((float)x + ju) / (float)cam.width;            // integrator.h:384-385
+    float v = ((float)y + jv) / (float)cam.height;
+    camera_ray(cam, u, v, pv.o, pv.d);
+    pv.beta = mk3(1.0f, 1.0f, 1.0f);
+    pv.depth = 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// raygen: first path of every slot
+// ---------------------------------------------------------------------------------------------
+template <int RNG>
+__global__ void __launch_bounds__(kBlock) k_raygen(WaveState ws, FilmView film, CameraView cam, RenderParams rp) {
+    uint32_t slot = blockIdx.x * kBlock + threadIdx.x;
+    if (slot >= rp.n_slots) return;
+    ws.queue[0][slot] = slot;
+    PathVertex pv;
+    uint32_t flags = 0;
+    if (RNG == 0) {
+        uint32_t pixel = ws.slot_pixel[slot];
+        uint4 a = film.rngA[pixel]; uint2 b = film.rngB[pixel];
+        XorwowRng rng; rng.st = Xorwow{a.x, a.y, a.z, a.w, b.x, b.y};
+        if (rp.spp > 0) {
+            float ju = rng.next(), jv = rng.next();
+            start_path(cam, pixel, ju, jv, pv);
+            film.rngA[pixel] = make_uint4(rng.st.v0, rng.st.v1, rng.st.v2, rng.st.v3);
+            film.rngB[pixel] = make_uint2(rng.st.v4, rng.st.d);
+        } else { pv.o = pv.d = pv.beta = mk3(0, 0, 0); pv.depth = 0; flags = kDeadFlag; }
+        ws.D[slot] = make_uint2(pixel, 0u);
+    } else {
+        // path index == slot for the first wave; pixel-major so neighbouring lanes take neighbouring pixels
+        unsigned long long path = slot;
+        if (path < rp.total_paths) {
+            uint32_t local = (uint32_t)(path % rp.n_owned), sample = (uint32_t)(path / rp.n_owned) + rp.sample_begin;
+            uint32_t pixel = ws.slot_pixel[local];
+            PhiloxRng rng; rng.seek(((unsigned long long)sample << 32) | pixel, 0u, rp.seed);
+            float ju = rng.next(), jv = rng.next();
+            start_path(cam, pixel, ju, jv, pv);
+            ws.D[slot] = make_uint2(pixel, sample);
+        } else { pv.o = pv.d = pv.beta = mk3(0, 0, 0); pv.depth = 0; flags = kDeadFlag; ws.D[slot] = make_uint2(0u, 0u); }
+    }
+    ws.C[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+    store_vertex(ws, slot, pv, flags);
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// extend: closest hit for the ray of every live slot in the queue
+// ---------------------------------------------------------------------------------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(kBlock) k_extend(WaveState ws, SceneView scene, int q) {
+    uint32_t k = blockIdx.x * kBlock + threadIdx.x;
+    uint32_t qlen = (uint32_t)ws.counters[CTR_QLEN];
+    if (k >= qlen) return;
+    uint32_t slot = ws.queue[q][k];
+    float4 a = ws.A[slot], b = ws.B[slot];
+    if (__float_as_uint(b.z) & kDeadFlag) return;
+    float t;
+    TraceCounters tc = {0u, 0u};
+    uint32_t tri = trace_closest<24, COUNT>(scene, v3(a.x, a.y, a.z), v3(a.w, b.x, b.y), 1e-4f, FLT_MAX, t, &tc);
+    uint32_t prim = kMiss;
+    if (tri != kMiss) prim = __float_as_uint(ldq(scene.tris + (size_t)tri * kTriQuads).w);
+    reinterpret_cast<float2*>(ws.C + slot)[1] = make_float2(t, __uint_as_float(prim));
+    if (COUNT) { atomicAdd(&ws.counters[CTR_NODE_VISITS], (unsigned long long)tc.nodes); atomicAdd(&ws.counters[CTR_TRI_TESTS], (unsigned long long)tc.tris); }
+}
+
+// ---------------------------------------------------------------------------------------------
+// shade (+ Russian roulette + film accumulate + in-place regeneration).  FUSED = true also does the
+// extend step in the same kernel ("bounce" pipeline), so no hit record goes through HBM.
+// ---------------------------------------------------------------------------------------------
+template <int RNG, bool FUSED>
+__global__ void __launch_bounds__(kBlock) k_shade(WaveState ws, SceneView scene, FilmView film, CameraView cam, RenderParams rp, int q) {
+    uint32_t k = blockIdx.x * kBlock + threadIdx.x;
+    uint32_t qlen = (uint32_t)ws.counters[CTR_QLEN];
+    bool live = k < qlen;
+    uint32_t slot = live ? ws.queue[q][k] : 0u;
+    float4 a, b, c;
+    if (live) {
+        b = ws.B[slot];
+        live = !(__float_as_uint(b.z) & kDeadFlag);
+    }
+    bool ended = false, died = false;
+    if (live) {
+        a = ws.A[slot]; c = ws.C[slot];
+        PathVertex pv;
+        pv.o = v3(a.x, a.y, a.z); pv.d = v3(a.w, b.x, b.y);
+        pv.beta = v3(b.w, c.x, c.y);
+        pv.depth = (int)(__float_as_uint(b.z) & 0xFFFFu);
+        uint2 dd = ws.D[slot];
+        uint32_t pixel = dd.x;
+        float t = c.z; uint32_t prim = __float_as_uint(c.w);
+        if (FUSED) {
+            uint32_t tri = trace_closest<24, false>(scene, pv.o, pv.d, 1e-4f, FLT_MAX, t, nullptr);
+            prim = tri == kMiss ? kMiss : __float_as_uint(ldq(scene.tris + (size_t)tri * kTriQuads).w);
+        }
+        vec3 rad = mk3(0.f, 0.f, 0.f);
+        bool cont;
+        XorwowRng xr; PhiloxRng pr;
+        if (RNG == 0) {
+            uint4 ra = film.rngA[pixel]; uint2 rb = film.rngB[pixel];
+            xr.st = Xorwow{ra.x, ra.y, ra.z, ra.w, rb.x, rb.y};
+            cont = shade_bounce(scene, rp.shade, pv, prim, t, xr, rad);
+        } else {
+            pr.seek(((unsigned long long)dd.y << 32) | pixel, 1u + (uint32_t)pv.depth, rp.seed);
+            cont = shade_bounce(scene, rp.shade, pv, prim, t, pr, rad);
+        }
+        if (rad.x != 0.f || rad.y != 0.f || rad.z != 0.f) {
+            if (RNG == 0) {            // the pixel is private to this slot: plain read-modify-write
+                float4 acc = film.accum[pixel];
+                acc.x += rad.x; acc.y += rad.y; acc.z += rad.z;
+                film.accum[pixel] = acc;
+            } else {                   // samples of one pixel may be in flight in several slots
+                float* acc = reinterpret_cast<float*>(film.accum + pixel);
+                atomicAdd(acc + 0, rad.x); atomicAdd(acc + 1, rad.y); atomicAdd(acc + 2, rad.z);
+            }
+        }
+        ended = !cont;
+        uint32_t flags = 0;
+        if (RNG == 0) {
+            if (ended) {
+                uint32_t done = dd.y + 1u;
+                if (done < (uint32_t)rp.spp) {
+                    float ju = xr.next(), jv = xr.next();
+                    start_path(cam, pixel, ju, jv, pv);
+                } else { died = true; flags = kDeadFlag; }
+                ws.D[slot] = make_uint2(pixel, done);
+            }
+            film.rngA[pixel] = make_uint4(xr.st.v0, xr.st.v1, xr.st.v2, xr.st.v3);
+            film.rngB[pixel] = make_uint2(xr.st.v4, xr.st.d);
+        }
+        if (RNG == 1) {
+            // warp-aggregated fetch of the next path indices (one atomic per warp)
+            unsigned need = __ballot_sync(__activemask(), ended);
+            if (ended) {
+                int leader = __ffs(need) - 1;
+                unsigned long long base = 0;
+                if ((int)(threadIdx.x & 31) == leader) base = atomicAdd(&ws.counters[CTR_NEXT_PATH], (unsigned long long)__popc(need));
+                base = __shfl_sync(need, base, leader);
+                unsigned long long path = base + (unsigned long long)__popc(need & ((1u << (threadIdx.x & 31)) - 1u));
+                if (path < rp.total_paths) {
+                    uint32_t local = (uint32_t)(path % rp.n_owned), sample = (uint32_t)(path / rp.n_owned) + rp.sample_begin;
+                    uint32_t npx = ws.slot_pixel[local];
+                    pr.seek(((unsigned long long)sample << 32) | npx, 0u, rp.seed);
+                    float ju = pr.next(), jv = pr.next();
+                    start_path(cam, npx, ju, jv, pv);
+                    ws.D[slot] = make_uint2(npx, sample);
+                } else { died = true; flags = kDeadFlag; }
+            }
+        }
+        ws.A[slot] = make_float4(pv.o.x, pv.o.y, pv.o.z, pv.d.x);
+        ws.B[slot] = make_float4(pv.d.y, pv.d.z, __uint_as_float((uint32_t)pv.depth | flags), pv.beta.x);
+        if (FUSED) ws.C[slot] = make_float4(pv.beta.y, pv.beta.z, 0.f, 0.f);
+        else reinterpret_cast<float2*>(ws.C + slot)[0] = make_float2(pv.beta.y, pv.beta.z);
+    }
+    // statistics: one atomic per warp per counter
+    unsigned m_live = __ballot_sync(0xFFFFFFFFu, live);
+    unsigned m_end = __ballot_sync(0xFFFFFFFFu, ended);
+    unsigned m_died = __ballot_sync(0xFFFFFFFFu, died);
+    if ((threadIdx.x & 31) == 0) {
+        if (m_live) atomicAdd(&ws.counters[CTR_SEGMENTS], (unsigned long long)__popc(m_live));
+        if (m_end) atomicAdd(&ws.counters[CTR_PATHS], (unsigned long long)__popc(m_end));
+        if (m_died) atomicAdd(&ws.counters[CTR_LIVE], (unsigned long long)(-(long long)__popc(m_died)));
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// compact: stable removal of dead slots from the queue.  count -> scan -> scatter -> commit.
+// Each block owns 1024 consecutive queue entries; order is preserved so state accesses stay coalesced.
+// ---------------------------------------------------------------------------------------------
+constexpr int kCompactChunk = 1024;
+
+__device__ __forceinline__ bool slot_live(const WaveState& ws, uint32_t slot) {
+    return !(__float_as_uint(ws.B[slot].z) & kDeadFlag);
+}
+
+__global__ void __launch_bounds__(kBlock) k_compact_count(WaveState ws, int q, uint32_t* block_counts) {
+    uint32_t qlen = (uint32_t)ws.counters[CTR_QLEN];
+    __shared__ uint32_t total;
+    if (threadIdx.x == 0) total = 0;
+    __syncthreads();
+    uint32_t mine = 0;
+    for (int r = 0; r < kCompactChunk / kBlock; r++) {
+        uint32_t k = blockIdx.x * kCompactChunk + r * kBlock + threadIdx.x;
+        if (k < qlen && slot_live(ws, ws.queue[q][k])) mine++;
+    }
+    mine = __reduce_add_sync(0xFFFFFFFFu, mine);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(&total, mine);
+    __syncthreads();
+    if (threadIdx.x == 0) block_counts[blockIdx.x] = total;
+}
+
+// single block: exclusive scan of block_counts[0..nb) in place; block_counts[nb] = total
+__global__ void __launch_bounds__(1024) k_compact_scan(uint32_t* block_counts, uint32_t nb) {
+    __shared__ uint32_t warp_sums[32];
+    __shared__ uint32_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < nb; base += 1024) {
+        uint32_t i = base + threadIdx.x;
+        uint32_t v = i < nb ? block_counts[i] : 0u;
+        uint32_t incl = v;
+        for (int o = 1; o < 32; o <<= 1) { uint32_t n = __shfl_up_sync(0xFFFFFFFFu, incl, o); if ((threadIdx.x & 31) >= o) incl += n; }
+        if ((threadIdx.x & 31) == 31) warp_sums[threadIdx.x >> 5] = incl;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = warp_sums[threadIdx.x], wi = w;
+            for (int o = 1; o < 32; o <<= 1) { uint32_t n = __shfl_up_sync(0xFFFFFFFFu, wi, o); if ((int)threadIdx.x >= o) wi += n; }
+            warp_sums[threadIdx.x] = wi - w;      // exclusive
+        }
+        __syncthreads();
+        uint32_t excl = carry + warp_sums[threadIdx.x >> 5] + incl - v;
+        if (i < nb) block_counts[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) block_counts[nb] = carry;
+}
+
+__global__ void __launch_bounds__(kBlock) k_compact_scatter(WaveState ws, int q, const uint32_t* block_offsets) {
+    uint32_t qlen = (uint32_t)ws.counters[CTR_QLEN];
+    __shared__ uint32_t warp_counts[kBlock / 32];
+    __shared__ uint32_t running;
+    if (threadIdx.x == 0) running = block_offsets[blockIdx.x];
+    __syncthreads();
+    const uint32_t* src = ws.queue[q];
+    uint32_t* dst = ws.queue[q ^ 1];
+    for (int r = 0; r < kCompactChunk / kBlock; r++) {
+        uint32_t k = blockIdx.x * kCompactChunk + r * kBlock + threadIdx.x;
+        uint32_t slot = k < qlen ? src[k] : 0u;
+        bool keep = k < qlen && slot_live(ws, slot);
+        unsigned m = __ballot_sync(0xFFFFFFFFu, keep);
+        int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        if (lane == 0) warp_counts[warp] = __popc(m);
+        __syncthreads();
+        uint32_t before = running;
+        for (int w = 0; w < warp; w++) before += warp_counts[w];
+        if (keep) dst[before + __popc(m & ((1u << lane) - 1u))] = slot;
+        __syncthreads();
+        if (threadIdx.x == 0) { uint32_t t = 0; for (int w = 0; w < kBlock / 32; w++) t += warp_counts[w]; running += t; }
+        __syncthreads();
+    }
+}
+
+__global__ void k_compact_commit(WaveState ws, const uint32_t* block_offsets, uint32_t nb) {
+    ws.counters[CTR_QLEN] = block_offsets[nb];
+}
+
+// ---------------------------------------------------------------------------------------------
+// resolve / film read-back (integrator.h:393-407)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) k_resolve(FilmView film, float inv_spp, uint8_t* rgb8, int flip_y) {
+    uint32_t p = blockIdx.x * kBlock + threadIdx.x;
+    uint32_t npix = (uint32_t)film.width * (uint32_t)film.height;
+    if (p >= npix) return;
+    float4 a = film.accum[p];
+    uint32_t x = p % (uint32_t)film.width, y = p / (uint32_t)film.width;
+    uint32_t o = flip_y ? ((uint32_t)film.height - 1u - y) * (uint32_t)film.width + x : p;
+    rgb8[3 * (size_t)o + 0] = tonemap_channel(a.x * inv_spp);
+    rgb8[3 * (size_t)o + 1] = tonemap_channel(a.y * inv_spp);
+    rgb8[3 * (size_t)o + 2] = tonemap_channel(a.z * inv_spp);
+}
+
+__global__ void __launch_bounds__(kBlock) k_film_scale(FilmView film, float inv_spp, float* linear_rgb) {
+    uint32_t p = blockIdx.x * kBlock + threadIdx.x;
+    uint32_t npix = (uint32_t)film.width * (uint32_t)film.height;
+    if (p >= npix) return;
+    float4 a = film.accum[p];
+    linear_rgb[3 * (size_t)p + 0] = a.x * inv_spp;
+    linear_rgb[3 * (size_t)p + 1] = a.y * inv_spp;
+    linear_rgb[3 * (size_t)p + 2] = a.z * inv_spp;
+}
+
+// ---------------------------------------------------------------------------------------------
+// queries for parity tests
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) k_primary_ids(SceneView scene, CameraView cam, int w, int h, int32_t* prim, float* tout) {
+    uint32_t p = blockIdx.x * kBlock + threadIdx.x;
+    if (p >= (uint32_t)w * (uint32_t)h) return;
+    int x = (int)(p % (uint32_t)w), y = (int)(p / (uint32_t)w);
+    float u = ((float)x + 0.5f) / (float)w, v = ((float)y + 0.5f) / (float)h;
+    vec3 o, d; camera_ray(cam, u, v, o, d);
+    float t;
+    uint32_t tri = trace_closest<24, false>(scene, o, d, 1e-4f, FLT_MAX, t, nullptr);
+    prim[p] = tri == kMiss ? -1 : (int32_t)__float_as_uint(ldq(scene.tris + (size_t)tri * kTriQuads).w);
+    tout[p] = tri == kMiss ? -1.0f : t;
+}
+
+__global__ void __launch_bounds__(kBlock) k_trace_rays(SceneView scene, const float* __restrict__ rays, size_t n, float t_min, int32_t* prim,
+                                                       float* tout) {
+    size_t i = (size_t)blockIdx.x * kBlock + threadIdx.x;
+    if (i >= n) return;
+    vec3 o = v3(rays[6 * i], rays[6 * i + 1], rays[6 * i + 2]);
+    vec3 d = unit(v3(rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5]));   // Ray ctor normalises (core/ray.h:9-12)
+    float t;
+    uint32_t tri = trace_closest<24, false>(scene, o, d, t_min, FLT_MAX, t, nullptr);
+    prim[i] = tri == kMiss ? -1 : (int32_t)__float_as_uint(ldq(scene.tris + (size_t)tri * kTriQuads).w);
+    tout[i] = tri == kMiss ? -1.0f : t;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------------------------
+static inline unsigned blocks_for(size_t n, int per_block) { return (unsigned)((n + (size_t)per_block - 1) / (size_t)per_block); }
+
+uint32_t owned_pixel_count(int w, int h, int shard_mode, int rank, int world) {
+    if (shard_mode != 1 || world <= 1) return (uint32_t)w * (uint32_t)h;
+    uint32_t rows = 0;
+    for (int band = rank; band * kBandRows < h; band += world) {
+        int r0 = band * kBandRows, r1 = r0 + kBandRows;
+        if (r1 > h) r1 = h;
+        rows += (uint32_t)(r1 - r0);
+    }
+    return rows * (uint32_t)w;
+}
+
+void launch_rng_init(cudaStream_t st, const FilmView& film, unsigned long long seed_base, const uint32_t* jump_tables) {
+    size_t npix = (size_t)film.width * film.height;
+    if (!npix) return;
+    k_rng_init<<<blocks_for(npix, kBlock), kBlock, 0, st>>>(film, seed_base, jump_tables);
+}
+void launch_slot_pixels(cudaStream_t st, uint32_t* slot_pixel, int w, int h, int shard_mode, int rank, int world, uint32_t n_owned) {
+    if (!n_owned) return;
+    k_slot_pixels<<<blocks_for(n_owned, kBlock), kBlock, 0, st>>>(slot_pixel, w, h, shard_mode, rank, world, n_owned);
+}
+void launch_raygen(cudaStream_t st, int rng_mode, const WaveState& ws, const FilmView& film, const CameraView& cam, const RenderParams& rp) {
+    if (!rp.n_slots) return;
+    unsigned g = blocks_for(rp.n_slots, kBlock);
+    if (rng_mode == 0) k_raygen<0><<<g, kBlock, 0, st>>>(ws, film, cam, rp);
+    else k_raygen<1><<<g, kBlock, 0, st>>>(ws, film, cam, rp);
+}
+void launch_extend(cudaStream_t st, const WaveState& ws, const SceneView& scene, int q, uint32_t qlen_bound, bool count) {
+    if (!qlen_bound) return;
+    unsigned g = blocks_for(qlen_bound, kBlock);
+    if (count) k_extend<true><<<g, kBlock, 0, st>>>(ws, scene, q);
+    else k_extend<false><<<g, kBlock, 0, st>>>(ws, scene, q);
+}
+void launch_shade(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FilmView& film, const CameraView& cam,
+                  const RenderParams& rp, int q, uint32_t qlen_bound) {
+    if (!qlen_bound) return;
+    unsigned g = blocks_for(qlen_bound, kBlock);
+    if (rng_mode == 0) k_shade<0, false><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp, q);
+    else k_shade<1, false><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp, q);
+}
+void launch_bounce(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FilmView& film, const CameraView& cam,
+                   const RenderParams& rp, int q, uint32_t qlen_bound) {
+    if (!qlen_bound) return;
+    unsigned g = blocks_for(qlen_bound, kBlock);
+    if (rng_mode == 0) k_shade<0, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp, q);
+    else k_shade<1, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp, q);
+}
+void launch_compact(cudaStream_t st, const WaveState& ws, int q, uint32_t qlen_bound, uint32_t* scratch) {
+    if (!qlen_bound) return;
+    unsigned nb = blocks_for(qlen_bound, kCompactChunk);
+    k_compact_count<<<nb, kBlock, 0, st>>>(ws, q, scratch);
+    k_compact_scan<<<1, 1024, 0, st>>>(scratch, nb);
+    k_compact_scatter<<<nb, kBlock, 0, st>>>(ws, q, scratch);
+    k_compact_commit<<<1, 1, 0, st>>>(ws, scratch, nb);
+}
+void launch_resolve(cudaStream_t st, const FilmView& film, float inv_spp, uint8_t* rgb8, int flip_y) {
+    size_t npix = (size_t)film.width * film.height;
+    if (!npix) return;
+    k_resolve<<<blocks_for(npix, kBlock), kBlock, 0, st>>>(film, inv_spp, rgb8, flip_y);
+}
+void launch_film_scale(cudaStream_t st, const FilmView& film, float inv_spp, float* linear_rgb) {
+    size_t npix = (size_t)film.width * film.height;
+    if (!npix) return;
+    k_film_scale<<<blocks_for(npix, kBlock), kBlock, 0, st>>>(film, inv_spp, linear_rgb);
+}
+void launch_primary_ids(cudaStream_t st, const SceneView& scene, const CameraView& cam, int w, int h, int32_t* prim, float* t) {
+    size_t n = (size_t)w * h;
+    if (!n) return;
+    k_primary_ids<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, cam, w, h, prim, t);
+}
+void launch_trace_rays(cudaStream_t st, const SceneView& scene, const float* rays, size_t n, float t_min, int32_t* prim, float* t) {
+    if (!n) return;
+    k_trace_rays<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, rays, n, t_min, prim, t);
+}
+
+}  // namespace ptx

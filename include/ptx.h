@@ -106,7 +106,7 @@ int ptx_scene_from_triangles(ptx_ctx* ctx, const float* v, const float* normals,
                              ptx_scene** out);
 int ptx_scene_build_accel(ptx_scene* scene, const ptx_build_opts* opts);     /* rebuild with other options */
 int ptx_scene_stats_get(const ptx_scene* scene, ptx_scene_stats* out);
-int ptx_scene_get_primitives(const ptx_scene* scene, ptx_primitive* out, int64_t capacity);
+int ptx_scene_get_primitives(const ptx_scene* scene, ptx_primitive* out, int64_t capacity);   /* returns the count (>= 0) */
 void ptx_scene_destroy(ptx_scene* scene);
 
 /* ---- camera: the reference's Sensor (rendering/sensor.h:14-101), same field names ------------ */
@@ -166,6 +166,7 @@ typedef struct {
     uint64_t compactions;
     float render_ms;          /* CUDA-event time of the last ptx_render on the ctx stream */
     float extend_ms, shade_ms, other_ms;   /* filled when opts.reserved[0] & 1 (per-stage timing) */
+    uint64_t node_visits, tri_tests;       /* filled when opts.reserved[0] & 2 (instrumented extend) */
 } ptx_render_stats;
 
 int ptx_render(ptx_ctx* ctx, const ptx_scene* scene, const ptx_camera* cam, ptx_film* film,

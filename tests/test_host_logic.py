@@ -1,0 +1,250 @@
+"""CPU tests (-m "not gpu") of the product's host logic and of its kernel cores compiled for the host.
+
+tests/host_emu.cpp compiles traverse.h / shade.h / rng.h (the __host__ __device__ bodies the CUDA
+kernels call) plus the host builders and loader into tests/_build/libptx_hostemu.so.  These tests
+check them against reference-generated golden vectors and the oracle.  No compute call goes through
+libptx.so here (it needs a GPU); for libptx.so only loading and the exported symbols are checked.
+"""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT, SCENES
+
+
+class CamView(C.Structure):
+    _fields_ = [("origin", C.c_float * 3), ("llc", C.c_float * 3), ("horizontal", C.c_float * 3), ("vertical", C.c_float * 3),
+                ("width", C.c_int), ("height", C.c_int)]
+
+
+@pytest.fixture(scope="module")
+def emu(built):
+    L = C.CDLL(os.path.join(ROOT, "tests", "_build", "libptx_hostemu.so"))
+    L.emu_scene_load.restype = C.c_void_p
+    L.emu_scene_load.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int]
+    L.emu_scene_from_prims.restype = C.c_void_p
+    L.emu_scene_from_prims.argtypes = [C.c_void_p, C.c_int64, C.c_int]
+    L.emu_scene_free.argtypes = [C.c_void_p]
+    L.emu_scene_counts.restype = C.c_int64
+    L.emu_scene_counts.argtypes = [C.c_void_p] * 5
+    L.emu_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.emu_primary_ids.argtypes = [C.c_void_p] * 4
+    L.emu_render.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.emu_parse_obj.restype = C.c_int64
+    L.emu_parse_obj.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_int64]
+    L.emu_xorwow_init.argtypes = [C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]
+    return L
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(os.path.join(GOLDEN, "reference_vectors.npz"))
+
+
+def P(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+def cam_view(pkg, w, h):
+    c = pkg.default_camera(w, h)
+    v = CamView()
+    v.origin[:] = c.origin; v.llc[:] = c.lower_left_corner; v.horizontal[:] = c.horizontal; v.vertical[:] = c.vertical
+    v.width, v.height = w, h
+    return v
+
+
+# ---- C ABI: the library loads and exports everything include/ptx.h declares ----------------------
+def test_abi_exports_every_declared_symbol(pkg):
+    hdr = open(os.path.join(ROOT, "include", "ptx.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(ptx_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 30
+    L = pkg.lib()
+    missing = [s for s in sorted(declared) if not hasattr(L, s)]
+    assert not missing, missing
+    assert set(pkg.EXPORTS) == declared
+    assert b"sm_100a" in L.ptx_version()
+
+
+def test_struct_sizes_match_header(pkg):
+    b = pkg.binding if hasattr(pkg, "binding") else pkg
+    assert C.sizeof(b.Primitive) == 4 + 48 + 36 + 4 == b.PRIM_DTYPE.itemsize
+    assert C.sizeof(b.Camera) == 4 * 3 + 12 * 6 + 8 + 8
+    assert C.sizeof(b.RenderOpts) == 64
+    assert C.sizeof(b.Material) == 32
+
+
+# ---- camera (host maths in libptx.so; no GPU needed) ----------------------------------------------
+@pytest.mark.parametrize("w,h", [(512, 512), (1920, 1080), (37, 91)])
+def test_default_camera_matches_reference_sensor(pkg, oracle, w, h):
+    c = pkg.default_camera(w, h)
+    o = oracle.camera(w, h)
+    for a, b in ((c.origin, o.origin), (c.lower_left_corner, o.llc), (c.horizontal, o.horizontal), (c.vertical, o.vertical)):
+        assert np.array_equal(bits(list(a)), bits(list(b)))
+    assert abs(c.origin[0] + 3.7283e-07) < 1e-10 and abs(c.origin[2] - 8.52936) < 1e-5
+
+
+def test_look_at_camera_matches_oracle(pkg, oracle):
+    eye, at, up = (1.0, 2.0, 7.5), (0.2, 2.4, -1.0), (0.1, 1.0, 0.0)
+    for orbit in (False, True):
+        c = pkg.look_at_camera(eye, at, up, 55.0, 200, 120, orbit=orbit)
+        o = oracle.camera_lookat(eye, at, up, 55.0, 200, 120, orbit=orbit)
+        for a, b in ((c.origin, o.origin), (c.lower_left_corner, o.llc), (c.horizontal, o.horizontal), (c.vertical, o.vertical)):
+            assert np.array_equal(bits(list(a)), bits(list(b)))
+
+
+# ---- loader ---------------------------------------------------------------------------------------
+@pytest.mark.parametrize("tag", ["cbox_cq0", "cbox_quads_cq0", "cbox_quads_cq1"])
+def test_obj_loader_matches_reference_loadOBJ(pkg, gold, tag):
+    name, cq = tag.rsplit("_cq", 1)
+    prims = pkg.parse_scene_file(os.path.join(SCENES, name + ".obj"), convert_quads=bool(int(cq)))
+    ref = gold[tag + "_prims"]
+    assert len(prims) == len(ref)
+    for i, p in enumerate(prims):
+        nv = 3 if p["type"] == 0 else 4
+        assert p["type"] == ref[i, 0:1].view(np.int32)[0]
+        assert np.array_equal(bits(p["v"][:nv].ravel()), bits(ref[i, 1:1 + 3 * nv]))
+        assert np.array_equal(bits(p["normal"]), bits(ref[i, 13:16]))
+        assert np.array_equal(bits(p["bsdf"]), bits(ref[i, 16:19])) and np.array_equal(bits(p["Le"]), bits(ref[i, 19:22]))
+
+
+def test_obj_loader_edge_cases(pkg, tmp_path):
+    (tmp_path / "m.mtl").write_text("newmtl A\nKd 0.1 0.2 0.3\nKe 1 2 3\nnewmtl M\nKd 0.5 0.5 0.5\nKs 0.9 0.8 0.7\nillum 3\n")
+    (tmp_path / "s.obj").write_text(
+        "mtllib m.mtl\nv 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nv 0 0 1\nvn 0 0 2\n"
+        "f 1 2 3\n"                 # triangle, geometric normal, default material (before usemtl)
+        "usemtl A\nf 1//1 2//1 3//1 4//1   # quad with vn and trailing comment\n"
+        "f 1/7 2/7 3/7\n"           # v/vt form
+        "f 1 2\n"                   # 2 vertices: ignored
+        "f 1 2 3 4 5\n"             # 5 vertices: ignored
+        "f 1 2 9\n"                 # out of range: ignored
+        "f -1 -2 -3\n"              # relative indices: not supported by the reference, ignored
+        "usemtl Nope\nf 3 2 1\n"    # unknown material -> default
+        "usemtl M\nf 1 2 5\n"
+        "s off\no thing\n")
+    prims = pkg.parse_scene_file(tmp_path / "s.obj")
+    assert [int(p["type"]) for p in prims] == [0, 1, 0, 0, 0]
+    assert np.allclose(prims[0]["bsdf"], 0.8) and np.allclose(prims[0]["normal"], [0, 0, 1])
+    assert np.allclose(prims[1]["bsdf"], [0.1, 0.2, 0.3]) and np.allclose(prims[1]["Le"], [1, 2, 3]) and np.allclose(prims[1]["normal"], [0, 0, 1])
+    assert np.allclose(prims[3]["bsdf"], 0.8) and np.allclose(prims[3]["normal"], [0, 0, -1])
+    assert prims[4]["material_type"] == 0 and np.allclose(prims[4]["bsdf"], 0.5)      # reference semantics: Ks/illum ignored
+    mir = pkg.parse_scene_file(tmp_path / "s.obj", mirror_from_mtl=True)
+    assert mir[4]["material_type"] == 1 and np.allclose(mir[4]["bsdf"], [0.9, 0.8, 0.7])
+    sub = pkg.parse_scene_file(tmp_path / "s.obj", subdivision=2)
+    assert len(sub) == 5 * 16
+    with pytest.raises(pkg.PtxError):
+        pkg.parse_scene_file(tmp_path / "missing.obj")
+    (tmp_path / "empty.obj").write_text("# nothing\n")
+    with pytest.raises(pkg.PtxError):
+        pkg.parse_scene_file(tmp_path / "empty.obj")
+    with pytest.raises(pkg.PtxError):
+        pkg.parse_scene_file(tmp_path / "scene.xyz")
+
+
+# ---- RNG ------------------------------------------------------------------------------------------
+def test_xorwow_jump_tables_reproduce_curand_init(emu):
+    import json
+    tab = np.zeros(64 * 800, np.uint32)
+    emu.emu_jump_tables(P(tab))
+    for k in json.load(open(os.path.join(GOLDEN, "xorwow_kat.json"))):
+        out = np.zeros(6, np.uint32)
+        emu.emu_xorwow_init(k["seed"], k["subsequence"], P(tab), P(out))
+        assert list(out) == k["v"] + [k["d"]], k
+
+
+def test_philox_known_answers(emu):
+    """Random123 kat_vectors for philox4x32-10."""
+    out = np.zeros(4, np.uint32)
+    for ctr_key, want in (((0, 0, 0, 0, 0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+                          ((0xffffffff,) * 6, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+                          ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344, 0xa4093822, 0x299f31d0), (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))):
+        emu.emu_philox(*[C.c_uint32(x) for x in ctr_key], P(out))
+        assert tuple(int(x) for x in out) == want
+
+
+# ---- BVH8 build + traversal core --------------------------------------------------------------------
+@pytest.mark.parametrize("tag", ["cbox_cq0", "cbox_quads_cq0", "cbox_quads_cq1"])
+@pytest.mark.parametrize("max_leaf", [1, 3])
+def test_bvh8_traversal_primary_ids_match_reference(pkg, emu, gold, tag, max_leaf):
+    name, cq = tag.rsplit("_cq", 1)
+    s = emu.emu_scene_load(os.path.join(SCENES, name + ".obj").encode(), int(cq), 0, max_leaf)
+    for w, h in ((64, 64), (160, 90)):
+        cv = cam_view(pkg, w, h)
+        ids = np.zeros((h, w), np.int32); ts = np.zeros((h, w), np.float32)
+        emu.emu_primary_ids(s, C.byref(cv), P(ids), P(ts))
+        assert np.array_equal(ids, gold[f"{tag}_ids_{w}x{h}"].astype(np.int32))
+        assert np.array_equal(bits(ts), bits(gold[f"{tag}_t_{w}x{h}"]))
+    emu.emu_scene_free(s)
+
+
+@pytest.mark.parametrize("name", ["cbox", "cbox_quads"])
+def test_bvh8_random_rays_match_reference_linear_scan(emu, gold, name):
+    s = emu.emu_scene_load(os.path.join(SCENES, name + ".obj").encode(), 0, 0, 3)
+    rays = np.ascontiguousarray(gold[name + "_rays"])
+    ids = np.zeros(len(rays), np.int32); ts = np.zeros(len(rays), np.float32)
+    emu.emu_trace(s, P(rays), len(rays), C.c_float(1e-4), P(ids), P(ts), None)
+    ref = gold[name + "_rays_lin_ids"].astype(np.int32)
+    diff = ids != ref
+    assert diff.sum() <= 2                      # only exact ties may differ
+    assert np.array_equal(bits(ts[~diff]), bits(gold[name + "_rays_lin_t"][~diff]))
+    emu.emu_scene_free(s)
+
+
+def test_bvh8_on_subdivided_and_random_soup(pkg, emu, oracle):
+    """Deeper trees: subdivided Cornell box (8192 tris) and a random triangle soup, BVH8 vs the oracle's linear scan."""
+    rng = np.random.default_rng(5)
+    prims = pkg.parse_scene_file(os.path.join(SCENES, "cbox.obj"), subdivision=4)
+    assert len(prims) == 32 * 256
+    soup = np.zeros(3000, prims.dtype)
+    c = rng.uniform(-3, 3, (3000, 1, 3)).astype(np.float32)
+    soup["v"][:, :3] = c + rng.normal(scale=0.25, size=(3000, 3, 3)).astype(np.float32)
+    soup["normal"] = [0, 0, 1]; soup["bsdf"] = 0.5
+    for plist in (prims, soup):
+        s = emu.emu_scene_from_prims(P(plist), len(plist), 3)
+        nt, nn, dp, sah = C.c_int64(), C.c_int64(), C.c_int(), C.c_float()
+        assert emu.emu_scene_counts(s, C.byref(nt), C.byref(nn), C.byref(dp), C.byref(sah)) == len(plist)
+        assert nt.value == len(plist) and nn.value >= len(plist) / 24 and dp.value >= 3
+        osc = oracle.scene_from_prims(plist)
+        o = rng.uniform(-2.5, 2.5, (600, 3)); d = rng.normal(size=(600, 3))
+        rays = np.concatenate([o, d], 1).astype(np.float32)
+        ids = np.zeros(600, np.int32); ts = np.zeros(600, np.float32); ctr = np.zeros(2, np.uint64)
+        emu.emu_trace(s, P(rays), 600, C.c_float(1e-4), P(ids), P(ts), P(ctr))
+        oids, ots = oracle.intersect(osc, rays, mode=1)
+        same = ids == oids
+        assert same.mean() > 0.99
+        assert np.array_equal(bits(ts[same]), bits(ots[same]))
+        assert ctr[1] / 600 < 0.05 * len(plist)        # the tree actually culls: far fewer tests than a linear scan
+        emu.emu_scene_free(s); oracle.free(osc)
+
+
+def test_empty_and_tiny_scenes(pkg, emu):
+    one = np.zeros(1, pkg.PRIM_DTYPE)
+    one["v"][0, :3] = [[0, 0, 0], [1, 0, 0], [0, 1, 0]]; one["normal"] = [0, 0, 1]
+    rays = np.array([[0.2, 0.2, 1, 0, 0, -1], [2, 2, 1, 0, 0, -1]], np.float32)
+    for plist, want in ((one, [0, -1]), (one[:0], [-1, -1])):
+        s = emu.emu_scene_from_prims(P(plist) if len(plist) else None, len(plist), 3)
+        ids = np.zeros(2, np.int32); ts = np.zeros(2, np.float32)
+        emu.emu_trace(s, P(rays), 2, C.c_float(1e-4), P(ids), P(ts), None)
+        assert list(ids) == want
+        emu.emu_scene_free(s)
+
+
+# ---- integrator core (shade.h) --------------------------------------------------------------------
+@pytest.mark.parametrize("tag,w,h,spp,depth", [("cbox_cq0", 48, 48, 8, 8), ("cbox_quads_cq0", 64, 36, 4, 16), ("cbox_quads_cq1", 32, 32, 16, 5)])
+def test_integrator_core_bit_exact_vs_reference(pkg, emu, gold, tag, w, h, spp, depth):
+    name, cq = tag.rsplit("_cq", 1)
+    s = emu.emu_scene_load(os.path.join(SCENES, name + ".obj").encode(), int(cq), 0, 3)
+    cv = cam_view(pkg, w, h)
+    lin = np.zeros((h, w, 3), np.float32); rgb = np.zeros((h, w, 3), np.uint8); seg = C.c_uint64()
+    emu.emu_render(s, C.byref(cv), spp, depth, 2023, P(lin), P(rgb), C.byref(seg))
+    key = f"{tag}_{w}x{h}_s{spp}_d{depth}"
+    assert np.array_equal(bits(lin), bits(gold[key + "_linear"]))
+    assert np.array_equal(rgb, gold[key + "_rgb8"])
+    emu.emu_scene_free(s)
