@@ -1,0 +1,280 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the path-tracing hot path (contract: see the task statement).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--rng compat|philox]
+                    [--pipeline fused|wavefront] [--workload c1|c2|c4]
+
+One "step" = one frame of the hot path: ptx_render (raygen/extend/shade/compact) + film resolve.
+N = 1 workload = BASELINE.json configs[1]: scenes/cbox_quads.obj, 1920x1080, 1024 spp, depth 16, reference
+Russian roulette.  N > 1: the same frame, sharded over the ranks (tiles with the compat RNG, sample ranges
+with the counter RNG) with the film combined by one NCCL all-reduce ("scaling": "strong").
+Metric = Mpaths*bounces/s = 1e-6 * path segments (exact device counter) / seconds, whole job.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (scene, width, height, spp, depth)
+    "c1": ("cbox.obj", 512, 512, 64, 8),
+    "c2": ("cbox_quads.obj", 1920, 1080, 1024, 16),
+    "c4": ("cbox_quads.obj", 3840, 2160, 4096, 8),
+}
+METRIC = "Mpaths*bounces/s"
+
+
+def read_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get("hbm_gbs", 6650.0), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.gpu, self.samples, self.reasons, self.max_mhz, self.stop_flag = gpu_index, [], set(), None, False
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self.stop_flag:
+            try:
+                r = subprocess.run(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                   capture_output=True, text=True, timeout=5)
+                f = [x.strip() for x in r.stdout.strip().split(",")]
+                self.samples.append(float(f[0])); self.max_mhz = float(f[1])
+                for n, v in zip(names, f[2:]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def ref_host_run(scene, w, h, spp, depth, frames, threads=0):
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_host")
+    r = subprocess.run([exe, "render", scene, str(w), str(h), str(spp), str(depth), str(frames), "-", "0", str(threads)],
+                       capture_output=True, text=True, check=True)
+    return json.loads(r.stdout.strip().splitlines()[-1])
+
+
+def segments_per_path_estimate(scene, w, h, depth):
+    """Exact segment counts come from the oracle (same streams as the reference): used to convert the
+    reference's ms/frame into the metric, since the reference has no segment counter."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_binding
+    o = oracle_binding.Oracle()
+    s = o.load_obj(scene)
+    sw, sh = max(16, w // 8), max(9, h // 8)
+    _, _, st = o.render(s, sw, sh, 4, depth)
+    o.free(s)
+    return st[0] / st[1]
+
+
+def run_reference(args, scene_path, w, h, spp, depth):
+    """--impl reference: the reference's own CPU build (oracle/_ref/ref_host: its unmodified headers compiled
+    for the host, OpenMP over rows) on a bounded sample of the workload, all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    sample_spp = 2
+    seg_per_path = segments_per_path_estimate(scene_path, w, h, depth)
+    for _ in range(args.warmup):
+        ref_host_run(scene_path, w, h, 1, depth, 1)
+    t_ms = []
+    for _ in range(args.steps):
+        j = ref_host_run(scene_path, w, h, sample_spp, depth, 1)
+        t_ms.append(j["ms_per_frame"])
+        threads = j["threads"]
+    ms = sum(t_ms) / len(t_ms)
+    value = w * h * sample_spp * seg_per_path / (ms * 1e-3) * 1e-6
+    sample = f"{w}x{h}, {sample_spp} of {spp} spp per step, depth {depth}"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload_desc, "sample": sample, "segments_per_path": seg_per_path},
+        "cpu_baseline": {"value": value, "unit": METRIC, "cores": threads, "kind": "reference", "sample": sample, "host_cores": cores},
+        "e2e": {"value": value, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+class DeviceArray:
+    """__cuda_array_interface__ view of a raw device pointer, so torch can wrap the film accumulator."""
+
+    def __init__(self, ptr, nfloats):
+        self.__cuda_array_interface__ = {"shape": (nfloats,), "typestr": "<f4", "data": (ptr, False), "version": 3, "strides": None}
+
+
+def run_ours(args, scene_path, w, h, spp, depth):
+    import __graft_entry__ as ge
+    pkg = ge.load_package()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    rng_mode = pkg.RNG_PHILOX if args.rng == "philox" else pkg.RNG_XORWOW_COMPAT
+    pipeline = pkg.PIPELINE_FUSED if args.pipeline == "fused" else pkg.PIPELINE_WAVEFRONT
+    shard_mode = pkg.SHARD_NONE if world == 1 else (pkg.SHARD_SAMPLES if rng_mode == pkg.RNG_PHILOX else pkg.SHARD_TILES)
+
+    dist = torch = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    ctx = pkg.Context(local_rank)
+    scene = ctx.load_scene(scene_path)              # scene replicated on every GPU (one-time, outside the timed region)
+    cam = pkg.default_camera(w, h)
+    film = ctx.create_film(w, h)
+    film_ptr, film_bytes = film.device_buffer()
+    film_tensor = None
+    if world > 1:
+        film_tensor = torch.as_tensor(DeviceArray(film_ptr, film_bytes // 4), device=torch.device("cuda", local_rank))
+        lib_stream = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", local_rank))
+    import numpy as np
+    rgb_host = np.empty((h, w, 3), np.uint8)
+
+    def barrier():
+        ctx.sync()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    kw = dict(spp=spp, max_depth=depth, rng_mode=rng_mode, pipeline=pipeline, shard_mode=shard_mode, shard_rank=rank, shard_world=world)
+
+    def step(host_output, stage_timing=False):
+        """One frame.  host_output=False: result stays in HBM (device resolve). True: RGB8 image copied to the host."""
+        st = ctx.render(scene, cam, film, stage_timing=stage_timing, **kw)
+        if world > 1:
+            with torch.cuda.stream(lib_stream):
+                dist.all_reduce(film_tensor)          # NCCL film combine over NVLink (sum of disjoint tiles / sample ranges)
+            film.set_sample_count(spp)
+        if host_output:
+            film.rgb8(out=rgb_host)                   # resolve + D2H of w*h*3 bytes, like renderFrame (application.h:211-212)
+        else:
+            film.resolve_device()                     # RGB8 stays in HBM (the film's own device buffer)
+        return st
+
+    for _ in range(args.warmup):
+        step(False)
+    # ---- timed region A: inputs resident in HBM, device events on the launching stream ------------
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    ctx.timer_start()
+    seg = launches = 0
+    for _ in range(args.steps):
+        st = step(False)
+        seg += st["segments"]; launches += st["kernel_launches"] + 1
+    ms_dev = ctx.timer_stop()
+    barrier()
+    # ---- timed region B: end to end through the C ABI with host buffers ---------------------------
+    barrier()
+    t0 = time.perf_counter()
+    seg_e2e = 0
+    for _ in range(args.steps):
+        cam = pkg.default_camera(w, h)                # host camera update + by-value upload, like renderFrame (application.h:161-164)
+        st = step(True)
+        seg_e2e += st["segments"]
+    ctx.sync()
+    ms_e2e = (time.perf_counter() - t0) * 1e3
+    barrier()
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    # ---- dominant-kernel timing (separate, per-launch events; not part of the timed regions) ------
+    st_t = step(False, stage_timing=True)
+
+    seg_all, seg_e2e_all, ms_dev_max, ms_e2e_max = seg, seg_e2e, ms_dev, ms_e2e
+    if world > 1:
+        t = torch.tensor([float(seg), float(seg_e2e)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t)
+        seg_all, seg_e2e_all = t[0].item(), t[1].item()
+        m = torch.tensor([ms_dev, ms_e2e], dtype=torch.float64, device="cuda")
+        dist.all_reduce(m, op=dist.ReduceOp.MAX)
+        ms_dev_max, ms_e2e_max = m[0].item(), m[1].item()
+
+    if rank == 0:
+        peak, peak_src = read_peaks()
+        value = seg_all / (ms_dev_max * 1e-3) * 1e-6
+        e2e_value = seg_e2e_all / (ms_e2e_max * 1e-3) * 1e-6
+        fused = pipeline == pkg.PIPELINE_FUSED
+        # algorithmic bytes per segment of the dominant kernel
+        if fused:
+            bytes_per_seg = 4 + 48 + 8 + 48 + (48 if rng_mode == pkg.RNG_XORWOW_COMPAT else 0)
+            kname, k_ms = "k_shade<rng,FUSED> (bounce: extend+shade)", st_t["shade_ms"]
+        else:
+            bytes_per_seg = 4 + 48 + 8 + 40 + (48 if rng_mode == pkg.RNG_XORWOW_COMPAT else 0)
+            kname, k_ms = "k_shade<rng>", st_t["shade_ms"]
+        achieved = st_t["segments"] * bytes_per_seg / (k_ms * 1e-3) * 1e-9 if k_ms > 0 else None
+        out = {
+            "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_dev_max / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload_desc, "rng": args.rng, "pipeline": args.pipeline,
+                       "sharding": {0: "none", 1: "tiles", 2: "sample ranges"}[shard_mode],
+                       "l2": "no flush: per-step working set (path state + RNG + film, %.0f MB) exceeds the 126 MB L2 and is regenerated every step" % (w * h * 100 / 1e6 / world),
+                       "segments_per_step": seg_all / args.steps},
+            "clocks": sampler.summary(),
+            "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": ctypes.sizeof(pkg.Camera), "d2h_bytes_per_step": w * h * 3,
+                    "ms_per_step": ms_e2e_max / args.steps},
+            "gpu_launches": launches,
+            "roofline": {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
+                         "traffic": None, "peak_source": peak_src, "bytes_per_segment": bytes_per_seg,
+                         "kernel_ms_per_step": k_ms, "kernel_share_of_step": k_ms / st_t["render_ms"] if st_t["render_ms"] else None},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                cb_spp = 2
+                spp_ratio = segments_per_path_estimate(scene_path, w, h, depth)
+                j = ref_host_run(scene_path, w, h, cb_spp, depth, 1)
+                out["cpu_baseline"] = {"value": w * h * cb_spp * spp_ratio / (j["ms_per_frame"] * 1e-3) * 1e-6, "unit": METRIC, "cores": j["threads"],
+                                       "kind": "reference", "sample": f"{w}x{h}, {cb_spp} of {spp} spp, depth {depth}, oracle/_ref/ref_host (reference headers, host build, OpenMP rows)"}
+            except Exception as e:       # noqa: BLE001
+                out["cpu_baseline"] = {"value": None, "error": str(e)[:200]}
+        print(json.dumps(out))
+    film.close(); scene.close(); ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rng", default="compat", choices=["compat", "philox"])
+    ap.add_argument("--pipeline", default="fused", choices=["fused", "wavefront"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--spp", type=int, default=0, help="override spp (reduced runs are NOT the headline)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    scene, w, h, spp, depth = WORKLOADS[args.workload]
+    if args.spp > 0:
+        spp = args.spp
+    args.workload_desc = f"{args.workload}: scenes/{scene} {w}x{h}, {spp} spp, max depth {depth}, reference Russian roulette (depth>2, cap 0.95), SAMPLING_BSDF"
+    scene_path = os.path.join(ROOT, "scenes", scene)
+    if args.impl == "reference":
+        run_reference(args, scene_path, w, h, spp, depth)
+    else:
+        run_ours(args, scene_path, w, h, spp, depth)
+
+
+if __name__ == "__main__":
+    main()

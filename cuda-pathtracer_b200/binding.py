@@ -73,6 +73,7 @@ class RenderStats(C.Structure):
 
 EXPORTS = [
     "ptx_ctx_create", "ptx_ctx_destroy", "ptx_last_error", "ptx_sync", "ptx_ctx_device_info", "ptx_version",
+    "ptx_timer_start", "ptx_timer_stop", "ptx_ctx_stream",
     "ptx_scene_load", "ptx_parse_scene_file", "ptx_free_primitives", "ptx_scene_from_primitives", "ptx_scene_from_triangles",
     "ptx_scene_build_accel", "ptx_scene_stats_get", "ptx_scene_get_primitives", "ptx_scene_destroy",
     "ptx_camera_set", "ptx_camera_update", "ptx_camera_orbit", "ptx_camera_default",
@@ -180,6 +181,19 @@ class Context:
 
     def sync(self):
         _check(lib().ptx_sync(self._h), self._h)
+
+    def timer_start(self):
+        _check(lib().ptx_timer_start(self._h), self._h)
+
+    def timer_stop(self):
+        ms = C.c_float()
+        _check(lib().ptx_timer_stop(self._h, C.byref(ms)), self._h)
+        return ms.value
+
+    def stream(self):
+        p = C.c_void_p()
+        _check(lib().ptx_ctx_stream(self._h, C.byref(p)), self._h)
+        return p.value or 0
 
     def device_info(self):
         sm, ma, mi, mem = C.c_int(), C.c_int(), C.c_int(), C.c_size_t()
@@ -291,6 +305,10 @@ class Film:
 
     def clear(self):
         _check(lib().ptx_film_clear(self._h), self.ctx._h)
+
+    def resolve_device(self, dev_ptr=None, flip_y=False):
+        """Resolve into a DEVICE buffer (w*h*3 bytes): caller-owned, or the film's own when dev_ptr is None."""
+        _check(lib().ptx_film_resolve_rgb8(self._h, C.c_void_p(dev_ptr) if dev_ptr else None, 1, int(flip_y)), self.ctx._h)
 
     def rgb8(self, flip_y=False, out=None):
         img = out if out is not None else np.empty((self.height, self.width, 3), np.uint8)

@@ -37,7 +37,7 @@ struct ptx_ctx {
     uint32_t* d_scratch = nullptr; size_t scratch_words = 0;
     unsigned long long* h_counters = nullptr;   // pinned
     int slot_key[5] = {-1, -1, -1, -1, -1};     // (w, h, shard_mode, rank, world) the slot map was built for
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, tev0 = nullptr, tev1 = nullptr;
     std::vector<cudaEvent_t> stage_events;
     ptx_render_stats stats{};
 };
@@ -129,6 +129,7 @@ void ptx_ctx_destroy(ptx_ctx* c) {
     cudaFreeHost(c->h_counters);
     for (auto ev : c->stage_events) cudaEventDestroy(ev);
     if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->tev0) { cudaEventDestroy(c->tev0); cudaEventDestroy(c->tev1); }
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -138,6 +139,29 @@ int ptx_sync(ptx_ctx* c) {
     if (!c) return fail(nullptr, PTX_ERR_INVALID, "ptx_sync: ctx is NULL");
     PTX_CUDA(c, cudaSetDevice(c->device));
     PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return PTX_OK;
+}
+
+int ptx_timer_start(ptx_ctx* c) {
+    if (!c) return fail(nullptr, PTX_ERR_INVALID, "ptx_timer_start: ctx is NULL");
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    if (!c->tev0) { PTX_CUDA(c, cudaEventCreate(&c->tev0)); PTX_CUDA(c, cudaEventCreate(&c->tev1)); }
+    PTX_CUDA(c, cudaEventRecord(c->tev0, c->stream));
+    return PTX_OK;
+}
+
+int ptx_timer_stop(ptx_ctx* c, float* ms) {
+    if (!c || !ms || !c->tev0) return fail(c, PTX_ERR_INVALID, "ptx_timer_stop: timer not started");
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    PTX_CUDA(c, cudaEventRecord(c->tev1, c->stream));
+    PTX_CUDA(c, cudaEventSynchronize(c->tev1));
+    PTX_CUDA(c, cudaEventElapsedTime(ms, c->tev0, c->tev1));
+    return PTX_OK;
+}
+
+int ptx_ctx_stream(const ptx_ctx* c, void** stream) {
+    if (!c || !stream) return fail(nullptr, PTX_ERR_INVALID, "ptx_ctx_stream: NULL argument");
+    *stream = (void*)c->stream;
     return PTX_OK;
 }
 
@@ -395,7 +419,8 @@ int ptx_film_clear(ptx_film* f) {
 }
 
 int ptx_film_resolve_rgb8(ptx_film* f, uint8_t* dst, int dst_is_device, int flip_y) {
-    if (!f || !dst) return fail(nullptr, PTX_ERR_INVALID, "ptx_film_resolve_rgb8: NULL argument");
+    if (!f || (!dst && !dst_is_device)) return fail(nullptr, PTX_ERR_INVALID, "ptx_film_resolve_rgb8: NULL argument");
+    if (!dst) dst = f->d_rgb8;                                         // device-resident result in the film's own buffer
     ptx_ctx* c = f->ctx;
     PTX_CUDA(c, cudaSetDevice(c->device));
     float inv = f->total_spp > 0.f ? 1.0f / f->total_spp : 0.f;      // `color /= float(spp)`: k = 1/spp, multiply
@@ -564,7 +589,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     FilmView fv = film->view();
     const bool fused = opts->pipeline == 1;
     const bool count_work = (opts->reserved[0] & 2) != 0;
-    const bool stage_timing = (opts->reserved[0] & 1) != 0 && !fused;
+    const bool stage_timing = (opts->reserved[0] & 1) != 0;
 
     unsigned long long live0 = (rp.spp > 0) ? std::min<unsigned long long>(rp.n_slots, rng_mode == PTX_RNG_PHILOX ? rp.total_paths : rp.n_slots) : 0ull;
     unsigned long long* hc = c->h_counters;
@@ -593,7 +618,9 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
         if (stage_timing) iters = std::min(iters, kBatch);
         for (int i = 0; i < iters; i++) {
             if (fused) {
+                if (stage_timing) cudaEventRecord(c->stage_events[3 * i + 1], c->stream);
                 launch_bounce(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, q, qbound);
+                if (stage_timing) cudaEventRecord(c->stage_events[3 * i + 2], c->stream);
                 st.kernel_launches++;
             } else {
                 if (stage_timing) cudaEventRecord(c->stage_events[3 * i], c->stream);
@@ -611,7 +638,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
         if (stage_timing)
             for (int i = 0; i < iters; i++) {
                 float a = 0.f, b = 0.f;
-                cudaEventElapsedTime(&a, c->stage_events[3 * i], c->stage_events[3 * i + 1]);
+                if (!fused) cudaEventElapsedTime(&a, c->stage_events[3 * i], c->stage_events[3 * i + 1]);
                 cudaEventElapsedTime(&b, c->stage_events[3 * i + 1], c->stage_events[3 * i + 2]);
                 st.extend_ms += a; st.shade_ms += b;
             }

@@ -42,6 +42,10 @@ const char* ptx_last_error(const ptx_ctx* ctx);           /* ctx may be NULL: la
 int ptx_sync(ptx_ctx* ctx);                                /* cudaDeviceSynchronize, application.h:199 */
 int ptx_ctx_device_info(const ptx_ctx* ctx, int* sm_count, int* cc_major, int* cc_minor, size_t* total_mem);
 const char* ptx_version(void);
+/* CUDA-event stopwatch on the ctx stream (what bench.py times steps with) and the raw cudaStream_t */
+int ptx_timer_start(ptx_ctx* ctx);
+int ptx_timer_stop(ptx_ctx* ctx, float* ms);               /* records, synchronises, returns elapsed ms */
+int ptx_ctx_stream(const ptx_ctx* ctx, void** stream);
 
 /* ---- scene --------------------------------------------------------------------------------- */
 /* One reference `Primitive` minus its radiosity payload (rendering/primitive.h:21-29,
@@ -130,7 +134,8 @@ int ptx_camera_default(ptx_camera* cam, int width, int height);
 int ptx_film_create(ptx_ctx* ctx, int width, int height, ptx_film** out);   /* also runs render_init */
 int ptx_film_reset(ptx_film* film, uint64_t seed_base);                     /* re-seed (reference: 2023) + clear */
 int ptx_film_clear(ptx_film* film);                                         /* clear accumulation only */
-/* Reinhard + gamma 1/2.2 + 255.99 quantisation of integrator.h:393-407; row 0 = bottom unless flip_y */
+/* Reinhard + gamma 1/2.2 + 255.99 quantisation of integrator.h:393-407; row 0 = bottom unless flip_y.
+ * dst_is_device with dst == NULL resolves into the film's own device buffer (result stays in HBM). */
 int ptx_film_resolve_rgb8(ptx_film* film, uint8_t* dst, int dst_is_device, int flip_y);
 int ptx_film_read_linear(ptx_film* film, float* rgb_host);                  /* w*h*3 pre-tonemap means */
 int ptx_film_write(ptx_film* film, const char* path);                        /* .ppm (RGB8, top row first) or .pfm */
