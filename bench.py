@@ -128,7 +128,7 @@ def run_ours(args, scene_path, w, h, spp, depth):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     rng_mode = pkg.RNG_PHILOX if args.rng == "philox" else pkg.RNG_XORWOW_COMPAT
-    pipeline = pkg.PIPELINE_FUSED if args.pipeline == "fused" else pkg.PIPELINE_WAVEFRONT
+    pipeline = {"fused": pkg.PIPELINE_FUSED, "wavefront": pkg.PIPELINE_WAVEFRONT, "loop": pkg.PIPELINE_LOOP}[args.pipeline]
     shard_mode = pkg.SHARD_NONE if world == 1 else (pkg.SHARD_SAMPLES if rng_mode == pkg.RNG_PHILOX else pkg.SHARD_TILES)
 
     dist = torch = None
@@ -215,7 +215,14 @@ def run_ours(args, scene_path, w, h, spp, depth):
         e2e_value = seg_e2e_all / (ms_e2e_max * 1e-3) * 1e-6
         fused = pipeline == pkg.PIPELINE_FUSED
         # algorithmic bytes per segment of the dominant kernel
-        if fused:
+        loop = pipeline == pkg.PIPELINE_LOOP
+        bytes_per_slot_launch = None
+        if loop:
+            # per live slot per launch: queue 4 + read A,B,C,E 64 + D 8 + write A,B,C,E 64 + D 8, compat adds RNG 24+24 and pixel sum 16+16
+            bytes_per_slot_launch = 148 + (80 if rng_mode == pkg.RNG_XORWOW_COMPAT else 0)
+            bytes_per_seg = bytes_per_slot_launch * st_t["slot_launches"] / max(st_t["segments"], 1)
+            kname, k_ms = "k_path_loop<rng> (extend+shade+regenerate, state in registers)", st_t["shade_ms"]
+        elif fused:
             bytes_per_seg = 4 + 48 + 8 + 48 + (48 if rng_mode == pkg.RNG_XORWOW_COMPAT else 0)
             kname, k_ms = "k_shade<rng,FUSED> (bounce: extend+shade)", st_t["shade_ms"]
         else:
@@ -260,7 +267,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rng", default="compat", choices=["compat", "philox"])
-    ap.add_argument("--pipeline", default="fused", choices=["fused", "wavefront"])
+    ap.add_argument("--pipeline", default="loop", choices=["loop", "fused", "wavefront"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override spp (reduced runs are NOT the headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")

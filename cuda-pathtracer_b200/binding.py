@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(HERE, "libptx.so")
 
 RNG_XORWOW_COMPAT, RNG_PHILOX = 0, 1
 SHARD_NONE, SHARD_TILES, SHARD_SAMPLES = 0, 1, 2
-PIPELINE_WAVEFRONT, PIPELINE_FUSED = 0, 1
+PIPELINE_WAVEFRONT, PIPELINE_FUSED, PIPELINE_LOOP = 0, 1, 2
 
 
 class PtxError(RuntimeError):
@@ -68,7 +68,7 @@ class RenderOpts(C.Structure):
 class RenderStats(C.Structure):
     _fields_ = [("segments", C.c_uint64), ("paths", C.c_uint64), ("iterations", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("compactions", C.c_uint64), ("render_ms", C.c_float), ("extend_ms", C.c_float), ("shade_ms", C.c_float),
-                ("other_ms", C.c_float), ("node_visits", C.c_uint64), ("tri_tests", C.c_uint64)]
+                ("other_ms", C.c_float), ("node_visits", C.c_uint64), ("tri_tests", C.c_uint64), ("slot_launches", C.c_uint64)]
 
 
 EXPORTS = [
@@ -235,12 +235,13 @@ class Context:
 
     # -- rendering ----------------------------------------------------------------------------
     def render(self, scene, camera, film, spp, max_depth=5, rng_mode=RNG_XORWOW_COMPAT, accumulate=False, shard_mode=SHARD_NONE,
-               shard_rank=0, shard_world=1, pipeline=PIPELINE_WAVEFRONT, stage_timing=False, count_work=False, sampling_mode=0):
+               shard_rank=0, shard_world=1, pipeline=PIPELINE_WAVEFRONT, stage_timing=False, count_work=False, sampling_mode=0, loop_iters=0):
         o = RenderOpts()
         o.spp, o.max_depth, o.rng_mode, o.sampling_mode = int(spp), int(max_depth), int(rng_mode), int(sampling_mode)
         o.accumulate, o.shard_mode, o.shard_rank, o.shard_world = int(accumulate), int(shard_mode), int(shard_rank), int(shard_world)
         o.pipeline = int(pipeline)
         o.reserved[0] = (1 if stage_timing else 0) | (2 if count_work else 0)
+        o.reserved[1] = int(loop_iters)
         _check(lib().ptx_render(self._h, scene._h, C.byref(camera), film._h, C.byref(o)), self._h)
         return self.render_stats()
 

@@ -123,7 +123,7 @@ void ptx_ctx_destroy(ptx_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    cudaFree(c->ws.A); cudaFree(c->ws.B); cudaFree(c->ws.C); cudaFree(c->ws.D);
+    cudaFree(c->ws.A); cudaFree(c->ws.B); cudaFree(c->ws.C); cudaFree(c->ws.D); cudaFree(c->ws.E);
     cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]); cudaFree(c->ws.slot_pixel); cudaFree(c->ws.counters);
     cudaFree(c->d_scratch); cudaFree(c->d_jump);
     cudaFreeHost(c->h_counters);
@@ -515,14 +515,15 @@ namespace {
 int ensure_wave_capacity(ptx_ctx* c, uint32_t slots, uint32_t owned) {
     uint32_t need = std::max(slots, owned);
     if (need > c->ws.capacity) {
-        cudaFree(c->ws.A); cudaFree(c->ws.B); cudaFree(c->ws.C); cudaFree(c->ws.D);
+        cudaFree(c->ws.A); cudaFree(c->ws.B); cudaFree(c->ws.C); cudaFree(c->ws.D); cudaFree(c->ws.E);
         cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]); cudaFree(c->ws.slot_pixel);
-        c->ws.A = c->ws.B = c->ws.C = nullptr; c->ws.D = nullptr; c->ws.queue[0] = c->ws.queue[1] = c->ws.slot_pixel = nullptr;
+        c->ws.A = c->ws.B = c->ws.C = c->ws.E = nullptr; c->ws.D = nullptr; c->ws.queue[0] = c->ws.queue[1] = c->ws.slot_pixel = nullptr;
         c->ws.capacity = 0; c->slot_key[0] = -1;
         size_t n = need;
         PTX_CUDA(c, cudaMalloc(&c->ws.A, n * sizeof(float4)));
         PTX_CUDA(c, cudaMalloc(&c->ws.B, n * sizeof(float4)));
         PTX_CUDA(c, cudaMalloc(&c->ws.C, n * sizeof(float4)));
+        PTX_CUDA(c, cudaMalloc(&c->ws.E, n * sizeof(float4)));
         PTX_CUDA(c, cudaMalloc(&c->ws.D, n * sizeof(uint2)));
         PTX_CUDA(c, cudaMalloc(&c->ws.queue[0], n * sizeof(uint32_t)));
         PTX_CUDA(c, cudaMalloc(&c->ws.queue[1], n * sizeof(uint32_t)));
@@ -588,6 +589,10 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     CameraView cv = camera_view(*cam, w, h);
     FilmView fv = film->view();
     const bool fused = opts->pipeline == 1;
+    const bool path_loop = opts->pipeline == 2;
+    // bounces per path-loop launch: a compat-mode slot lives for >= spp segments, so long launches waste
+    // little on lanes that die early; reserved[1] overrides (tuning / tests)
+    int loop_iters = opts->reserved[1] > 0 ? opts->reserved[1] : 2 * std::min(std::max(rp.spp, 16), 256);
     const bool count_work = (opts->reserved[0] & 2) != 0;
     const bool stage_timing = (opts->reserved[0] & 1) != 0;
 
@@ -616,7 +621,14 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
         int iters = (int)std::min<long long>(std::max<long long>(first_check, 1), 4096);
         if (st.iterations > 0) iters = kBatch;
         if (stage_timing) iters = std::min(iters, kBatch);
-        for (int i = 0; i < iters; i++) {
+        if (path_loop) {
+            iters = loop_iters;
+            if (stage_timing) cudaEventRecord(c->stage_events[1], c->stream);
+            launch_path_loop(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, q, qbound, iters);
+            if (stage_timing) cudaEventRecord(c->stage_events[2], c->stream);
+            st.kernel_launches++; st.iterations += (uint64_t)iters;
+        }
+        for (int i = 0; i < iters && !path_loop; i++) {
             if (fused) {
                 if (stage_timing) cudaEventRecord(c->stage_events[3 * i + 1], c->stream);
                 launch_bounce(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, q, qbound);
@@ -636,9 +648,9 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
         PTX_CUDA(c, cudaMemcpyAsync(hc, c->ws.counters, sizeof(unsigned long long) * CTR_COUNT, cudaMemcpyDeviceToHost, c->stream));
         PTX_CUDA(c, cudaStreamSynchronize(c->stream));
         if (stage_timing)
-            for (int i = 0; i < iters; i++) {
+            for (int i = 0; i < (path_loop ? 1 : iters); i++) {
                 float a = 0.f, b = 0.f;
-                if (!fused) cudaEventElapsedTime(&a, c->stage_events[3 * i], c->stage_events[3 * i + 1]);
+                if (!fused && !path_loop) cudaEventElapsedTime(&a, c->stage_events[3 * i], c->stage_events[3 * i + 1]);
                 cudaEventElapsedTime(&b, c->stage_events[3 * i + 1], c->stage_events[3 * i + 2]);
                 st.extend_ms += a; st.shade_ms += b;
             }
@@ -658,7 +670,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     cudaEventElapsedTime(&st.render_ms, c->ev0, c->ev1);
     st.segments = hc[CTR_SEGMENTS]; st.paths = hc[CTR_PATHS];
     st.other_ms = st.render_ms - st.extend_ms - st.shade_ms;
-    st.node_visits = hc[CTR_NODE_VISITS]; st.tri_tests = hc[CTR_TRI_TESTS];
+    st.node_visits = hc[CTR_NODE_VISITS]; st.tri_tests = hc[CTR_TRI_TESTS]; st.slot_launches = hc[CTR_SLOT_LAUNCHES];
     c->stats = st;
     if (shard_mode == PTX_SHARD_SAMPLES) film->total_spp += (float)spp_local;   // partial: caller reduces and sets the total
     else film->total_spp += (float)opts->spp;

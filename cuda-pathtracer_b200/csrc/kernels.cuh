@@ -28,6 +28,7 @@ struct WaveState {
     float4* A;
     float4* B;
     float4* C;
+    float4* E;                // path-loop pipeline: { L.r, L.g, L.b, - } radiance of the path in flight
     uint2* D;                 // philox mode: { pixel, sample index }; compat mode: { pixel, samples done }
     uint32_t* queue[2];       // live slot indices (ping-pong for compaction)
     uint32_t* slot_pixel;     // slot -> pixel for the pixels this rank owns
@@ -37,7 +38,7 @@ struct WaveState {
 };
 
 // indices into WaveState::counters
-enum { CTR_SEGMENTS = 0, CTR_PATHS = 1, CTR_LIVE = 2, CTR_QLEN = 3, CTR_NEXT_PATH = 4, CTR_NODE_VISITS = 5, CTR_TRI_TESTS = 6, CTR_COUNT = 8 };
+enum { CTR_SEGMENTS = 0, CTR_PATHS = 1, CTR_LIVE = 2, CTR_QLEN = 3, CTR_NEXT_PATH = 4, CTR_NODE_VISITS = 5, CTR_TRI_TESTS = 6, CTR_SLOT_LAUNCHES = 7, CTR_COUNT = 8 };
 
 struct FilmView {
     float4* accum;            // per pixel: sum r, g, b, (unused)
@@ -64,6 +65,10 @@ void launch_shade(cudaStream_t st, int rng_mode, const WaveState& ws, const Scen
                   const CameraView& cam, const RenderParams& rp, int q, uint32_t qlen_bound);
 void launch_bounce(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FilmView& film,
                    const CameraView& cam, const RenderParams& rp, int q, uint32_t qlen_bound);
+// path-loop pipeline: every live slot runs up to `iters` bounces (extend + shade + regeneration) with its
+// state in registers; state goes through HBM once per launch instead of once per bounce
+void launch_path_loop(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FilmView& film,
+                      const CameraView& cam, const RenderParams& rp, int q, uint32_t qlen_bound, int iters);
 // compacts queue[q] -> queue[q^1]; scratch holds per-block counts (>= ceil(qlen_bound/1024)+1 words)
 void launch_compact(cudaStream_t st, const WaveState& ws, int q, uint32_t qlen_bound, uint32_t* scratch);
 void launch_resolve(cudaStream_t st, const FilmView& film, float inv_spp, uint8_t* rgb8, int flip_y);

@@ -28,6 +28,15 @@ PTX_HD uint32_t popc32(uint32_t x) {
 #endif
 }
 PTX_HD uint32_t byte_of(uint32_t w, int i) { return (w >> (8 * i)) & 0xFFu; }
+// byte i of w as a float.  Device: one PRMT builds 0x4B0000bb = 2^23 + b, one FADD removes 2^23 (exact),
+// which keeps the conversion off the quarter-rate XU pipe that I2F.U8 runs on (ncu r1a: XU 60-67 % busy).
+PTX_HD float byte_to_float(uint32_t w, int i) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7440u + (uint32_t)i)) - 8388608.0f;
+#else
+    return (float)byte_of(w, i);
+#endif
+}
 // per byte: 0x80 -> 0xFF, 0x00 -> 0x00
 PTX_HD uint32_t sign_extend_s8x4(uint32_t x) { return ((x >> 7) & 0x01010101u) * 0xFFu; }
 
@@ -53,29 +62,39 @@ PTX_HD bool intersect_tri(vec3 v0, vec3 e1, vec3 e2, vec3 o, vec3 d, float t_min
     return false;
 }
 
-// Closest hit along (o, d) in [t_min, t_max).  Returns the triangle slot (index into tris) or kMiss;
-// t_hit receives the distance.  STACK entries of 8 bytes live in registers/local memory.
-template <int STACK, bool COUNT>
-PTX_HD uint32_t trace_closest(const SceneView& s, vec3 o, vec3 d, float t_min, float t_max, float& t_hit,
-                              TraceCounters* ctr) {
+// Resumable closest-hit traversal.  One step() = visit ONE wide node (the nearest pending child of the
+// current node group), test the triangles of the leaves it hit, then fetch the next node group from
+// the stack.  Kernels that keep a path per lane call step() once per loop iteration and shade as soon
+// as a lane's traversal finishes, so a lane whose ray needed one node visit does not idle while its
+// neighbours visit three (k_path_loop).  trace_closest() below just runs step() to completion.
+// STACK entries of 8 bytes live in registers/local memory.
+template <int STACK>
+struct Traversal {
     uint32_t stack_x[STACK], stack_y[STACK];
-    int sp = 0;
-    float closest = t_max;
-    uint32_t best = kMiss;
+    int sp;
+    float closest;
+    uint32_t best;                 // triangle slot (index into tris) of the closest accepted hit, or kMiss
+    uint32_t ng_x, ng_y;           // node group: base index, (hit bits 31..24 | imask 7..0)
+    float idx, idy, idz;           // 1/d with zero components replaced by +-2^-80
 
-    const float ooeps = 8.271806e-25f;   // 2^-80: keeps 1/d finite for axis-parallel rays
-    float idx = 1.0f / (fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
-    float idy = 1.0f / (fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
-    float idz = 1.0f / (fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
-    // octant: bit set where the direction is negative; slot priority = slot ^ octinv
-    uint32_t oct = (d.x < 0.0f ? 4u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 1u : 0u);
-    uint32_t octinv = 7u - oct;
-    uint32_t octinv4 = octinv * 0x01010101u;
+    PTX_HD void begin(vec3 d, float t_max) {
+        sp = 0; closest = t_max; best = kMiss;
+        const float ooeps = 8.271806e-25f;   // 2^-80: keeps 1/d finite for axis-parallel rays
+        idx = 1.0f / (fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
+        idy = 1.0f / (fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
+        idz = 1.0f / (fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
+        ng_x = 0; ng_y = 0x80000000u;        // the root as a one-child group
+    }
 
-    uint32_t ng_x = 0, ng_y = 0x80000000u;   // node group: base index, (hit bits 31..24 | imask 7..0)
-    uint32_t tg_x = 0, tg_y = 0;             // triangle group: base index, hit bits 23..0
+    // returns true when the traversal is complete (closest / best are final)
+    template <bool COUNT>
+    PTX_HD bool step(const SceneView& s, vec3 o, vec3 d, float t_min, TraceCounters* ctr) {
+        // octant: bit set where the direction is negative; slot priority = slot ^ octinv
+        uint32_t oct = (d.x < 0.0f ? 4u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 1u : 0u);
+        uint32_t octinv = 7u - oct;
+        uint32_t octinv4 = octinv * 0x01010101u;
+        uint32_t tg_x = 0, tg_y = 0;         // triangle group: base index, hit bits 23..0
 
-    for (;;) {
         if (ng_y > 0x00FFFFFFu) {
             uint32_t imask = ng_y & 0xFFu;
             uint32_t bit = hi_bit(ng_y);
@@ -99,6 +118,7 @@ PTX_HD uint32_t trace_closest(const SceneView& s, vec3 o, vec3 d, float t_min, f
 #endif
             for (int half = 0; half < 2; half++) {
                 uint32_t meta4 = half ? n1.w : n1.z;
+                if (meta4 == 0u) continue;                 // four empty slots (small nodes fill the low slots first)
                 uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
                 uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
                 uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
@@ -112,12 +132,12 @@ PTX_HD uint32_t trace_closest(const SceneView& s, vec3 o, vec3 d, float t_min, f
 #pragma unroll
 #endif
                 for (int j = 0; j < 4; j++) {
-                    float tminx = (float)byte_of(nearx, j) * sx + ox;
-                    float tminy = (float)byte_of(neary, j) * sy + oy;
-                    float tminz = (float)byte_of(nearz, j) * sz + oz;
-                    float tmaxx = (float)byte_of(farx, j) * sx + ox;
-                    float tmaxy = (float)byte_of(fary, j) * sy + oy;
-                    float tmaxz = (float)byte_of(farz, j) * sz + oz;
+                    float tminx = byte_to_float(nearx, j) * sx + ox;
+                    float tminy = byte_to_float(neary, j) * sy + oy;
+                    float tminz = byte_to_float(nearz, j) * sz + oz;
+                    float tmaxx = byte_to_float(farx, j) * sx + ox;
+                    float tmaxy = byte_to_float(fary, j) * sy + oy;
+                    float tmaxz = byte_to_float(farz, j) * sz + oz;
                     float cmin = fmaxf(fmaxf(tminx, tminy), fmaxf(tminz, t_min));
                     float cmax = fminf(fminf(tmaxx, tmaxy), fminf(tmaxz, closest));
                     if (cmin <= cmax) hitmask |= byte_of(child_bits4, j) << byte_of(bit_index4, j);
@@ -126,7 +146,7 @@ PTX_HD uint32_t trace_closest(const SceneView& s, vec3 o, vec3 d, float t_min, f
             ng_y = (hitmask & 0xFF000000u) | (n0.w >> 24);
             tg_y = hitmask & 0x00FFFFFFu;
         } else {
-            tg_x = ng_x; tg_y = ng_y;
+            tg_x = ng_x; tg_y = ng_y;        // a postponed triangle group popped from the stack
             ng_x = 0; ng_y = 0;
         }
 
@@ -141,13 +161,24 @@ PTX_HD uint32_t trace_closest(const SceneView& s, vec3 o, vec3 d, float t_min, f
         }
 
         if (ng_y <= 0x00FFFFFFu) {
-            if (sp == 0) break;
+            if (sp == 0) return true;
             sp--;
             ng_x = stack_x[sp]; ng_y = stack_y[sp];
         }
+        return false;
     }
-    t_hit = closest;
-    return best;
+};
+
+// Closest hit along (o, d) in [t_min, t_max).  Returns the triangle slot (index into tris) or kMiss;
+// t_hit receives the distance.
+template <int STACK, bool COUNT>
+PTX_HD uint32_t trace_closest(const SceneView& s, vec3 o, vec3 d, float t_min, float t_max, float& t_hit,
+                              TraceCounters* ctr) {
+    Traversal<STACK> tr;
+    tr.begin(d, t_max);
+    while (!tr.template step<COUNT>(s, o, d, t_min, ctr)) {}
+    t_hit = tr.closest;
+    return tr.best;
 }
 
 }  // namespace ptx

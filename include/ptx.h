@@ -159,7 +159,8 @@ typedef struct {
     int32_t shard_rank, shard_world;
     int32_t rr_start_depth;   /* 0 => 3  (depth > 2, integrator.h:207) */
     float rr_cap;             /* 0 => 0.95 */
-    int32_t pipeline;         /* 0 = wavefront (raygen/extend/shade/compact); 1 = fused bounce kernel */
+    int32_t pipeline;         /* 0 = wavefront (raygen/extend/shade/compact); 1 = fused bounce kernel (one launch per bounce);
+                                 2 = path loop (state in registers for reserved[1] bounces per launch, default min(max(spp,16),256)) */
     int32_t reserved[5];
 } ptx_render_opts;
 
@@ -172,6 +173,7 @@ typedef struct {
     float render_ms;          /* CUDA-event time of the last ptx_render on the ctx stream */
     float extend_ms, shade_ms, other_ms;   /* filled when opts.reserved[0] & 1 (per-stage timing) */
     uint64_t node_visits, tri_tests;       /* filled when opts.reserved[0] & 2 (instrumented extend) */
+    uint64_t slot_launches;                /* path loop: sum over launches of the live slots that entered the kernel */
 } ptx_render_stats;
 
 int ptx_render(ptx_ctx* ctx, const ptx_scene* scene, const ptx_camera* cam, ptx_film* film,
