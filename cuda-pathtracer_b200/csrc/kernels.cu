@@ -294,13 +294,14 @@ __global__ void __launch_bounds__(kBlock) k_path_loop(WaveState ws, SceneView sc
     // loop so that __syncwarp can force reconvergence between the phases.  After `iters` steps lanes
     // park at their next segment boundary (the traversal stack is not saved across launches).
     bool alive = live, parked = false;
-    Traversal<24> tr;
+    Traversal tr;
+    TravStack<24> stk;
     tr.begin(pv.d, FLT_MAX);
     for (int it = 0;; it++) {
         const bool active = alive && !parked;
         if (!__any_sync(kFull, active)) break;
         bool done = false;
-        if (active) done = tr.template step<false>(scene, pv.o, pv.d, 1e-4f, nullptr);
+        if (active) done = tr.template step<false, 24>(scene, stk, pv.o, pv.d, 1e-4f, nullptr);
         __syncwarp();
         bool cont = true;
         if (done) {

@@ -44,6 +44,19 @@ struct TraceCounters {
     uint32_t nodes, tris;
 };
 
+// 1/x for the slab tests only (never for hit distances): one MUFU.RCP on the device (<= 1 ulp) instead of
+// the 16-instruction IEEE division; the child boxes are quantised outwards by up to a whole cell, so the
+// last ulp of 1/d does not decide a box test.
+PTX_HD float rcp_fast(float x) {
+#if defined(__CUDA_ARCH__)
+    float r;
+    asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+#else
+    return 1.0f / x;
+#endif
+}
+
 // Moeller-Trumbore on a precomputed edge record.  Returns true and updates (closest, u, v) on accept.
 PTX_HD bool intersect_tri(vec3 v0, vec3 e1, vec3 e2, vec3 o, vec3 d, float t_min, float& closest) {
     const float EPSILON = 1e-8f;
@@ -68,9 +81,14 @@ PTX_HD bool intersect_tri(vec3 v0, vec3 e1, vec3 e2, vec3 o, vec3 d, float t_min
 // as a lane's traversal finishes, so a lane whose ray needed one node visit does not idle while its
 // neighbours visit three (k_path_loop).  trace_closest() below just runs step() to completion.
 // STACK entries of 8 bytes live in registers/local memory.
+// The stack lives in its own object so that the scalar members of Traversal stay in registers
+// (one struct holding both was kept in local memory as a whole: STL/LDL of idx.. in ncu r1c).
 template <int STACK>
+struct TravStack {
+    uint32_t x[STACK], y[STACK];
+};
+
 struct Traversal {
-    uint32_t stack_x[STACK], stack_y[STACK];
     int sp;
     float closest;
     uint32_t best;                 // triangle slot (index into tris) of the closest accepted hit, or kMiss
@@ -80,15 +98,15 @@ struct Traversal {
     PTX_HD void begin(vec3 d, float t_max) {
         sp = 0; closest = t_max; best = kMiss;
         const float ooeps = 8.271806e-25f;   // 2^-80: keeps 1/d finite for axis-parallel rays
-        idx = 1.0f / (fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
-        idy = 1.0f / (fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
-        idz = 1.0f / (fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
+        idx = rcp_fast(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
+        idy = rcp_fast(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
+        idz = rcp_fast(fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
         ng_x = 0; ng_y = 0x80000000u;        // the root as a one-child group
     }
 
     // returns true when the traversal is complete (closest / best are final)
-    template <bool COUNT>
-    PTX_HD bool step(const SceneView& s, vec3 o, vec3 d, float t_min, TraceCounters* ctr) {
+    template <bool COUNT, int STACK>
+    PTX_HD bool step(const SceneView& s, TravStack<STACK>& stk, vec3 o, vec3 d, float t_min, TraceCounters* ctr) {
         // octant: bit set where the direction is negative; slot priority = slot ^ octinv
         uint32_t oct = (d.x < 0.0f ? 4u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 1u : 0u);
         uint32_t octinv = 7u - oct;
@@ -99,7 +117,7 @@ struct Traversal {
             uint32_t imask = ng_y & 0xFFu;
             uint32_t bit = hi_bit(ng_y);
             ng_y &= ~(1u << bit);
-            if (ng_y > 0x00FFFFFFu) { stack_x[sp] = ng_x; stack_y[sp] = ng_y; sp++; }
+            if (ng_y > 0x00FFFFFFu) { stk.x[sp] = ng_x; stk.y[sp] = ng_y; sp++; }
             uint32_t slot = (bit - 24u) ^ octinv;
             uint32_t rel = popc32(imask & ~(0xFFFFFFFFu << slot));
             const u32x4* np = s.nodes + (size_t)(ng_x + rel) * kNodeQuads;
@@ -163,7 +181,7 @@ struct Traversal {
         if (ng_y <= 0x00FFFFFFu) {
             if (sp == 0) return true;
             sp--;
-            ng_x = stack_x[sp]; ng_y = stack_y[sp];
+            ng_x = stk.x[sp]; ng_y = stk.y[sp];
         }
         return false;
     }
@@ -174,9 +192,10 @@ struct Traversal {
 template <int STACK, bool COUNT>
 PTX_HD uint32_t trace_closest(const SceneView& s, vec3 o, vec3 d, float t_min, float t_max, float& t_hit,
                               TraceCounters* ctr) {
-    Traversal<STACK> tr;
+    Traversal tr;
+    TravStack<STACK> stk;
     tr.begin(d, t_max);
-    while (!tr.template step<COUNT>(s, o, d, t_min, ctr)) {}
+    while (!tr.template step<COUNT, STACK>(s, stk, o, d, t_min, ctr)) {}
     t_hit = tr.closest;
     return tr.best;
 }
