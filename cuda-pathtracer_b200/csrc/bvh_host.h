@@ -8,20 +8,9 @@
 #include <cstdint>
 #include <vector>
 
-#include "layout.h"
+#include "bvh_common.h"
 
 namespace ptx {
-
-struct TriIn {          // one input triangle: vertices + the reference primitive it belongs to
-    float v0[3], v1[3], v2[3];
-    uint32_t prim_id;
-};
-
-struct Bvh2Node {
-    aabb box;
-    uint32_t left, right;    // children (inner) ; leaf: left = first index into order[], right = 0
-    uint32_t count;          // > 0 => leaf
-};
 
 struct Bvh2 {
     std::vector<Bvh2Node> nodes;      // nodes[0] = root
@@ -39,16 +28,5 @@ struct Bvh8Result {
 
 void build_bvh2_sah(const TriIn* tris, size_t n, int bins, int max_leaf, Bvh2& out);
 void collapse_bvh8(const Bvh2& b2, const TriIn* tris, size_t n, Bvh8Result& out);
-
-// shared with the device builder's tests: quantise one wide node
-struct WideChild {
-    aabb box;
-    uint32_t is_inner;       // 1 inner, 0 leaf
-    uint32_t tri_count;      // leaf only, 1..3
-    uint32_t tri_offset;     // leaf only: offset from the node's tri_base
-};
-void encode_node(const aabb& node_box, const WideChild* slots /*8, box.lo.x > box.hi.x => empty*/, uint32_t child_base,
-                 uint32_t tri_base, u32x4 out[5]);
-void pack_triangle(const TriIn& t, f32x4 out[3]);
 
 }  // namespace ptx
