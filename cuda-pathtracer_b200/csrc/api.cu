@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "../../include/ptx.h"
+#include "bvh_gpu.h"
 #include "bvh_host.h"
 #include "kernels.cuh"
 #include "loader.h"
@@ -24,6 +25,7 @@ using namespace ptx;
 
 namespace {
 thread_local std::string g_last_error;
+constexpr int kTraversalStack = 24;      // entries of the traversal stack in the kernels (trace_closest<24>, TravStack<24>)
 }
 
 struct ptx_ctx {
@@ -246,29 +248,42 @@ int build_accel(ptx_scene* s, const ptx_build_opts* bo) {
     size_t n = s->packed.tris.size();
     if (n > 0x7FFFFFF0ull) return fail(c, PTX_ERR_INVALID, "scene too large: triangle count must fit 31 bits");
     PTX_CUDA(c, cudaEventRecord(c->ev0, c->stream));
-    Bvh8Result r;
-    {
+    size_t node_bytes = 0, tri_bytes = 0;
+    float sah = 0.f; int depth = 0; aabb bounds;
+    if (builder == 0) {
+        // device builder: breadth-first binned SAH + BVH8 collapse, result stays in HBM (bvh_gpu.cu)
+        GpuBvhResult g; std::string berr;
+        cudaError_t e = build_bvh8_gpu(c->stream, s->packed.tris.data(), n, max_leaf, kTraversalStack, g, berr);
+        if (e != cudaSuccess) { cudaFree(g.d_nodes); cudaFree(g.d_tris); return fail(c, PTX_ERR_CUDA, "GPU BVH build failed: " + berr); }
+        s->d_nodes = g.d_nodes; s->d_tris = g.d_tris;
+        s->view.n_nodes = g.n_nodes; s->view.n_tris = g.n_tris;
+        node_bytes = (size_t)g.n_nodes * kNodeQuads * sizeof(u32x4); tri_bytes = (size_t)g.n_tris * kTriQuads * sizeof(f32x4);
+        sah = g.sah_cost; depth = g.max_depth; bounds = g.bounds;
+    } else {
+        Bvh8Result r;
         Bvh2 b2;
         build_bvh2_sah(s->packed.tris.data(), n, bins, max_leaf, b2);
         collapse_bvh8(b2, s->packed.tris.data(), n, r);
+        if (r.max_depth > kTraversalStack) return fail(c, PTX_ERR_INVALID, "BVH8 deeper than the traversal stack");
         builder = 1;
+        node_bytes = r.nodes.size() * sizeof(u32x4); tri_bytes = r.tris.size() * sizeof(f32x4);
+        PTX_CUDA(c, cudaMalloc(&s->d_nodes, node_bytes));
+        PTX_CUDA(c, cudaMalloc(&s->d_tris, std::max<size_t>(tri_bytes, sizeof(f32x4))));
+        PTX_CUDA(c, cudaMemcpyAsync(s->d_nodes, r.nodes.data(), node_bytes, cudaMemcpyHostToDevice, c->stream));
+        if (!r.tris.empty()) PTX_CUDA(c, cudaMemcpyAsync(s->d_tris, r.tris.data(), tri_bytes, cudaMemcpyHostToDevice, c->stream));
+        PTX_CUDA(c, cudaStreamSynchronize(c->stream));      // r goes out of scope
+        s->view.n_nodes = (uint32_t)(r.nodes.size() / kNodeQuads);
+        s->view.n_tris = (uint32_t)r.tri_src.size();
+        sah = r.sah_cost; depth = r.max_depth; bounds = r.bounds;
     }
-    size_t node_bytes = r.nodes.size() * sizeof(u32x4), tri_bytes = std::max<size_t>(r.tris.size(), 1) * sizeof(f32x4);
-    PTX_CUDA(c, cudaMalloc(&s->d_nodes, node_bytes));
-    PTX_CUDA(c, cudaMalloc(&s->d_tris, tri_bytes));
-    PTX_CUDA(c, cudaMemcpyAsync(s->d_nodes, r.nodes.data(), node_bytes, cudaMemcpyHostToDevice, c->stream));
-    if (!r.tris.empty())
-        PTX_CUDA(c, cudaMemcpyAsync(s->d_tris, r.tris.data(), r.tris.size() * sizeof(f32x4), cudaMemcpyHostToDevice, c->stream));
     PTX_CUDA(c, cudaEventRecord(c->ev1, c->stream));
     PTX_CUDA(c, cudaStreamSynchronize(c->stream));
     float ms = 0.f; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
     s->view.nodes = s->d_nodes; s->view.tris = s->d_tris;
-    s->view.n_nodes = (uint32_t)(r.nodes.size() / kNodeQuads);
-    s->view.n_tris = (uint32_t)r.tri_src.size();
     s->stats.n_nodes = s->view.n_nodes; s->stats.n_triangles = s->view.n_tris;
-    s->stats.node_bytes = (int64_t)node_bytes; s->stats.triangle_bytes = (int64_t)(r.tris.size() * sizeof(f32x4));
-    s->stats.sah_cost = r.sah_cost; s->stats.max_depth = r.max_depth; s->stats.builder = builder; s->stats.build_ms = ms;
-    st3(s->stats.bounds_min, r.bounds.lo); st3(s->stats.bounds_max, r.bounds.hi);
+    s->stats.node_bytes = (int64_t)node_bytes; s->stats.triangle_bytes = (int64_t)tri_bytes;
+    s->stats.sah_cost = sah; s->stats.max_depth = depth; s->stats.builder = builder; s->stats.build_ms = ms;
+    st3(s->stats.bounds_min, bounds.lo); st3(s->stats.bounds_max, bounds.hi);
     return PTX_OK;
 }
 

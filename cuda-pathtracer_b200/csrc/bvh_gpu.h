@@ -1,0 +1,28 @@
+// bvh_gpu.h -- device BVH builder (bvh_gpu.cu): binned-SAH BVH2 built breadth-first on the GPU, collapsed and
+// compressed to the BVH8 layout of layout.h without leaving HBM.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+
+#include "bvh_common.h"
+
+namespace ptx {
+
+struct GpuBvhResult {
+    u32x4* d_nodes = nullptr;      // n_nodes * 5, cudaMalloc'ed; owned by the caller
+    f32x4* d_tris = nullptr;       // n_tris * 3
+    uint32_t n_nodes = 0, n_tris = 0;
+    uint32_t n_bvh2_nodes = 0;
+    int bvh2_levels = 0;
+    int max_depth = 0;             // BVH8 depth
+    float sah_cost = 0.f;
+    aabb bounds;
+};
+
+// h_tris: n input triangles on the host.  Returns cudaSuccess or the failing CUDA error; `err` gets the text.
+// A tree deeper than `max_bvh8_depth` (the traversal stack size) is reported as cudaErrorInvalidValue.
+cudaError_t build_bvh8_gpu(cudaStream_t stream, const TriIn* h_tris, size_t n, int max_leaf, int max_bvh8_depth, GpuBvhResult& out,
+                           std::string& err);
+
+}  // namespace ptx
