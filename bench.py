@@ -2,7 +2,7 @@
 """bench.py -- headline benchmark of the path-tracing hot path (contract: see the task statement).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--rng compat|philox]
-                    [--pipeline fused|wavefront] [--workload c1|c2|c4]
+                    [--pipeline fused|wavefront] [--workload c1|c2|c3|c4]
 
 One "step" = one frame of the hot path: ptx_render (raygen/extend/shade/compact) + film resolve.
 N = 1 workload = BASELINE.json configs[1]: scenes/cbox_quads.obj, 1920x1080, 1024 spp, depth 16, reference
@@ -27,6 +27,8 @@ WORKLOADS = {
     "c1": ("cbox.obj", 512, 512, 64, 8),
     "c2": ("cbox_quads.obj", 1920, 1080, 1024, 16),
     "c4": ("cbox_quads.obj", 3840, 2160, 4096, 8),
+    # generated on the box (cuda-pathtracer_b200/scenegen.py): two displaced icospheres, 10 485 772 triangles, Cornell enclosure
+    "c3": ("generated:c3_level9", 1920, 1080, 256, 8),
 }
 METRIC = "Mpaths*bounces/s"
 
@@ -139,7 +141,16 @@ def run_ours(args, scene_path, w, h, spp, depth):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     ctx = pkg.Context(local_rank)
-    scene = ctx.load_scene(scene_path)              # scene replicated on every GPU (one-time, outside the timed region)
+    generated = os.path.basename(scene_path).startswith("generated:")
+    if generated:                                   # scene replicated on every GPU (one-time, outside the timed region)
+        from cuda_pathtracer_b200 import scenegen
+        level = int(scene_path.rsplit("level", 1)[1])
+        tris, mat, mats = scenegen.c3_scene(pkg.parse_scene_file(os.path.join(ROOT, "scenes", "cbox_quads.obj")), level)
+        scene = ctx.scene_from_triangles(tris, mat, mats, builder=0)
+        del tris, mat
+    else:
+        scene = ctx.load_scene(scene_path)
+    scene_stats = scene.stats()
     cam = pkg.default_camera(w, h)
     film = ctx.create_film(w, h)
     film_ptr, film_bytes = film.device_buffer()
@@ -228,6 +239,15 @@ def run_ours(args, scene_path, w, h, spp, depth):
         else:
             bytes_per_seg = 4 + 48 + 8 + 40 + (48 if rng_mode == pkg.RNG_XORWOW_COMPAT else 0)
             kname, k_ms = "k_shade<rng>", st_t["shade_ms"]
+        traversal = None
+        if scene_stats["node_bytes"] + scene_stats["triangle_bytes"] > 126e6:
+            # scene larger than L2: the bound is node + triangle fetch traffic; N_node, N_tri per segment
+            # measured by the instrumented extend kernel on a 2-spp frame outside the timed region
+            kwc = dict(kw); kwc.update(spp=2, pipeline=pkg.PIPELINE_WAVEFRONT)
+            st_c = ctx.render(scene, cam, film, count_work=True, **kwc)
+            n_node, n_tri = st_c["node_visits"] / st_c["segments"], st_c["tri_tests"] / st_c["segments"]
+            bytes_per_seg = n_node * 80 + n_tri * 48
+            traversal = {"nodes_per_segment": n_node, "tris_per_segment": n_tri, "node_bytes": 80, "tri_bytes": 48}
         achieved = st_t["segments"] * bytes_per_seg / (k_ms * 1e-3) * 1e-9 if k_ms > 0 else None
         out = {
             "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -243,9 +263,14 @@ def run_ours(args, scene_path, w, h, spp, depth):
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
                          "traffic": None, "peak_source": peak_src, "bytes_per_segment": bytes_per_seg,
-                         "kernel_ms_per_step": k_ms, "kernel_share_of_step": k_ms / st_t["render_ms"] if st_t["render_ms"] else None},
+                         "kernel_ms_per_step": k_ms, "kernel_share_of_step": k_ms / st_t["render_ms"] if st_t["render_ms"] else None,
+                         "traversal": traversal, "bytes_per_slot_launch": bytes_per_slot_launch},
+            "scene": {k: scene_stats[k] for k in ("n_triangles", "n_nodes", "node_bytes", "triangle_bytes", "build_ms", "builder", "max_depth", "sah_cost")},
         }
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and generated:
+            out["cpu_baseline"] = {"value": None, "unit": METRIC, "cores": 0, "kind": "reference",
+                                   "sample": "not runnable: the reference keeps 4 364-byte primitives (45.8 GB for this scene) and builds its BVH on one host thread (BASELINE.md)"}
+        elif world == 1 and not args.no_cpu_baseline:
             try:
                 cb_spp = 2
                 spp_ratio = segments_per_path_estimate(scene_path, w, h, depth)
@@ -277,6 +302,10 @@ def main():
         spp = args.spp
     args.workload_desc = f"{args.workload}: scenes/{scene} {w}x{h}, {spp} spp, max depth {depth}, reference Russian roulette (depth>2, cap 0.95), SAMPLING_BSDF"
     scene_path = os.path.join(ROOT, "scenes", scene)
+    if args.impl == "reference" and scene.startswith("generated:"):
+        if int(os.environ.get("RANK", "0")) == 0:
+            print(json.dumps({"impl": "reference", "unavailable": "reference cannot hold this scene (4 364 B per primitive, single-thread BVH build); see BASELINE.md"}))
+        return
     if args.impl == "reference":
         run_reference(args, scene_path, w, h, spp, depth)
     else:

@@ -79,6 +79,7 @@ EXPORTS = [
     "ptx_camera_set", "ptx_camera_update", "ptx_camera_orbit", "ptx_camera_default",
     "ptx_film_create", "ptx_film_reset", "ptx_film_clear", "ptx_film_resolve_rgb8", "ptx_film_read_linear", "ptx_film_write",
     "ptx_film_device_buffer", "ptx_film_set_sample_count", "ptx_film_destroy",
+    "ptx_shard_pixel_count", "ptx_shard_owned_pixels", "ptx_shard_sample_range",
     "ptx_render", "ptx_render_stats_get", "ptx_trace_primary_ids", "ptx_trace_rays", "ptx_film_rng_state",
 ]
 
@@ -116,6 +117,10 @@ def lib():
         L.ptx_film_read_linear.argtypes = [C.c_void_p, C.c_void_p]
         L.ptx_film_device_buffer.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.ptx_camera_set.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float]
+        L.ptx_shard_pixel_count.restype = C.c_int64
+        L.ptx_shard_pixel_count.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+        L.ptx_shard_owned_pixels.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int64]
+        L.ptx_shard_sample_range.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -142,6 +147,21 @@ def parse_scene_file(path, convert_quads=False, subdivision=0, mirror_from_mtl=F
         return np.frombuffer(buf, dtype=PRIM_DTYPE).copy()
     finally:
         lib().ptx_free_primitives(p)
+
+
+def shard_owned_pixels(width, height, shard_mode, rank, world):
+    """Pixel indices (y*w + x) rank `rank` of `world` renders (host arithmetic only)."""
+    n = lib().ptx_shard_pixel_count(int(width), int(height), int(shard_mode), int(rank), int(world))
+    _check(int(n))
+    out = np.empty(int(n), np.uint32)
+    _check(lib().ptx_shard_owned_pixels(int(width), int(height), int(shard_mode), int(rank), int(world), _ptr(out), int(n)))
+    return out
+
+
+def shard_sample_range(spp, shard_mode, rank, world):
+    first, count = C.c_int32(), C.c_int32()
+    _check(lib().ptx_shard_sample_range(int(spp), int(shard_mode), int(rank), int(world), C.byref(first), C.byref(count)))
+    return first.value, count.value
 
 
 def default_camera(width, height):

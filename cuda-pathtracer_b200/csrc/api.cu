@@ -583,8 +583,9 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     if (!opts->accumulate) film->sample_base = 0;
     rp.sample_begin = film->sample_base;                   // progressive frames continue the sample index
     if (shard_mode == PTX_SHARD_SAMPLES) {
-        int lo = (int)((long long)opts->spp * rank / world), hi = (int)((long long)opts->spp * (rank + 1) / world);
-        spp_local = hi - lo;
+        int32_t lo = 0, cnt = 0;
+        ptx_shard_sample_range(opts->spp, shard_mode, rank, world, &lo, &cnt);
+        spp_local = cnt;
         rp.sample_begin += (uint32_t)lo;
     }
     rp.spp = spp_local;
@@ -690,6 +691,33 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     if (shard_mode == PTX_SHARD_SAMPLES) film->total_spp += (float)spp_local;   // partial: caller reduces and sets the total
     else film->total_spp += (float)opts->spp;
     film->sample_base += (uint32_t)opts->spp;
+    return PTX_OK;
+}
+
+int64_t ptx_shard_pixel_count(int width, int height, int shard_mode, int rank, int world) {
+    if (width <= 0 || height <= 0 || world <= 0 || rank < 0 || rank >= world) return fail(nullptr, PTX_ERR_INVALID, "ptx_shard_pixel_count: bad argument");
+    return (int64_t)owned_pixel_count(width, height, shard_mode, rank, world);
+}
+
+int ptx_shard_owned_pixels(int width, int height, int shard_mode, int rank, int world, uint32_t* pixels_out, int64_t capacity) {
+    int64_t n = ptx_shard_pixel_count(width, height, shard_mode, rank, world);
+    if (n < 0) return (int)n;
+    if (!pixels_out || capacity < n) return fail(nullptr, PTX_ERR_INVALID, "ptx_shard_owned_pixels: buffer too small");
+    // same map as k_slot_pixels (kernels.cu)
+    const uint32_t band_px = (uint32_t)kBandRows * (uint32_t)width;
+    for (int64_t i = 0; i < n; i++) {
+        if (shard_mode != PTX_SHARD_TILES || world <= 1) { pixels_out[i] = (uint32_t)i; continue; }
+        uint32_t local_band = (uint32_t)i / band_px, within = (uint32_t)i % band_px;
+        pixels_out[i] = (local_band * (uint32_t)world + (uint32_t)rank) * band_px + within;
+    }
+    return PTX_OK;
+}
+
+int ptx_shard_sample_range(int spp, int shard_mode, int rank, int world, int32_t* first, int32_t* count) {
+    if (spp < 0 || world <= 0 || rank < 0 || rank >= world || !first || !count) return fail(nullptr, PTX_ERR_INVALID, "ptx_shard_sample_range: bad argument");
+    if (shard_mode != PTX_SHARD_SAMPLES) { *first = 0; *count = spp; return PTX_OK; }
+    int lo = (int)((long long)spp * rank / world), hi = (int)((long long)spp * (rank + 1) / world);
+    *first = lo; *count = hi - lo;
     return PTX_OK;
 }
 

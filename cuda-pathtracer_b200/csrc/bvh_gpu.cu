@@ -9,7 +9,7 @@
 //   1. k_prim_setup      triangle AABB + centroid, scene / centroid bounds (warp-reduced float atomics)
 //   2. Morton sort       30-bit codes of the centroids, cub radix sort -> processing order (locality for the atomics)
 //   3. per level, over ALL primitives, no data movement (a primitive only carries the id of its current node):
-//        k_bin           16 bins on the node's longest centroid axis: box + count per bin (atomics)
+//        k_bin           16 bins on each axis of the node's centroid bounds: box + count per bin (atomics)
 //        k_split         one thread per node of the level: SAH sweep, leaf decision, child boxes / counts
 //        scan            exclusive sum of the split flags -> deterministic child indices
 //        k_make_children write the two children
@@ -60,8 +60,8 @@ struct PrimBox {           // 32 B: AABB of one triangle (centroid = box centre,
 struct BuildNode {
     OrdBox cbox;           // centroid bounds (filled by atomics while the parent is relabelled)
     uint32_t rank_lo, rank_hi;   // min / max Morton rank of its primitives (fallback split)
-    int32_t axis;          // split axis chosen for this node (-1: none)
-    float cmin, cscale;    // bin = (centroid[axis] - cmin) * cscale
+    int32_t axis;          // -1: no centroid extent (leaf or rank split); >= 0: binned; after k_split the chosen split axis
+    float cmin[3], cscale[3];    // bin on axis a = (centroid[a] - cmin[a]) * cscale[a]; cscale[a] == 0: axis not binned
     int32_t split_bin;     // primitives with bin <= split_bin go left; -2 => fallback split by rank
     uint32_t rank_mid;
     uint32_t pcount;       // primitives in the node
@@ -150,7 +150,7 @@ __global__ void k_init_root(Bvh2Node* nodes, BuildNode* bn, const OrdBox* scene,
     nodes[0].box = ordbox_to_aabb(scene[0]);
     nodes[0].left = 0; nodes[0].right = 0; nodes[0].count = 0;
     BuildNode b;
-    b.cbox = scene[1]; b.rank_lo = 0; b.rank_hi = n - 1; b.axis = -1; b.cmin = 0.f; b.cscale = 0.f; b.split_bin = -1; b.rank_mid = 0;
+    b.cbox = scene[1]; b.rank_lo = 0; b.rank_hi = n - 1; b.axis = -1; for (int a = 0; a < 3; a++) { b.cmin[a] = 0.f; b.cscale[a] = 0.f; } b.split_bin = -1; b.rank_mid = 0;
     b.pcount = n; b.fbox = ordbox_empty(); b.box_from_atomics = 0;
     bn[0] = b;
 }
@@ -161,21 +161,22 @@ __global__ void __launch_bounds__(kThreads) k_prepare(Bvh2Node* nodes, BuildNode
     if (node >= le) return;
     BuildNode b = bn[node];
     if (b.box_from_atomics) nodes[node].box = ordbox_to_aabb(b.fbox);
-    int axis = -1; float best = 0.f, cmin = 0.f;
-    if (b.pcount > 1) {
-        for (int a = 0; a < 3; a++) {
+    int axis = -1;
+    for (int a = 0; a < 3; a++) {
+        b.cmin[a] = 0.f; b.cscale[a] = 0.f;
+        if (b.pcount > 1) {
             float lo = ordbox_lo(b.cbox, a), hi = ordbox_hi(b.cbox, a);
-            if (hi - lo > best) { best = hi - lo; axis = a; cmin = lo; }
+            if (hi > lo) { b.cmin[a] = lo; b.cscale[a] = (float)kBins / (hi - lo); axis = a; }
         }
     }
-    b.axis = axis; b.cmin = cmin; b.cscale = axis >= 0 ? (float)kBins / best : 0.f;
+    b.axis = axis;
     b.split_bin = -1;
     bn[node] = b;
 }
 
-__device__ __forceinline__ int bin_of(const PrimBox& pb, const BuildNode& b) {
-    float c = 0.5f * (pb.lo[b.axis] + pb.hi[b.axis]);
-    int k = (int)((c - b.cmin) * b.cscale);
+__device__ __forceinline__ int bin_of(const PrimBox& pb, int axis, float cmin, float cscale) {
+    float c = 0.5f * (pb.lo[axis] + pb.hi[axis]);
+    int k = (int)((c - cmin) * cscale);
     return k < 0 ? 0 : (k >= kBins ? kBins - 1 : k);
 }
 
@@ -185,12 +186,16 @@ __global__ void __launch_bounds__(kThreads) k_bin(const PrimBox* __restrict__ bo
     if (r >= n) return;
     uint32_t node = prim_node[r];
     if (node < lb || node >= le) return;
-    const BuildNode b = bn[node];
-    if (b.axis < 0) return;
+    const BuildNode* b = bn + node;
+    if (b->axis < 0) return;
     const PrimBox pb = boxes[r];
-    Bin* dst = bins + (size_t)(node - lb) * kBins + bin_of(pb, b);
-    ordbox_atomic_grow(&dst->box, pb.lo, pb.hi);
-    atomicAdd(&dst->count, 1u);
+    for (int a = 0; a < 3; a++) {
+        const float cs = b->cscale[a];
+        if (!(cs > 0.f)) continue;
+        Bin* dst = bins + ((size_t)(node - lb) * 3 + a) * kBins + bin_of(pb, a, b->cmin[a], cs);
+        ordbox_atomic_grow(&dst->box, pb.lo, pb.hi);
+        atomicAdd(&dst->count, 1u);
+    }
 }
 
 __global__ void __launch_bounds__(kThreads) k_split(Bvh2Node* nodes, BuildNode* bn, uint32_t lb, uint32_t le, const Bin* __restrict__ bins,
@@ -208,23 +213,28 @@ __global__ void __launch_bounds__(kThreads) k_split(Bvh2Node* nodes, BuildNode* 
             sc[node - lb] = c;
         }
     } else {
-        const Bin* nb = bins + (size_t)(node - lb) * kBins;
-        float right_area[kBins];
-        aabb acc = aabb_empty();
-        for (int k = kBins - 1; k > 0; k--) {
-            if (nb[k].count) aabb_grow(acc, ordbox_to_aabb(nb[k].box));
-            right_area[k] = aabb_half_area(acc);
+        float best_cost = FLT_MAX; int best_bin = -1, best_axis = -1;
+        for (int ax = 0; ax < 3; ax++) {
+            if (!(b.cscale[ax] > 0.f)) continue;
+            const Bin* nb = bins + ((size_t)(node - lb) * 3 + ax) * kBins;
+            float right_area[kBins];
+            aabb acc = aabb_empty();
+            for (int k = kBins - 1; k > 0; k--) {
+                if (nb[k].count) aabb_grow(acc, ordbox_to_aabb(nb[k].box));
+                right_area[k] = aabb_half_area(acc);
+            }
+            acc = aabb_empty();
+            uint32_t nl = 0;
+            for (int k = 0; k < kBins - 1; k++) {
+                if (nb[k].count) aabb_grow(acc, ordbox_to_aabb(nb[k].box));
+                nl += nb[k].count;
+                uint32_t nr = cnt - nl;
+                if (nl == 0 || nr == 0) continue;
+                float c = aabb_half_area(acc) * (float)nl + right_area[k + 1] * (float)nr;
+                if (c < best_cost) { best_cost = c; best_bin = k; best_axis = ax; }
+            }
         }
-        acc = aabb_empty();
-        uint32_t nl = 0; float best_cost = FLT_MAX; int best_bin = -1;
-        for (int k = 0; k < kBins - 1; k++) {
-            if (nb[k].count) aabb_grow(acc, ordbox_to_aabb(nb[k].box));
-            nl += nb[k].count;
-            uint32_t nr = cnt - nl;
-            if (nl == 0 || nr == 0) continue;
-            float c = aabb_half_area(acc) * (float)nl + right_area[k + 1] * (float)nr;
-            if (c < best_cost) { best_cost = c; best_bin = k; }
-        }
+        const Bin* nb = bins + ((size_t)(node - lb) * 3 + (best_axis < 0 ? 0 : best_axis)) * kBins;
         float parent_area = aabb_half_area(nodes[node].box);
         float split_cost = kTravCost + (parent_area > 0.f ? best_cost / parent_area : (float)cnt);
         bool leaf = cnt <= (uint32_t)max_leaf && (float)cnt <= split_cost;
@@ -240,7 +250,7 @@ __global__ void __launch_bounds__(kThreads) k_split(Bvh2Node* nodes, BuildNode* 
                 else { aabb_grow(c.rbox, ordbox_to_aabb(nb[k].box)); c.rcount += nb[k].count; }
             }
             sc[node - lb] = c;
-            b.split_bin = best_bin; flag = 1;
+            b.split_bin = best_bin; b.axis = best_axis; flag = 1;
         }
     }
     if (!flag) { nodes[node].count = cnt; nodes[node].left = 0; nodes[node].right = 0; }     // leaf; `left` = first slot, set after the final sort
@@ -260,7 +270,7 @@ __global__ void __launch_bounds__(kThreads) k_make_children(Bvh2Node* nodes, Bui
         Bvh2Node nn; nn.box = side ? c.rbox : c.lbox; nn.left = 0; nn.right = 0; nn.count = 0;
         nodes[l + side] = nn;
         BuildNode b;
-        b.cbox = ordbox_empty(); b.rank_lo = 0xFFFFFFFFu; b.rank_hi = 0u; b.axis = -1; b.cmin = 0.f; b.cscale = 0.f; b.split_bin = -1; b.rank_mid = 0;
+        b.cbox = ordbox_empty(); b.rank_lo = 0xFFFFFFFFu; b.rank_hi = 0u; b.axis = -1; for (int a = 0; a < 3; a++) { b.cmin[a] = 0.f; b.cscale[a] = 0.f; } b.split_bin = -1; b.rank_mid = 0;
         b.pcount = fallback ? 0u : (side ? c.rcount : c.lcount);
         b.fbox = ordbox_empty(); b.box_from_atomics = fallback ? 1u : 0u;
         bn[l + side] = b;
@@ -281,8 +291,8 @@ __global__ void __launch_bounds__(kThreads) k_relabel(const PrimBox* __restrict_
     uint32_t side;
     if (split_bin == -2) side = r > b->rank_mid ? 1u : 0u;
     else {
-        BuildNode bb; bb.axis = b->axis; bb.cmin = b->cmin; bb.cscale = b->cscale;
-        side = bin_of(pb, bb) > split_bin ? 1u : 0u;
+        const int ax = b->axis;
+        side = bin_of(pb, ax, b->cmin[ax], b->cscale[ax]) > split_bin ? 1u : 0u;
     }
     uint32_t child = left + side;
     prim_node[r] = child;
@@ -436,11 +446,11 @@ cudaError_t build_bvh8_gpu(cudaStream_t st, const TriIn* h_tris, size_t n_in, in
             level_cap = std::max<size_t>((size_t)width * 2, 1024);
             BG_CUDA(cudaStreamSynchronize(st));
             BG_CUDA(d_flags.alloc(4 * level_cap)); BG_CUDA(d_scan.alloc(4 * level_cap));
-            BG_CUDA(d_sc.alloc(sizeof(SplitChildren) * level_cap)); BG_CUDA(d_bins.alloc(sizeof(Bin) * kBins * level_cap));
+            BG_CUDA(d_sc.alloc(sizeof(SplitChildren) * level_cap)); BG_CUDA(d_bins.alloc(sizeof(Bin) * 3 * kBins * level_cap));
         }
         k_prepare<<<grid_for(width), kThreads, 0, st>>>(d_nodes.as<Bvh2Node>(), d_bn.as<BuildNode>(), lb, le);
         // all-zero = empty boxes, count 0
-        BG_CUDA(cudaMemsetAsync(d_bins.p, 0, sizeof(Bin) * kBins * (size_t)width, st));
+        BG_CUDA(cudaMemsetAsync(d_bins.p, 0, sizeof(Bin) * 3 * kBins * (size_t)width, st));
         k_bin<<<grid_for(n), kThreads, 0, st>>>(d_boxes.as<PrimBox>(), d_prim_node.as<uint32_t>(), n, d_bn.as<BuildNode>(), lb, le, d_bins.as<Bin>());
         k_split<<<grid_for(width), kThreads, 0, st>>>(d_nodes.as<Bvh2Node>(), d_bn.as<BuildNode>(), lb, le, d_bins.as<Bin>(), max_leaf,
                                                        d_flags.as<uint32_t>(), d_sc.as<SplitChildren>());

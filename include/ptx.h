@@ -176,6 +176,12 @@ typedef struct {
     uint64_t slot_launches;                /* path loop: sum over launches of the live slots that entered the kernel */
 } ptx_render_stats;
 
+/* Host-side sharding arithmetic (no device work; what a multi-process driver and the CPU tests use to check that the
+ * ranks' shares are disjoint and complete).  Tiles: bands of 4 image rows dealt round-robin; samples: contiguous ranges. */
+int64_t ptx_shard_pixel_count(int width, int height, int shard_mode, int rank, int world);
+int ptx_shard_owned_pixels(int width, int height, int shard_mode, int rank, int world, uint32_t* pixels_out, int64_t capacity);
+int ptx_shard_sample_range(int spp, int shard_mode, int rank, int world, int32_t* first, int32_t* count);
+
 int ptx_render(ptx_ctx* ctx, const ptx_scene* scene, const ptx_camera* cam, ptx_film* film,
                const ptx_render_opts* opts);
 int ptx_render_stats_get(const ptx_ctx* ctx, ptx_render_stats* out);
