@@ -640,7 +640,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
         if (path_loop) {
             iters = loop_iters;
             if (stage_timing) cudaEventRecord(c->stage_events[1], c->stream);
-            launch_path_loop(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, q, qbound, iters);
+            launch_path_loop(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, q, qbound, iters, opts->reserved[2]);
             if (stage_timing) cudaEventRecord(c->stage_events[2], c->stream);
             st.kernel_launches++; st.iterations += (uint64_t)iters;
         }

@@ -248,8 +248,8 @@ __device__ __forceinline__ void start_path_xy(const CameraView& cam, float fx, f
     pv.depth = 0;
 }
 
-template <int RNG>
-__global__ void __launch_bounds__(kBlock) k_path_loop(WaveState ws, SceneView scene, FilmView film, CameraView cam, RenderParams rp, int q,
+template <int RNG, int MINB>
+__global__ void __launch_bounds__(kBlock, MINB) k_path_loop(WaveState ws, SceneView scene, FilmView film, CameraView cam, RenderParams rp, int q,
                                                       int iters) {
     constexpr unsigned kFull = 0xFFFFFFFFu;
     uint32_t k = blockIdx.x * kBlock + threadIdx.x;
@@ -567,11 +567,16 @@ void launch_bounce(cudaStream_t st, int rng_mode, const WaveState& ws, const Sce
     else k_shade<1, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp, q);
 }
 void launch_path_loop(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FilmView& film, const CameraView& cam,
-                      const RenderParams& rp, int q, uint32_t qlen_bound, int iters) {
+                      const RenderParams& rp, int q, uint32_t qlen_bound, int iters, int min_blocks) {
     if (!qlen_bound || iters <= 0) return;
     unsigned g = blocks_for(qlen_bound, kBlock);
-    if (rng_mode == 0) k_path_loop<0><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp, q, iters);
-    else k_path_loop<1><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp, q, iters);
+    if (min_blocks == 4) {          // 64 registers, 4 CTAs / SM
+        if (rng_mode == 0) k_path_loop<0, 4><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp, q, iters);
+        else k_path_loop<1, 4><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp, q, iters);
+    } else {                        // 80 registers, 3 CTAs / SM
+        if (rng_mode == 0) k_path_loop<0, 3><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp, q, iters);
+        else k_path_loop<1, 3><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp, q, iters);
+    }
 }
 void launch_compact(cudaStream_t st, const WaveState& ws, int q, uint32_t qlen_bound, uint32_t* scratch) {
     if (!qlen_bound) return;

@@ -15,7 +15,7 @@ with pkg.Context(0) as ctx:
     print(json.dumps(scene.stats()), flush=True)
     cam = pkg.default_camera(w, h)
     film = ctx.create_film(w, h)
-    for name, kw in [("loop/xorwow", dict(pipeline=2)), ("loop/philox", dict(pipeline=2, rng_mode=1)), ("fused/xorwow", dict(pipeline=1)),
+    for name, kw in [("loop/xorwow", dict(pipeline=2)), ("loop/xorwow/mb4", dict(pipeline=2, loop_min_blocks=4)), ("loop/philox/mb4", dict(pipeline=2, rng_mode=1, loop_min_blocks=4)), ("loop/philox", dict(pipeline=2, rng_mode=1)), ("fused/xorwow", dict(pipeline=1)),
                      ("wavefront/xorwow", dict(pipeline=0)), ("wavefront/xorwow/timed", dict(pipeline=0, stage_timing=True)),
                      ("wavefront/xorwow/count", dict(pipeline=0, count_work=True))]:
         for rep in range(2):

@@ -12,7 +12,7 @@ with pkg.Context(0) as ctx:
     print(scene.stats())
     cam = pkg.default_camera(w, h)
     t0 = time.time(); film = ctx.create_film(w, h); ctx.sync(); print("film create + rng init s", time.time() - t0)
-    for name, kw in [("loop/xorwow", dict(pipeline=2)), ("loop/xorwow/64", dict(pipeline=2, loop_iters=64)), ("loop/xorwow/timed", dict(pipeline=2, stage_timing=True)), ("loop/philox", dict(pipeline=2, rng_mode=1)), ("wavefront/xorwow", {}), ("fused/xorwow", dict(pipeline=1)), ("wavefront/philox", dict(rng_mode=1)),
+    for name, kw in [("loop/xorwow", dict(pipeline=2)), ("loop/xorwow/mb4", dict(pipeline=2, loop_min_blocks=4)), ("loop/xorwow/256", dict(pipeline=2, loop_iters=256)), ("loop/philox/mb4", dict(pipeline=2, rng_mode=1, loop_min_blocks=4)), ("loop/xorwow/timed", dict(pipeline=2, stage_timing=True)), ("loop/philox", dict(pipeline=2, rng_mode=1)), ("wavefront/xorwow", {}), ("fused/xorwow", dict(pipeline=1)), ("wavefront/philox", dict(rng_mode=1)),
                      ("fused/philox", dict(rng_mode=1, pipeline=1)), ("wavefront/xorwow/timed", dict(stage_timing=True)),
                      ("wavefront/xorwow/count", dict(count_work=True))]:
         for rep in range(2):
