@@ -136,9 +136,9 @@ def _ptr(a):
     return a.ctypes.data_as(C.c_void_p)
 
 
-def parse_scene_file(path, convert_quads=False, subdivision=0, mirror_from_mtl=False):
-    """Host-only parse (loadOBJ semantics): structured numpy array in the reference's primitive numbering."""
-    opts = LoadOpts(int(convert_quads), int(subdivision), 0, int(mirror_from_mtl), 0)
+def parse_scene_file(path, convert_quads=False, subdivision=0, mirror_from_mtl=False, triangle_cap=0):
+    """Host-only parse (loadOBJ / loadPBRT semantics): structured numpy array in the reference's primitive numbering."""
+    opts = LoadOpts(int(convert_quads), int(subdivision), int(triangle_cap), int(mirror_from_mtl), 0)
     p = C.c_void_p()
     n = C.c_int64()
     _check(lib().ptx_parse_scene_file(os.fspath(path).encode(), C.byref(opts), C.byref(p), C.byref(n)))

@@ -315,8 +315,10 @@ int parse_file(const char* path, const ptx_load_opts* opts, std::vector<ptx_prim
     std::string p = path ? path : "";
     if (has_suffix(p, ".obj")) {
         if (!load_obj(p, opts && opts->mirror_from_mtl, prims, err)) return PTX_ERR_IO;
+    } else if (has_suffix(p, ".pbrt")) {
+        if (!load_pbrt(p, opts && opts->mirror_from_mtl, opts ? (long long)opts->triangle_cap : 0ll, prims, err)) return PTX_ERR_IO;
     } else {
-        err = "unsupported scene format (supported: .obj): " + p;      // loadScene, file_manager.h:291-315
+        err = "unsupported scene format (supported: .obj, .pbrt): " + p;      // loadScene, file_manager.h:291-315
         return PTX_ERR_UNSUPPORTED;
     }
     if (opts && opts->convert_quads) split_quads(prims);                // application_state.h:404-407

@@ -93,7 +93,13 @@ static void split_quads(std::vector<Primitive>& prims) {
 static bool load_scene(const char* path, bool convert_quads, HostScene& hs) {
     Primitive* list = nullptr; int n = 0;
     std::streambuf* old = std::cout.rdbuf(nullptr);   // silence the reference's banners
-    bool ok = loadOBJ(path, &list, n);
+    bool ok;
+#if defined(USE_PBRT_LOADER) && !defined(__CUDA_ARCH__)   // the reference hides loadPBRT from the device pass (file_manager.h:280)
+    std::string sp(path);
+    if (sp.size() > 5 && sp.substr(sp.size() - 5) == ".pbrt") ok = loadPBRT(sp, &list, n);      // utils/pbrt_loader.h:178
+    else
+#endif
+        ok = loadOBJ(path, &list, n);
     if (ok) {
         hs.prims.assign(list, list + n);
         delete[] list;

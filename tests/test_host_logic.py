@@ -248,3 +248,48 @@ def test_integrator_core_bit_exact_vs_reference(pkg, emu, gold, tag, w, h, spp, 
     assert np.array_equal(bits(lin), bits(gold[key + "_linear"]))
     assert np.array_equal(rgb, gold[key + "_rgb8"])
     emu.emu_scene_free(s)
+
+
+@pytest.mark.parametrize("name", ["basic", "materials", "transforms"])
+def test_pbrt_loader_matches_reference_loadPBRT(pkg, name):
+    """tests/golden/pbrt_vectors.npz holds what the reference's loadPBRT (utils/pbrt_loader.h:178-422 + its vendored
+    pbrtParser) returns for tests/pbrt/*.pbrt (tests/golden/make_golden_pbrt.py).  Order, vertices, normals, albedo and
+    emission must match bit for bit."""
+    gold = np.load(os.path.join(GOLDEN, "pbrt_vectors.npz"))
+    pr = pkg.parse_scene_file(os.path.join(ROOT, "tests", "pbrt", name + ".pbrt"))
+    assert len(pr) == len(gold[name + "_v"])
+    assert (pr["type"] == 0).all() and (gold[name + "_type"] == 0).all()
+    assert np.array_equal(pr["v"][:, :3].reshape(len(pr), 9), gold[name + "_v"])
+    assert np.array_equal(pr["normal"], gold[name + "_normal"])
+    assert np.array_equal(pr["bsdf"], gold[name + "_bsdf"])
+    assert np.array_equal(pr["Le"], gold[name + "_Le"])
+    assert (pr["material_type"] == 0).all()                      # reference semantics: mirrors are diffuse albedos
+
+
+def test_pbrt_loader_extension_and_errors(pkg, tmp_path):
+    pr = pkg.parse_scene_file(os.path.join(ROOT, "tests", "pbrt", "materials.pbrt"), mirror_from_mtl=True)
+    assert list(np.nonzero(pr["material_type"] == 1)[0]) == [4, 5]            # the two `Material "mirror"` triangles
+    bad = tmp_path / "bad.pbrt"
+    bad.write_text('WorldBegin\nShape "plymesh" "string filename" "x.ply"\nWorldEnd\n')
+    with pytest.raises(pkg.PtxError):
+        pkg.parse_scene_file(str(bad))
+    bad.write_text('WorldBegin\nFrobnicate 1 2 3\nWorldEnd\n')
+    with pytest.raises(pkg.PtxError):
+        pkg.parse_scene_file(str(bad))
+    bad.write_text('WorldBegin\nShape "sphere" "float radius" [1]\nWorldEnd\n')      # no triangles: loadPBRT returns false
+    with pytest.raises(pkg.PtxError):
+        pkg.parse_scene_file(str(bad))
+    with pytest.raises(pkg.PtxError):
+        pkg.parse_scene_file(str(tmp_path / "missing.pbrt"))
+
+
+def test_pbrt_triangle_cap_proxy(pkg):
+    """ptx_load_opts.triangle_cap reproduces the reference's bounding-box proxy (pbrt_loader.h:205-272): 12 triangles,
+    albedo (0.8, 0.2, 0.2), spanning the scene bounds."""
+    path = os.path.join(ROOT, "tests", "pbrt", "basic.pbrt")
+    full = pkg.parse_scene_file(path)
+    proxy = pkg.parse_scene_file(path, triangle_cap=5)
+    assert len(proxy) == 12 and np.allclose(proxy["bsdf"], [0.8, 0.2, 0.2])
+    fv, pv = full["v"][:, :3].reshape(-1, 3), proxy["v"][:, :3].reshape(-1, 3)
+    assert np.array_equal(fv.min(0), pv.min(0)) and np.array_equal(fv.max(0), pv.max(0))
+    assert len(pkg.parse_scene_file(path, triangle_cap=14)) == 14
