@@ -2,7 +2,7 @@
 """bench.py -- headline benchmark of the path-tracing hot path (contract: see the task statement).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--rng compat|philox]
-                    [--pipeline fused|wavefront] [--workload c1|c2|c3|c4]
+                    [--pipeline persist|loop|fused|wavefront] [--workload c1|c2|c3|c4]
 
 One "step" = one frame of the hot path: ptx_render (raygen/extend/shade/compact) + film resolve.
 N = 1 workload = BASELINE.json configs[1]: scenes/cbox_quads.obj, 1920x1080, 1024 spp, depth 16, reference
@@ -130,7 +130,7 @@ def run_ours(args, scene_path, w, h, spp, depth):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     rng_mode = pkg.RNG_PHILOX if args.rng == "philox" else pkg.RNG_XORWOW_COMPAT
-    pipeline = {"fused": pkg.PIPELINE_FUSED, "wavefront": pkg.PIPELINE_WAVEFRONT, "loop": pkg.PIPELINE_LOOP}[args.pipeline]
+    pipeline = {"fused": pkg.PIPELINE_FUSED, "wavefront": pkg.PIPELINE_WAVEFRONT, "loop": pkg.PIPELINE_LOOP, "persist": pkg.PIPELINE_PERSIST}[args.pipeline]
     shard_mode = pkg.SHARD_NONE if world == 1 else (pkg.SHARD_SAMPLES if rng_mode == pkg.RNG_PHILOX else pkg.SHARD_TILES)
 
     dist = torch = None
@@ -146,10 +146,12 @@ def run_ours(args, scene_path, w, h, spp, depth):
         from cuda_pathtracer_b200 import scenegen
         level = int(scene_path.rsplit("level", 1)[1])
         tris, mat, mats = scenegen.c3_scene(pkg.parse_scene_file(os.path.join(ROOT, "scenes", "cbox_quads.obj")), level)
-        scene = ctx.scene_from_triangles(tris, mat, mats, builder=0)
+        scene = ctx.scene_from_triangles(tris, mat, mats, builder=0, max_leaf=args.max_leaf)
         del tris, mat
     else:
         scene = ctx.load_scene(scene_path)
+        if args.max_leaf:
+            scene.rebuild(builder=0, max_leaf=args.max_leaf)
     scene_stats = scene.stats()
     cam = pkg.default_camera(w, h)
     film = ctx.create_film(w, h)
@@ -228,7 +230,13 @@ def run_ours(args, scene_path, w, h, spp, depth):
         # algorithmic bytes per segment of the dominant kernel
         loop = pipeline == pkg.PIPELINE_LOOP
         bytes_per_slot_launch = None
-        if loop:
+        if pipeline == pkg.PIPELINE_PERSIST:
+            # no path state in memory: per owned pixel and frame the compat kernel moves its id 4 + RNG state 24 + 24 + pixel sum 16 + 16 bytes;
+            # per path the counter-RNG kernel moves its pixel id 4 + three float atomics 12
+            per_item = 84.0 * (w * h / world) if rng_mode == pkg.RNG_XORWOW_COMPAT else 16.0 * st_t["paths"]
+            bytes_per_seg = per_item / max(st_t["segments"], 1)
+            kname, k_ms = "k_path_persist<rng> (one launch per frame: extend+shade+regenerate, all state in registers)", st_t["shade_ms"]
+        elif loop:
             # per live slot per launch: queue 4 + read A,B,C,E 64 + D 8 + write A,B,C,E 64 + D 8, compat adds RNG 24+24 and pixel sum 16+16
             bytes_per_slot_launch = 148 + (80 if rng_mode == pkg.RNG_XORWOW_COMPAT else 0)
             bytes_per_seg = bytes_per_slot_launch * st_t["slot_launches"] / max(st_t["segments"], 1)
@@ -292,10 +300,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rng", default="compat", choices=["compat", "philox"])
-    ap.add_argument("--pipeline", default="loop", choices=["loop", "fused", "wavefront"])
+    ap.add_argument("--pipeline", default="persist", choices=["persist", "loop", "fused", "wavefront"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override spp (reduced runs are NOT the headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--max-leaf", type=int, default=0, help="experiment: triangles per BVH8 leaf slot (1..3; 0 = library default)")
     args = ap.parse_args()
     scene, w, h, spp, depth = WORKLOADS[args.workload]
     if args.spp > 0:

@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(HERE, "libptx.so")
 
 RNG_XORWOW_COMPAT, RNG_PHILOX = 0, 1
 SHARD_NONE, SHARD_TILES, SHARD_SAMPLES = 0, 1, 2
-PIPELINE_WAVEFRONT, PIPELINE_FUSED, PIPELINE_LOOP = 0, 1, 2
+PIPELINE_WAVEFRONT, PIPELINE_FUSED, PIPELINE_LOOP, PIPELINE_PERSIST = 0, 1, 2, 3
 
 
 class PtxError(RuntimeError):

@@ -608,6 +608,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     FilmView fv = film->view();
     const bool fused = opts->pipeline == 1;
     const bool path_loop = opts->pipeline == 2;
+    const bool persist = opts->pipeline == 3;
     // bounces per path-loop launch: a compat-mode slot lives for >= spp segments, so long launches waste
     // little on lanes that die early; reserved[1] overrides (tuning / tests)
     int loop_iters = opts->reserved[1] > 0 ? opts->reserved[1] : 2 * std::min(std::max(rp.spp, 16), 256);
@@ -617,14 +618,21 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     unsigned long long live0 = (rp.spp > 0) ? std::min<unsigned long long>(rp.n_slots, rng_mode == PTX_RNG_PHILOX ? rp.total_paths : rp.n_slots) : 0ull;
     unsigned long long* hc = c->h_counters;
     for (int i = 0; i < CTR_COUNT; i++) hc[i] = 0;
-    hc[CTR_LIVE] = live0; hc[CTR_QLEN] = rp.n_slots; hc[CTR_NEXT_PATH] = rp.n_slots;
+    hc[CTR_LIVE] = live0; hc[CTR_QLEN] = rp.n_slots; hc[CTR_NEXT_PATH] = persist ? 0ull : rp.n_slots;
     PTX_CUDA(c, cudaMemcpyAsync(c->ws.counters, hc, sizeof(unsigned long long) * CTR_COUNT, cudaMemcpyHostToDevice, c->stream));
     PTX_CUDA(c, cudaStreamSynchronize(c->stream));      // hc is reused as the read-back buffer below
 
     ptx_render_stats st{};
     PTX_CUDA(c, cudaEventRecord(c->ev0, c->stream));
-    launch_raygen(c->stream, rng_mode, c->ws, fv, cv, rp);
-    st.kernel_launches++;
+    if (persist) {      // one launch for the whole frame: items are pulled from CTR_NEXT_PATH, nothing else to drive
+        launch_path_persist(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->reserved[2]);
+        PTX_CUDA(c, cudaGetLastError());
+        st.kernel_launches++;
+        live0 = 0;
+    } else {
+        launch_raygen(c->stream, rng_mode, c->ws, fv, cv, rp);
+        st.kernel_launches++;
+    }
 
     const int kBatch = 8;
     if (stage_timing && c->stage_events.size() < (size_t)kBatch * 3) {
@@ -686,6 +694,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     PTX_CUDA(c, cudaStreamSynchronize(c->stream));
     PTX_CUDA(c, cudaGetLastError());
     cudaEventElapsedTime(&st.render_ms, c->ev0, c->ev1);
+    if (persist) st.shade_ms = st.render_ms;               // the one kernel is the whole render
     st.segments = hc[CTR_SEGMENTS]; st.paths = hc[CTR_PATHS];
     st.other_ms = st.render_ms - st.extend_ms - st.shade_ms;
     st.node_visits = hc[CTR_NODE_VISITS]; st.tri_tests = hc[CTR_TRI_TESTS]; st.slot_launches = hc[CTR_SLOT_LAUNCHES];

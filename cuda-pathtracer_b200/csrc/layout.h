@@ -43,8 +43,8 @@ struct SceneView {
     const f32x4* prim_shade;
     const f32x4* materials;
     uint32_t n_nodes, n_tris, n_prims, n_mats;
-    // 0x4B000000 (2^23 as float bits), read by the kernels as a constant-bank operand of PRMT: see byte_to_float (traverse.h)
-    uint32_t byte_magic = 0x4B000000u;
+    // 0x3F800000 (1.0f), read by the kernels as a constant-bank operand of PRMT: see Traversal::step (traverse.h)
+    uint32_t byte_magic = 0x3F800000u;   // PRMT source for the byte -> float trick in traverse.h (kept out of the immediate field)
 };
 
 // Camera in the reference's Sensor terms (rendering/sensor.h:92-95): what get_ray needs.

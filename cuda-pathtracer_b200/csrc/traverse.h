@@ -113,9 +113,10 @@ struct Traversal {
         uint32_t octinv = 7u - oct;
         uint32_t octinv4 = octinv * 0x01010101u;
         uint32_t tg_x = 0, tg_y = 0;         // triangle group: base index, hit bits 23..0
-        // 0x4B000000 comes from the kernel parameter block (a constant-bank operand of PRMT): with the constant known at
+        // 0x3F800000 comes from the kernel parameter block (a constant-bank operand of PRMT): with the constant known at
         // compile time ptxas spends PRMT's single immediate on it and materialises every byte selector with a MOV
         const uint32_t magic = s.byte_magic;
+        (void)magic;
 
         if (ng_y > 0x00FFFFFFu) {
             uint32_t imask = ng_y & 0xFFu;
@@ -136,11 +137,46 @@ struct Traversal {
 
             uint32_t hitmask = 0;
 #if defined(__CUDA_ARCH__)
+            // Device form of the slab tests.  A quantised byte q becomes the float v = 1 + q 2^-15 with ONE PRMT
+            // (0x3F80qq00), and the "- 1" is folded into the additive term:  t = q s + o = v S + B  with S = 2^15 s,
+            // B = o - S.  B is rounded towards -inf for entry planes and +inf for exit planes, so the test stays
+            // conservative (the rounding is <= 2^-8 of one quantisation cell).  Entry and exit plane of an axis go
+            // through one packed FFMA2 (fma.rn.f32x2, sm_100): 3 issue slots per child instead of 6 FFMA + 6 FADD.
+            const float Sx = sx * 32768.0f, Sy = sy * 32768.0f, Sz = sz * 32768.0f;
+            const float2 S2x = make_float2(Sx, Sx), S2y = make_float2(Sy, Sy), S2z = make_float2(Sz, Sz);
+            const float2 B2x = make_float2(__fsub_rd(ox, Sx), __fsub_ru(ox, Sx));
+            const float2 B2y = make_float2(__fsub_rd(oy, Sy), __fsub_ru(oy, Sy));
+            const float2 B2z = make_float2(__fsub_rd(oz, Sz), __fsub_ru(oz, Sz));
 #pragma unroll
-#endif
             for (int half = 0; half < 2; half++) {
                 uint32_t meta4 = half ? n1.w : n1.z;
                 if (meta4 == 0u) continue;                 // four empty slots (small nodes fill the low slots first)
+                uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+                uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
+                uint32_t m4 = meta4 ^ (octinv4 & inner_mask4 & 0x07070707u);   // per byte: bits 7..5 unary count, 4..0 bit index
+                uint32_t qlox = half ? n2.y : n2.x, qloy = half ? n2.w : n2.z, qloz = half ? n3.y : n3.x;
+                uint32_t qhix = half ? n3.w : n3.z, qhiy = half ? n4.y : n4.x, qhiz = half ? n4.w : n4.z;
+                uint32_t nearx = d.x < 0.0f ? qhix : qlox, farx = d.x < 0.0f ? qlox : qhix;
+                uint32_t neary = d.y < 0.0f ? qhiy : qloy, fary = d.y < 0.0f ? qloy : qhiy;
+                uint32_t nearz = d.z < 0.0f ? qhiz : qloz, farz = d.z < 0.0f ? qloz : qhiz;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const uint32_t sel = 0x7604u + ((uint32_t)j << 4);       // {magic.3, magic.2, w.j, magic.0}
+                    float2 tx = __ffma2_rn(make_float2(__uint_as_float(__byte_perm(nearx, magic, sel)), __uint_as_float(__byte_perm(farx, magic, sel))), S2x, B2x);
+                    float2 ty = __ffma2_rn(make_float2(__uint_as_float(__byte_perm(neary, magic, sel)), __uint_as_float(__byte_perm(fary, magic, sel))), S2y, B2y);
+                    float2 tz = __ffma2_rn(make_float2(__uint_as_float(__byte_perm(nearz, magic, sel)), __uint_as_float(__byte_perm(farz, magic, sel))), S2z, B2z);
+                    float cmin = fmaxf(fmaxf(tx.x, ty.x), fmaxf(tz.x, t_min));
+                    float cmax = fminf(fminf(tx.y, ty.y), fminf(tz.y, closest));
+                    uint32_t mj = __byte_perm(m4, 0u, 0x4440u + (uint32_t)j);
+                    uint32_t bits;
+                    asm("shf.l.wrap.b32 %0, 0, %1, %2;" : "=r"(bits) : "r"(mj >> 5), "r"(mj));   // (mj >> 5) << (mj & 31)
+                    if (cmin <= cmax) hitmask |= bits;
+                }
+            }
+#else
+            for (int half = 0; half < 2; half++) {
+                uint32_t meta4 = half ? n1.w : n1.z;
+                if (meta4 == 0u) continue;
                 uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
                 uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
                 uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
@@ -150,21 +186,16 @@ struct Traversal {
                 uint32_t nearx = d.x < 0.0f ? qhix : qlox, farx = d.x < 0.0f ? qlox : qhix;
                 uint32_t neary = d.y < 0.0f ? qhiy : qloy, fary = d.y < 0.0f ? qloy : qhiy;
                 uint32_t nearz = d.z < 0.0f ? qhiz : qloz, farz = d.z < 0.0f ? qloz : qhiz;
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
                 for (int j = 0; j < 4; j++) {
-                    float tminx = byte_to_float(nearx, j, magic) * sx + ox;
-                    float tminy = byte_to_float(neary, j, magic) * sy + oy;
-                    float tminz = byte_to_float(nearz, j, magic) * sz + oz;
-                    float tmaxx = byte_to_float(farx, j, magic) * sx + ox;
-                    float tmaxy = byte_to_float(fary, j, magic) * sy + oy;
-                    float tmaxz = byte_to_float(farz, j, magic) * sz + oz;
+                    float tminx = (float)byte_of(nearx, j) * sx + ox, tmaxx = (float)byte_of(farx, j) * sx + ox;
+                    float tminy = (float)byte_of(neary, j) * sy + oy, tmaxy = (float)byte_of(fary, j) * sy + oy;
+                    float tminz = (float)byte_of(nearz, j) * sz + oz, tmaxz = (float)byte_of(farz, j) * sz + oz;
                     float cmin = fmaxf(fmaxf(tminx, tminy), fmaxf(tminz, t_min));
                     float cmax = fminf(fminf(tmaxx, tmaxy), fminf(tmaxz, closest));
                     if (cmin <= cmax) hitmask |= byte_of(child_bits4, j) << byte_of(bit_index4, j);
                 }
             }
+#endif
             ng_y = (hitmask & 0xFF000000u) | (n0.w >> 24);
             tg_y = hitmask & 0x00FFFFFFu;
             // (Software prefetch of the hit triangles / the nearest child with prefetch.global.L1 or .L2 was measured on C3

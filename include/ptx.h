@@ -160,7 +160,9 @@ typedef struct {
     int32_t rr_start_depth;   /* 0 => 3  (depth > 2, integrator.h:207) */
     float rr_cap;             /* 0 => 0.95 */
     int32_t pipeline;         /* 0 = wavefront (raygen/extend/shade/compact); 1 = fused bounce kernel (one launch per bounce);
-                                 2 = path loop (state in registers for reserved[1] bounces per launch, default min(max(spp,16),256)) */
+                                 2 = path loop (state in registers for reserved[1] bounces per launch, default min(max(spp,16),256));
+                                 3 = persistent path loop (one launch per frame; lanes pull pixels / paths from a counter, no path
+                                     state in memory).  reserved[2] = 4 selects the 64-register / 4-CTA-per-SM build of 2 and 3 */
     int32_t reserved[5];
 } ptx_render_opts;
 

@@ -102,12 +102,20 @@ void emu_philox(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
 }
 
 // the render loop of integrator.h:371-408 driven through shade.h / traverse.h (compat RNG), serial
+static TraceCounters g_render_ctr = {0, 0};     // node visits / triangle tests of the last emu_render (single-threaded test code)
+void emu_render_counters(uint64_t* out2) { out2[0] = g_render_ctr.nodes; out2[1] = g_render_ctr.tris; }
+int64_t emu_scene_nodes(const EmuScene* s, uint32_t* out, int64_t cap_nodes) {     // raw 80-byte nodes
+    int64_t n = (int64_t)s->view.n_nodes;
+    for (int64_t i = 0; i < n && i < cap_nodes; i++) memcpy(out + 20 * i, s->bvh.nodes.data() + kNodeQuads * i, 80);
+    return n;
+}
 void emu_render(const EmuScene* s, const CameraView* cam, int spp, int max_depth, uint64_t seed_base, float* linear,
                 uint8_t* rgb8, uint64_t* segments) {
     std::vector<uint32_t> tables((size_t)kXorwowJumps * kXorwowJumpWords);
     xorwow_build_jump_tables(tables.data());
     ShadeParams sp = {max_depth, 3, 0.95f};
     uint64_t seg = 0;
+    g_render_ctr = TraceCounters{0, 0};
     for (int y = 0; y < cam->height; y++)
         for (int x = 0; x < cam->width; x++) {
             int pix = y * cam->width + x;
@@ -123,7 +131,7 @@ void emu_render(const EmuScene* s, const CameraView* cam, int spp, int max_depth
                 vec3 L = mk3(0, 0, 0);
                 for (;;) {
                     float th; seg++;
-                    uint32_t tri = trace_closest<32, false>(s->view, pv.o, pv.d, 1e-4f, FLT_MAX, th, nullptr);
+                    uint32_t tri = trace_closest<32, true>(s->view, pv.o, pv.d, 1e-4f, FLT_MAX, th, &g_render_ctr);
                     uint32_t prim = tri == kMiss ? kMiss : f2u(s->view.tris[(size_t)tri * kTriQuads].w);
                     if (!shade_bounce(s->view, sp, pv, prim, th, rng, L)) break;
                 }
