@@ -391,8 +391,8 @@ __global__ void __launch_bounds__(kBlock, MINB) k_path_loop(WaveState ws, SceneV
 // ends (ncu r1h: lane efficiency 0.53 in the second launch of a 128-spp frame).  Lanes only idle in the
 // tail of the frame, when the counter has run dry.
 // ---------------------------------------------------------------------------------------------
-template <int RNG, int MINB>
-__global__ void __launch_bounds__(kBlock, MINB) k_path_persist(WaveState ws, SceneView scene, FilmView film, CameraView cam, RenderParams rp) {
+template <int RNG, int BLOCK, int MINB>
+__global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, SceneView scene, FilmView film, CameraView cam, RenderParams rp) {
     constexpr unsigned kFull = 0xFFFFFFFFu;
     const int lane = (int)(threadIdx.x & 31);
     const unsigned long long n_items = RNG == 0 ? (unsigned long long)rp.n_owned : rp.total_paths;
@@ -700,14 +700,19 @@ void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, con
                          const RenderParams& rp, int sm_count, int min_blocks) {
     if (rp.spp <= 0 || !rp.n_owned) return;
     const unsigned long long items = rng_mode == 0 ? (unsigned long long)rp.n_owned : rp.total_paths;
-    const int per_sm = min_blocks == 4 ? 4 : 3;
-    unsigned g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (items + kBlock - 1) / kBlock);
+    // resident CTAs: 3 x 256 threads at 80 registers (default), 4 x 256 at 64, or 7 x 128 at 72 (reserved[2] = 4 / 7)
+    const int per_sm = min_blocks == 4 ? 4 : (min_blocks == 7 ? 7 : 3);
+    const int block = min_blocks == 7 ? 128 : kBlock;
+    unsigned g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (items + block - 1) / block);
     if (per_sm == 4) {
-        if (rng_mode == 0) k_path_persist<0, 4><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
-        else k_path_persist<1, 4><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+        if (rng_mode == 0) k_path_persist<0, kBlock, 4><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+        else k_path_persist<1, kBlock, 4><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+    } else if (per_sm == 7) {
+        if (rng_mode == 0) k_path_persist<0, 128, 7><<<g, 128, 0, st>>>(ws, scene, film, cam, rp);
+        else k_path_persist<1, 128, 7><<<g, 128, 0, st>>>(ws, scene, film, cam, rp);
     } else {
-        if (rng_mode == 0) k_path_persist<0, 3><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
-        else k_path_persist<1, 3><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+        if (rng_mode == 0) k_path_persist<0, kBlock, 3><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+        else k_path_persist<1, kBlock, 3><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
     }
 }
 void launch_compact(cudaStream_t st, const WaveState& ws, int q, uint32_t qlen_bound, uint32_t* scratch) {
