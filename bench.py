@@ -170,7 +170,7 @@ def run_ours(args, scene_path, w, h, spp, depth):
             torch.cuda.synchronize()
 
     kw = dict(spp=spp, max_depth=depth, rng_mode=rng_mode, pipeline=pipeline, shard_mode=shard_mode, shard_rank=rank, shard_world=world,
-              loop_min_blocks=args.min_blocks)
+              loop_min_blocks=args.min_blocks, chunks=args.chunks)
 
     def step(host_output, stage_timing=False):
         """One frame.  host_output=False: result stays in HBM (device resolve). True: RGB8 image copied to the host."""
@@ -306,6 +306,7 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override spp (reduced runs are NOT the headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--min-blocks", type=int, default=0, help="experiment: occupancy variant of the path-loop kernels (0 = 3x256 threads/SM, 4 = 4x256, 7 = 7x128)")
+    ap.add_argument("--chunks", type=int, default=0, help="experiment: work items per pixel of the persistent kernel, compat RNG (0 = default 6, 1 = none)")
     ap.add_argument("--max-leaf", type=int, default=0, help="experiment: triangles per BVH8 leaf slot (1..3; 0 = library default)")
     args = ap.parse_args()
     scene, w, h, spp, depth = WORKLOADS[args.workload]

@@ -37,6 +37,7 @@ struct ptx_ctx {
     // wavefront state (grown on demand, reused across renders)
     WaveState ws{};
     uint32_t* d_scratch = nullptr; size_t scratch_words = 0;
+    uint32_t pixmap_capacity = 0, progress_capacity = 0;   // entries allocated in ws.slot_pixel / ws.progress
     unsigned long long* h_counters = nullptr;   // pinned
     int slot_key[5] = {-1, -1, -1, -1, -1};     // (w, h, shard_mode, rank, world) the slot map was built for
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, tev0 = nullptr, tev1 = nullptr;
@@ -126,7 +127,7 @@ void ptx_ctx_destroy(ptx_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     cudaFree(c->ws.A); cudaFree(c->ws.B); cudaFree(c->ws.C); cudaFree(c->ws.D); cudaFree(c->ws.E);
-    cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]); cudaFree(c->ws.slot_pixel); cudaFree(c->ws.counters);
+    cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]); cudaFree(c->ws.slot_pixel); cudaFree(c->ws.progress); cudaFree(c->ws.counters);
     cudaFree(c->d_scratch); cudaFree(c->d_jump);
     cudaFreeHost(c->h_counters);
     for (auto ev : c->stage_events) cudaEventDestroy(ev);
@@ -533,9 +534,9 @@ int ensure_wave_capacity(ptx_ctx* c, uint32_t slots, uint32_t owned) {
     uint32_t need = std::max(slots, owned);
     if (need > c->ws.capacity) {
         cudaFree(c->ws.A); cudaFree(c->ws.B); cudaFree(c->ws.C); cudaFree(c->ws.D); cudaFree(c->ws.E);
-        cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]); cudaFree(c->ws.slot_pixel);
-        c->ws.A = c->ws.B = c->ws.C = c->ws.E = nullptr; c->ws.D = nullptr; c->ws.queue[0] = c->ws.queue[1] = c->ws.slot_pixel = nullptr;
-        c->ws.capacity = 0; c->slot_key[0] = -1;
+        cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]);
+        c->ws.A = c->ws.B = c->ws.C = c->ws.E = nullptr; c->ws.D = nullptr; c->ws.queue[0] = c->ws.queue[1] = nullptr;
+        c->ws.capacity = 0;
         size_t n = need;
         PTX_CUDA(c, cudaMalloc(&c->ws.A, n * sizeof(float4)));
         PTX_CUDA(c, cudaMalloc(&c->ws.B, n * sizeof(float4)));
@@ -544,7 +545,6 @@ int ensure_wave_capacity(ptx_ctx* c, uint32_t slots, uint32_t owned) {
         PTX_CUDA(c, cudaMalloc(&c->ws.D, n * sizeof(uint2)));
         PTX_CUDA(c, cudaMalloc(&c->ws.queue[0], n * sizeof(uint32_t)));
         PTX_CUDA(c, cudaMalloc(&c->ws.queue[1], n * sizeof(uint32_t)));
-        PTX_CUDA(c, cudaMalloc(&c->ws.slot_pixel, n * sizeof(uint32_t)));
         c->ws.capacity = need;
     }
     size_t words = (size_t)need / 1024 + 8;
@@ -552,6 +552,23 @@ int ensure_wave_capacity(ptx_ctx* c, uint32_t slots, uint32_t owned) {
         cudaFree(c->d_scratch); c->d_scratch = nullptr; c->scratch_words = 0;
         PTX_CUDA(c, cudaMalloc(&c->d_scratch, words * sizeof(uint32_t)));
         c->scratch_words = words;
+    }
+    return PTX_OK;
+}
+
+// slot -> pixel map and per-pixel chunk progress: all the persistent kernel needs besides the film
+int ensure_pixmap(ptx_ctx* c, uint32_t owned, uint32_t film_pixels) {
+    if (owned > c->pixmap_capacity) {
+        cudaFree(c->ws.slot_pixel);
+        c->ws.slot_pixel = nullptr; c->pixmap_capacity = 0; c->slot_key[0] = -1;
+        PTX_CUDA(c, cudaMalloc(&c->ws.slot_pixel, (size_t)owned * sizeof(uint32_t)));
+        c->pixmap_capacity = owned;
+    }
+    if (film_pixels > c->progress_capacity) {
+        cudaFree(c->ws.progress);
+        c->ws.progress = nullptr; c->progress_capacity = 0;
+        PTX_CUDA(c, cudaMalloc(&c->ws.progress, (size_t)film_pixels * sizeof(uint32_t)));
+        c->progress_capacity = film_pixels;
     }
     return PTX_OK;
 }
@@ -595,8 +612,19 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     rp.total_paths = (unsigned long long)rp.n_owned * (unsigned long long)spp_local;
     rp.n_slots = rng_mode == PTX_RNG_XORWOW_COMPAT ? rp.n_owned : (uint32_t)std::min<unsigned long long>(rp.total_paths, kPhiloxPool);
 
-    int rc = ensure_wave_capacity(c, rp.n_slots, rp.n_owned);
+    const bool persist = opts->pipeline == 3;
+    int rc = ensure_pixmap(c, rp.n_owned, persist ? (uint32_t)w * (uint32_t)h : 0u);
+    if (rc == PTX_OK && !persist) rc = ensure_wave_capacity(c, rp.n_slots, rp.n_owned);
     if (rc != PTX_OK) return rc;
+    // compat RNG: a pixel's samples form one sequential chain; the persistent kernel splits it into n_chunks work items
+    // (1/2, 1/4, ... of the samples, the pixel's RNG state and running sum handed on through the film between them), so
+    // the tail of the frame is bounded by the small last chunk instead of a whole pixel.  reserved[3] overrides the count.
+    {
+        int log2spp = 0;
+        while ((rp.spp >> (log2spp + 1)) > 0) log2spp++;
+        int want = opts->reserved[3] > 0 ? opts->reserved[3] : 6;
+        rp.n_chunks = rp.spp > 0 ? std::min(want, log2spp + 1) : 1;
+    }
     int key[5] = {w, h, shard_mode, rank, world};
     if (memcmp(key, c->slot_key, sizeof key) != 0) {
         launch_slot_pixels(c->stream, c->ws.slot_pixel, w, h, shard_mode, rank, world, rp.n_owned);
@@ -608,7 +636,6 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     FilmView fv = film->view();
     const bool fused = opts->pipeline == 1;
     const bool path_loop = opts->pipeline == 2;
-    const bool persist = opts->pipeline == 3;
     // bounces per path-loop launch: a compat-mode slot lives for >= spp segments, so long launches waste
     // little on lanes that die early; reserved[1] overrides (tuning / tests)
     int loop_iters = opts->reserved[1] > 0 ? opts->reserved[1] : 2 * std::min(std::max(rp.spp, 16), 256);
@@ -625,6 +652,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     ptx_render_stats st{};
     PTX_CUDA(c, cudaEventRecord(c->ev0, c->stream));
     if (persist) {      // one launch for the whole frame: items are pulled from CTR_NEXT_PATH, nothing else to drive
+        if (rng_mode == PTX_RNG_XORWOW_COMPAT && rp.n_owned) PTX_CUDA(c, cudaMemsetAsync(c->ws.progress, 0, (size_t)w * h * sizeof(uint32_t), c->stream));
         launch_path_persist(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->reserved[2]);
         PTX_CUDA(c, cudaGetLastError());
         st.kernel_launches++;

@@ -395,22 +395,27 @@ template <int RNG, int BLOCK, int MINB>
 __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, SceneView scene, FilmView film, CameraView cam, RenderParams rp) {
     constexpr unsigned kFull = 0xFFFFFFFFu;
     const int lane = (int)(threadIdx.x & 31);
-    const unsigned long long n_items = RNG == 0 ? (unsigned long long)rp.n_owned : rp.total_paths;
+    // compat: item = (chunk c, owned pixel k), chunk-major, so chunk c of a pixel is handed out long after chunk c-1.
+    // Chunk c covers samples [spp - (spp >> c), spp - (spp >> (c+1))), the last one runs to spp: halves, then quarters, ...
+    // so most samples pay no hand-off and the frame's tail is bounded by the small last chunks.
+    const uint32_t n_chunks = RNG == 0 ? (uint32_t)rp.n_chunks : 0u;
+    const unsigned long long n_items = RNG == 0 ? (unsigned long long)rp.n_owned * n_chunks : rp.total_paths;
     uint32_t nseg = 0, npaths = 0;
     PathVertex pv;
     pv.o = pv.d = pv.beta = v3(0.f, 0.f, 0.f); pv.depth = 0;
     vec3 L = v3(0.f, 0.f, 0.f), acc = v3(0.f, 0.f, 0.f);
     uint32_t pixel = 0, sample = 0;                     // compat: samples finished; philox: global sample index
+    uint32_t chunk = 0;                                 // compat: chunk number of the item in flight
     XorwowRng xr; xr.st = Xorwow{0u, 0u, 0u, 0u, 0u, 0u};
     PhiloxRng pr; pr.blk = Philox4{0u, 0u, 0u, 0u}; pr.lane = 0;
     float fx = 0.f, fy = 0.f;
-    bool alive = false, dry = rp.spp <= 0;
+    bool alive = false, pending = false, dry = rp.spp <= 0;
     Traversal tr;
     TravStack<24> stk;
     tr.begin(pv.d, FLT_MAX);
     for (;;) {
-        // ---- fetch: every lane without a path asks for an item; one atomic per warp
-        const bool want = !alive && !dry;
+        // ---- fetch: every lane without work asks for an item; one atomic per warp
+        const bool want = !alive && !pending && !dry;
         const unsigned need = __ballot_sync(kFull, want);
         if (need) {
             unsigned long long base = 0;
@@ -420,30 +425,51 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
             if (want) {
                 const unsigned long long item = base + (unsigned long long)__popc(need & ((1u << lane) - 1u));
                 if (item < n_items) {
-                    alive = true;
-                    float ju, jv;
                     if (RNG == 0) {
-                        pixel = ws.slot_pixel[(uint32_t)item];
-                        sample = 0;
-                        uint4 ra = film.rngA[pixel]; uint2 rb = film.rngB[pixel];
-                        xr.st = Xorwow{ra.x, ra.y, ra.z, ra.w, rb.x, rb.y};
-                        float4 f = film.accum[pixel];
-                        acc = v3(f.x, f.y, f.z);
-                        ju = xr.next(); jv = xr.next();
+                        chunk = (uint32_t)(item / rp.n_owned);
+                        pixel = ws.slot_pixel[(uint32_t)(item % rp.n_owned)];
+                        pending = true;
                     } else {
                         pixel = ws.slot_pixel[(uint32_t)(item % rp.n_owned)];
                         sample = (uint32_t)(item / rp.n_owned) + rp.sample_begin;
                         pr.seek(((unsigned long long)sample << 32) | pixel, 0u, rp.seed);
-                        ju = pr.next(); jv = pr.next();
+                        float ju = pr.next(), jv = pr.next();
+                        start_path_xy(cam, (float)(int)(pixel % (uint32_t)cam.width), (float)(int)(pixel / (uint32_t)cam.width), ju, jv, pv);
+                        L = v3(0.f, 0.f, 0.f);
+                        tr.begin(pv.d, FLT_MAX);
+                        alive = true;
                     }
-                    fx = (float)(int)(pixel % (uint32_t)cam.width); fy = (float)(int)(pixel / (uint32_t)cam.width);
-                    start_path_xy(cam, fx, fy, ju, jv, pv);
-                    L = v3(0.f, 0.f, 0.f);
-                    tr.begin(pv.d, FLT_MAX);
                 } else dry = true;
             }
         }
-        if (!__any_sync(kFull, alive)) break;
+        // ---- compat: start the chunk once its predecessor has been committed (almost always at once; a lane that has to
+        //      wait just retries next iteration, so lanes of one warp can never block each other)
+        if (RNG == 0 && pending) {
+            bool ready = chunk == 0u;
+            if (!ready) {
+                uint32_t seen;                                                // relaxed gpu-scope load (served by L2)
+                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(ws.progress + pixel) : "memory");
+                ready = seen == chunk;
+            }
+            if (ready) {
+                // The loads below are issued only after the flag value is known (control dependency) and go to L2 (.cg), where
+                // the previous owner's release made its stores visible.  No acquire fence on purpose: a gpu-scope fence
+                // invalidates the SM's whole L1 (CCTL.IVALL), which holds the BVH -- measured -20 % on C2.
+                uint4 ra; uint2 rb; float4 f;
+                if (chunk == 0u) { ra = film.rngA[pixel]; rb = film.rngB[pixel]; f = film.accum[pixel]; }
+                else { ra = __ldcg(film.rngA + pixel); rb = __ldcg(film.rngB + pixel); f = __ldcg(film.accum + pixel); }   // L2: L1 may hold a stale line
+                xr.st = Xorwow{ra.x, ra.y, ra.z, ra.w, rb.x, rb.y};
+                acc = v3(f.x, f.y, f.z);
+                sample = (uint32_t)rp.spp - ((uint32_t)rp.spp >> chunk);
+                fx = (float)(int)(pixel % (uint32_t)cam.width); fy = (float)(int)(pixel / (uint32_t)cam.width);
+                float ju = xr.next(), jv = xr.next();
+                start_path_xy(cam, fx, fy, ju, jv, pv);
+                L = v3(0.f, 0.f, 0.f);
+                tr.begin(pv.d, FLT_MAX);
+                pending = false; alive = true;
+            }
+        }
+        if (!__any_sync(kFull, alive || pending)) break;
         // ---- extend: one wide-node visit (+ its triangles) per lane
         bool done = false;
         if (alive) done = tr.template step<false, 24>(scene, stk, pv.o, pv.d, 1e-4f, nullptr);
@@ -467,7 +493,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
                 acc = acc + L;
                 L = v3(0.f, 0.f, 0.f);
                 sample++;
-                if (sample < (uint32_t)rp.spp) {
+                if (sample < (chunk + 1u == n_chunks ? (uint32_t)rp.spp : (uint32_t)rp.spp - ((uint32_t)rp.spp >> (chunk + 1u)))) {
                     float ju = xr.next(), jv = xr.next();
                     start_path_xy(cam, fx, fy, ju, jv, pv);
                     cont = true;
@@ -475,6 +501,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
                     film.rngA[pixel] = make_uint4(xr.st.v0, xr.st.v1, xr.st.v2, xr.st.v3);
                     film.rngB[pixel] = make_uint2(xr.st.v4, xr.st.d);
                     film.accum[pixel] = make_float4(acc.x, acc.y, acc.z, 0.f);
+                    if (chunk + 1u < n_chunks)                                // release: hand the pixel to whoever holds its next chunk
+                        asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(ws.progress + pixel), "r"(chunk + 1u) : "memory");
                     alive = false;
                 }
             } else {

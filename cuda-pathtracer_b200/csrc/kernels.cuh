@@ -32,6 +32,7 @@ struct WaveState {
     uint2* D;                 // philox mode: { pixel, sample index }; compat mode: { pixel, samples done }
     uint32_t* queue[2];       // live slot indices (ping-pong for compaction)
     uint32_t* slot_pixel;     // slot -> pixel for the pixels this rank owns
+    uint32_t* progress;       // persistent kernel, compat RNG: sample chunks finished, per pixel of the film (zeroed per frame)
     // device counters (one 64-byte block): see CounterBlock
     unsigned long long* counters;
     uint32_t capacity;        // slots allocated
@@ -54,6 +55,7 @@ struct RenderParams {
     uint32_t n_owned;         // pixels owned by this rank
     unsigned long long total_paths;   // philox: n_owned * spp
     uint32_t sample_begin;    // philox sample-range sharding: first global sample index
+    int n_chunks;             // persistent kernel, compat RNG: work items per pixel (geometric sample ranges, see k_path_persist)
     unsigned long long seed;
 };
 

@@ -162,7 +162,10 @@ typedef struct {
     int32_t pipeline;         /* 0 = wavefront (raygen/extend/shade/compact); 1 = fused bounce kernel (one launch per bounce);
                                  2 = path loop (state in registers for reserved[1] bounces per launch, default min(max(spp,16),256));
                                  3 = persistent path loop (one launch per frame; lanes pull pixels / paths from a counter, no path
-                                     state in memory).  reserved[2] = 4 selects the 64-register / 4-CTA-per-SM build of 2 and 3 */
+                                     state in memory; with the compat RNG a pixel's samples are split into reserved[3] work items,
+                                     default 6: 1/2, 1/4, ... 1/32, 1/32 of spp, handed from lane to lane through the film,
+                                     so the frame's tail is one small chunk, not one pixel).
+                                     reserved[2] = 4 / 7 select the 4 x 256 / 7 x 128 threads-per-SM builds of 2 and 3 */
     int32_t reserved[5];
 } ptx_render_opts;
 
