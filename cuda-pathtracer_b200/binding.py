@@ -77,7 +77,7 @@ EXPORTS = [
     "ptx_scene_load", "ptx_parse_scene_file", "ptx_free_primitives", "ptx_scene_from_primitives", "ptx_scene_from_triangles",
     "ptx_scene_build_accel", "ptx_scene_stats_get", "ptx_scene_get_primitives", "ptx_scene_destroy",
     "ptx_camera_set", "ptx_camera_update", "ptx_camera_orbit", "ptx_camera_default",
-    "ptx_film_create", "ptx_film_reset", "ptx_film_clear", "ptx_film_resolve_rgb8", "ptx_film_read_linear", "ptx_film_write",
+    "ptx_film_create", "ptx_film_reset", "ptx_film_clear", "ptx_film_resolve_rgb8", "ptx_film_read_linear", "ptx_film_write", "ptx_write_png_rgb8",
     "ptx_film_device_buffer", "ptx_film_set_sample_count", "ptx_film_destroy",
     "ptx_shard_pixel_count", "ptx_shard_owned_pixels", "ptx_shard_sample_range",
     "ptx_render", "ptx_render_stats_get", "ptx_trace_primary_ids", "ptx_trace_rays", "ptx_film_rng_state",
@@ -110,6 +110,7 @@ def lib():
         L.ptx_scene_load.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_void_p]
         L.ptx_parse_scene_file.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ptx_film_write.argtypes = [C.c_void_p, C.c_char_p]
+        L.ptx_write_png_rgb8.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
         L.ptx_film_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.ptx_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ptx_trace_primary_ids.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
@@ -147,6 +148,13 @@ def parse_scene_file(path, convert_quads=False, subdivision=0, mirror_from_mtl=F
         return np.frombuffer(buf, dtype=PRIM_DTYPE).copy()
     finally:
         lib().ptx_free_primitives(p)
+
+
+def write_png_rgb8(path, rgb, flip_y=False):
+    """Host-only PNG writer (ptx_write_png_rgb8): rgb = (h, w, 3) uint8."""
+    rgb = np.ascontiguousarray(rgb, dtype=np.uint8)
+    h, w = rgb.shape[:2]
+    _check(lib().ptx_write_png_rgb8(os.fspath(path).encode(), int(w), int(h), _ptr(rgb), int(flip_y)))
 
 
 def shard_owned_pixels(width, height, shard_mode, rank, world):

@@ -17,6 +17,7 @@
 #include "bvh_gpu.h"
 #include "bvh_host.h"
 #include "kernels.cuh"
+#include "image_io.h"
 #include "loader.h"
 #include "rng.h"
 #include "scene_pack.h"
@@ -474,6 +475,13 @@ int ptx_film_write(ptx_film* f, const char* path) {
         if (!(fp = fopen(path, "wb"))) return fail(f->ctx, PTX_ERR_IO, "cannot write " + p);
         fprintf(fp, "PF\n%d %d\n-1.0\n", f->w, f->h);                  // PFM rows run bottom to top, like the film
         fwrite(lin.data(), sizeof(float), lin.size(), fp);
+    } else if (has_suffix(p, ".png")) {
+        std::vector<uint8_t> img(npix * 3);
+        int rc = ptx_film_resolve_rgb8(f, img.data(), 0, 0);             // film rows run bottom to top (the reference's h_image) ...
+        if (rc != PTX_OK) return rc;
+        if (!write_png_rgb8(path, f->w, f->h, img.data(), true))         // ... and the writer flips, like stbi_flip_vertically_on_write(1)
+            return fail(f->ctx, PTX_ERR_IO, "cannot write " + p);
+        return PTX_OK;
     } else {
         std::vector<uint8_t> img(npix * 3);
         int rc = ptx_film_resolve_rgb8(f, img.data(), 0, 1);             // vertical flip like the PNG export (ui_windows.h:205-207)
@@ -483,6 +491,12 @@ int ptx_film_write(ptx_film* f, const char* path) {
         fwrite(img.data(), 1, img.size(), fp);
     }
     fclose(fp);
+    return PTX_OK;
+}
+
+int ptx_write_png_rgb8(const char* path, int width, int height, const uint8_t* rgb_host, int flip_y) {
+    if (!path || !rgb_host || width <= 0 || height <= 0) return fail(nullptr, PTX_ERR_INVALID, "ptx_write_png_rgb8: bad argument");
+    if (!write_png_rgb8(path, width, height, rgb_host, flip_y != 0)) return fail(nullptr, PTX_ERR_IO, std::string("cannot write ") + path);
     return PTX_OK;
 }
 

@@ -138,7 +138,11 @@ int ptx_film_clear(ptx_film* film);                                         /* c
  * dst_is_device with dst == NULL resolves into the film's own device buffer (result stays in HBM). */
 int ptx_film_resolve_rgb8(ptx_film* film, uint8_t* dst, int dst_is_device, int flip_y);
 int ptx_film_read_linear(ptx_film* film, float* rgb_host);                  /* w*h*3 pre-tonemap means */
-int ptx_film_write(ptx_film* film, const char* path);                        /* .ppm (RGB8, top row first) or .pfm */
+int ptx_film_write(ptx_film* film, const char* path);                        /* by extension: .png / .ppm (RGB8, top row first) or
+                                                                                .pfm (linear radiance); replaces "Save PNG", ui_windows.h:195-210 */
+/* host-only PNG writer for an RGB8 image the caller already holds (e.g. the reference's h_image, flip_y = 1 like
+ * stbi_flip_vertically_on_write(1) + stbi_write_png, ui_windows.h:205-208).  Needs no GPU. */
+int ptx_write_png_rgb8(const char* path, int width, int height, const uint8_t* rgb_host, int flip_y);
 /* raw accumulation buffer (float4 per pixel: sum r,g,b + sample count) for NCCL film combine */
 int ptx_film_device_buffer(ptx_film* film, void** dev_ptr, size_t* bytes);
 int ptx_film_set_sample_count(ptx_film* film, float spp_total);             /* after an external reduce */

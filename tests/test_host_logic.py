@@ -293,3 +293,36 @@ def test_pbrt_triangle_cap_proxy(pkg):
     fv, pv = full["v"][:, :3].reshape(-1, 3), proxy["v"][:, :3].reshape(-1, 3)
     assert np.array_equal(fv.min(0), pv.min(0)) and np.array_equal(fv.max(0), pv.max(0))
     assert len(pkg.parse_scene_file(path, triangle_cap=14)) == 14
+
+
+def _decode_png(path):
+    """Minimal PNG reader for the test (8-bit RGB, filter 0 only): checks signature, chunk CRCs and the zlib stream."""
+    import struct, zlib
+    b = open(path, "rb").read()
+    assert b[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, chunks = 8, []
+    while pos < len(b):
+        n, typ = struct.unpack(">I4s", b[pos:pos + 8])
+        data = b[pos + 8:pos + 8 + n]
+        (crc,) = struct.unpack(">I", b[pos + 8 + n:pos + 12 + n])
+        assert crc == zlib.crc32(typ + data) & 0xFFFFFFFF
+        chunks.append((typ, data)); pos += 12 + n
+    assert [c[0] for c in chunks] == [b"IHDR", b"IDAT", b"IEND"]
+    w, h, depth, ctype, comp, flt, inter = struct.unpack(">IIBBBBB", chunks[0][1])
+    assert (depth, ctype, comp, flt, inter) == (8, 2, 0, 0, 0)
+    raw = np.frombuffer(zlib.decompress(chunks[1][1]), np.uint8).reshape(h, 1 + 3 * w)
+    assert (raw[:, 0] == 0).all()
+    return raw[:, 1:].reshape(h, w, 3)
+
+
+@pytest.mark.parametrize("w,h", [(1, 1), (7, 5), (301, 233)])
+def test_png_writer_roundtrip(pkg, tmp_path, w, h):
+    """The film's PNG export ("Save PNG", ui_windows.h:195-210): valid chunks / CRC / Adler, pixels intact, and flip_y
+    writing the rows bottom-up like stbi_flip_vertically_on_write(1).  (301 x 233 x 3 spans several stored blocks.)"""
+    img = np.random.default_rng(w * h).integers(0, 256, (h, w, 3), dtype=np.uint8)
+    pkg.write_png_rgb8(tmp_path / "a.png", img)
+    assert np.array_equal(_decode_png(tmp_path / "a.png"), img)
+    pkg.write_png_rgb8(tmp_path / "b.png", img, flip_y=True)
+    assert np.array_equal(_decode_png(tmp_path / "b.png"), img[::-1])
+    with pytest.raises(pkg.PtxError):
+        pkg.write_png_rgb8(tmp_path / "nodir" / "c.png", img)
