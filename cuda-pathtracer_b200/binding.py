@@ -80,7 +80,7 @@ EXPORTS = [
     "ptx_film_create", "ptx_film_reset", "ptx_film_clear", "ptx_film_resolve_rgb8", "ptx_film_read_linear", "ptx_film_write", "ptx_write_png_rgb8",
     "ptx_film_device_buffer", "ptx_film_set_sample_count", "ptx_film_destroy",
     "ptx_shard_pixel_count", "ptx_shard_owned_pixels", "ptx_shard_sample_range",
-    "ptx_render", "ptx_render_stats_get", "ptx_trace_primary_ids", "ptx_trace_rays", "ptx_film_rng_state",
+    "ptx_render", "ptx_render_stats_get", "ptx_trace_primary_ids", "ptx_trace_rays", "ptx_trace_occluded", "ptx_render_visibility", "ptx_film_rng_state",
 ]
 
 _lib = None
@@ -101,6 +101,8 @@ def lib():
             getattr(L, name).argtypes = [C.c_void_p]
         L.ptx_film_set_sample_count.argtypes = [C.c_void_p, C.c_float]
         L.ptx_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_float, C.c_void_p, C.c_void_p]
+        L.ptx_trace_occluded.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.ptx_render_visibility.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.ptx_film_reset.argtypes = [C.c_void_p, C.c_uint64]
         L.ptx_film_rng_state.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]
         L.ptx_scene_from_primitives.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
@@ -292,6 +294,20 @@ class Context:
         ts = np.empty(len(rays), np.float32)
         _check(lib().ptx_trace_rays(self._h, scene._h, _ptr(rays), len(rays), C.c_float(t_min), _ptr(ids), _ptr(ts)), self._h)
         return ids, ts
+
+    def trace_occluded(self, scene, segs):
+        """Scene::occluded(from, to) for (n, 6) float32 segments -> uint8[n]."""
+        segs = np.ascontiguousarray(segs, dtype=np.float32).reshape(-1, 6)
+        out = np.empty(len(segs), np.uint8)
+        _check(lib().ptx_trace_occluded(self._h, scene._h, _ptr(segs), len(segs), _ptr(out)), self._h)
+        return out
+
+    def render_visibility(self, scene, camera, film, spp, radiosity=None):
+        """render_radiosity view: RGB8 (h, w, 3), row 0 = bottom; radiosity = (n_primitives, 3) float32 or None."""
+        rad = None if radiosity is None else np.ascontiguousarray(radiosity, dtype=np.float32)
+        img = np.empty((film.height, film.width, 3), np.uint8)
+        _check(lib().ptx_render_visibility(self._h, scene._h, C.byref(camera), film._h, int(spp), None if rad is None else _ptr(rad), _ptr(img)), self._h)
+        return img
 
 
 class Scene:

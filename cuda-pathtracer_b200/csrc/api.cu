@@ -820,4 +820,40 @@ int ptx_trace_rays(ptx_ctx* c, const ptx_scene* scene, const float* rays_host, s
     return PTX_OK;
 }
 
+int ptx_trace_occluded(ptx_ctx* c, const ptx_scene* scene, const float* segs_host, size_t n, uint8_t* occluded_host) {
+    if (!c || !scene || (n && (!segs_host || !occluded_host))) return fail(c, PTX_ERR_INVALID, "ptx_trace_occluded: bad argument");
+    if (!n) return PTX_OK;
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    float* d_segs = nullptr; uint8_t* d_out = nullptr;
+    cudaError_t e = cudaMalloc(&d_segs, n * 24);
+    if (e == cudaSuccess) e = cudaMalloc(&d_out, n);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_segs, segs_host, n * 24, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) { launch_occluded(c->stream, scene->view, d_segs, n, d_out); e = cudaGetLastError(); }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(occluded_host, d_out, n, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d_segs); cudaFree(d_out);
+    if (e != cudaSuccess) return cuda_fail(c, e, "ptx_trace_occluded");
+    return PTX_OK;
+}
+
+int ptx_render_visibility(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_film* film, int spp, const float* radiosity_host,
+                          uint8_t* rgb8_host) {
+    if (!c || !scene || !cam || !film || !rgb8_host || spp <= 0) return fail(c, PTX_ERR_INVALID, "ptx_render_visibility: bad argument");
+    if (scene->ctx != c || film->ctx != c) return fail(c, PTX_ERR_INVALID, "ptx_render_visibility: scene/film belong to another context");
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    const size_t npix = (size_t)film->w * film->h, nprim = scene->view.n_prims;
+    float* d_rad = nullptr; uint8_t* d_img = nullptr;
+    cudaError_t e = cudaMalloc(&d_img, npix * 3);
+    if (e == cudaSuccess && radiosity_host && nprim) {
+        e = cudaMalloc(&d_rad, nprim * 12);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_rad, radiosity_host, nprim * 12, cudaMemcpyHostToDevice, c->stream);
+    }
+    if (e == cudaSuccess) { launch_visibility(c->stream, scene->view, film->view(), camera_view(*cam, film->w, film->h), spp, d_rad, d_img); e = cudaGetLastError(); }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(rgb8_host, d_img, npix * 3, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d_rad); cudaFree(d_img);
+    if (e != cudaSuccess) return cuda_fail(c, e, "ptx_render_visibility");
+    return PTX_OK;
+}
+
 }  // extern "C"

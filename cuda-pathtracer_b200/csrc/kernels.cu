@@ -659,6 +659,54 @@ __global__ void __launch_bounds__(kBlock) k_trace_rays(SceneView scene, const fl
     tout[i] = tri == kMiss ? -1.0f : t;
 }
 
+// Scene::occluded(from, to) (scene.h:132-149): the shadow ray starts 1e-4 along the normalised direction, is normalised
+// again by the Ray ctor, and any hit in [1e-4, dist - 1e-4) occludes.
+__global__ void __launch_bounds__(kBlock) k_occluded(SceneView scene, const float* __restrict__ segs, size_t n, uint8_t* out) {
+    size_t i = (size_t)blockIdx.x * kBlock + threadIdx.x;
+    if (i >= n) return;
+    vec3 from = v3(segs[6 * i], segs[6 * i + 1], segs[6 * i + 2]);
+    vec3 dir = v3(segs[6 * i + 3], segs[6 * i + 4], segs[6 * i + 5]) - from;
+    float dist = length(dir);
+    dir = div_scalar(dir, dist);
+    vec3 o = from + 1e-4f * dir;
+    vec3 d = unit(dir);
+    out[i] = trace_any<24>(scene, o, d, 1e-4f, dist - 1e-4f) ? 1 : 0;
+}
+
+// render_radiosity (integrator.h:460-504): per pixel, spp jittered primary rays; colour = Le + the radiosity stored for
+// the hit primitive (input of this kernel: the solver that produces it is out of scope); sqrt "gamma", clamp to 1.
+// Continues and writes back the pixel's XORWOW stream like the reference kernel.
+__global__ void __launch_bounds__(kBlock) k_visibility(SceneView scene, FilmView film, CameraView cam, int spp, const float* __restrict__ radiosity,
+                                                       uint8_t* rgb8) {
+    uint32_t p = blockIdx.x * kBlock + threadIdx.x;
+    if (p >= (uint32_t)cam.width * (uint32_t)cam.height) return;
+    float fx = (float)(int)(p % (uint32_t)cam.width), fy = (float)(int)(p / (uint32_t)cam.width);
+    uint4 ra = film.rngA[p]; uint2 rb = film.rngB[p];
+    XorwowRng xr; xr.st = Xorwow{ra.x, ra.y, ra.z, ra.w, rb.x, rb.y};
+    vec3 color = v3(0.f, 0.f, 0.f);
+    for (int s = 0; s < spp; s++) {
+        float u = (fx + xr.next()) / (float)cam.width;
+        float v = (fy + xr.next()) / (float)cam.height;
+        vec3 o, d; camera_ray(cam, u, v, o, d);
+        float t;
+        uint32_t tri = trace_closest<24, false>(scene, o, d, 1e-4f, FLT_MAX, t, nullptr);
+        if (tri != kMiss) {
+            uint32_t prim = __float_as_uint(ldq(scene.tris + (size_t)tri * kTriQuads).w);
+            uint32_t mat = f2u(ldq(scene.prim_shade + prim).w);
+            f32x4 ke = ldq(scene.materials + 2 * (size_t)mat + 1);
+            color = color + v3(ke.x, ke.y, ke.z);
+            if (radiosity) color = color + v3(radiosity[3 * (size_t)prim], radiosity[3 * (size_t)prim + 1], radiosity[3 * (size_t)prim + 2]);
+            else color = color + v3(0.f, 0.f, 0.f);
+        }
+    }
+    color = div_scalar(color, (float)spp);
+    rgb8[3 * (size_t)p + 0] = (uint8_t)(255.99f * sqrt_exact(fminf(color.x, 1.0f)));
+    rgb8[3 * (size_t)p + 1] = (uint8_t)(255.99f * sqrt_exact(fminf(color.y, 1.0f)));
+    rgb8[3 * (size_t)p + 2] = (uint8_t)(255.99f * sqrt_exact(fminf(color.z, 1.0f)));
+    film.rngA[p] = make_uint4(xr.st.v0, xr.st.v1, xr.st.v2, xr.st.v3);
+    film.rngB[p] = make_uint2(xr.st.v4, xr.st.d);
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
@@ -769,6 +817,16 @@ void launch_primary_ids(cudaStream_t st, const SceneView& scene, const CameraVie
 void launch_trace_rays(cudaStream_t st, const SceneView& scene, const float* rays, size_t n, float t_min, int32_t* prim, float* t) {
     if (!n) return;
     k_trace_rays<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, rays, n, t_min, prim, t);
+}
+
+void launch_occluded(cudaStream_t st, const SceneView& scene, const float* segs, size_t n, uint8_t* out) {
+    if (!n) return;
+    k_occluded<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, segs, n, out);
+}
+void launch_visibility(cudaStream_t st, const SceneView& scene, const FilmView& film, const CameraView& cam, int spp, const float* radiosity, uint8_t* rgb8) {
+    size_t n = (size_t)cam.width * cam.height;
+    if (!n || spp <= 0) return;
+    k_visibility<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, film, cam, spp, radiosity, rgb8);
 }
 
 }  // namespace ptx

@@ -79,6 +79,9 @@ void launch_resolve(cudaStream_t st, const FilmView& film, float inv_spp, uint8_
 void launch_film_scale(cudaStream_t st, const FilmView& film, float inv_spp, float* linear_rgb);
 void launch_primary_ids(cudaStream_t st, const SceneView& scene, const CameraView& cam, int w, int h, int32_t* prim, float* t);
 void launch_trace_rays(cudaStream_t st, const SceneView& scene, const float* rays, size_t n, float t_min, int32_t* prim, float* t);
+void launch_occluded(cudaStream_t st, const SceneView& scene, const float* segs, size_t n, uint8_t* out);
+void launch_visibility(cudaStream_t st, const SceneView& scene, const FilmView& film, const CameraView& cam, int spp, const float* radiosity,
+                       uint8_t* rgb8);
 void launch_slot_pixels(cudaStream_t st, uint32_t* slot_pixel, int w, int h, int shard_mode, int rank, int world, uint32_t n_owned);
 
 // pixels owned by `rank` under tile sharding: rows are dealt in bands of kBandRows

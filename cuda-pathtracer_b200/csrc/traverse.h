@@ -253,4 +253,19 @@ PTX_HD uint32_t trace_closest(const SceneView& s, vec3 o, vec3 d, float t_min, f
     return tr.best;
 }
 
+// Any hit along (o, d) in [t_min, t_max): the traversal stops at the first accepted triangle (Scene::occluded_bvh,
+// scene.h:152-190).  The answer does not depend on the visiting order.  (Reference detail not reproduced: its
+// Triangle::intersect accepts t == t_max, triangle.h:84, its Quad halves do not; here every record uses t < t_max.)
+template <int STACK>
+PTX_HD bool trace_any(const SceneView& s, vec3 o, vec3 d, float t_min, float t_max) {
+    Traversal tr;
+    TravStack<STACK> stk;
+    tr.begin(d, t_max);
+    for (;;) {
+        bool done = tr.template step<false, STACK>(s, stk, o, d, t_min, nullptr);
+        if (tr.best != kMiss) return true;
+        if (done) return false;
+    }
+}
+
 }  // namespace ptx

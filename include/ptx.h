@@ -202,6 +202,15 @@ int ptx_trace_primary_ids(ptx_ctx* ctx, const ptx_scene* scene, const ptx_camera
 /* closest hit for n host rays (6 floats: o, d; d normalised like the Ray ctor, core/ray.h:9-12) */
 int ptx_trace_rays(ptx_ctx* ctx, const ptx_scene* scene, const float* rays_host, size_t n, float t_min,
                    int32_t* prim_id_host, float* t_host);
+/* any-hit shadow query: Scene::occluded(from, to) (scene.h:132-190) for n segments of 6 floats (from.xyz, to.xyz);
+ * occluded_host[i] = 1 if something lies strictly between the two points (1e-4 off both ends, as the reference) */
+int ptx_trace_occluded(ptx_ctx* ctx, const ptx_scene* scene, const float* segs_host, size_t n, uint8_t* occluded_host);
+/* primary-visibility view: the render_radiosity kernel (integrator.h:460-504).  spp jittered primary rays per pixel from
+ * the film's RNG streams (advanced like the reference does); colour = Le + radiosity_host[3 * primitive] (3 floats per
+ * reference primitive, NULL = 0: the radiosity solver that fills them is outside this library), sqrt, clamp, RGB8
+ * [h][w][3] with row 0 at the bottom */
+int ptx_render_visibility(ptx_ctx* ctx, const ptx_scene* scene, const ptx_camera* cam, ptx_film* film, int spp,
+                          const float* radiosity_host, uint8_t* rgb8_host);
 /* XORWOW state after render_init for pixels [first, first+n): 6 words each (v[0..4], d) */
 int ptx_film_rng_state(ptx_film* film, int64_t first, int64_t n, uint32_t* out_host);
 

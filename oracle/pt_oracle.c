@@ -493,6 +493,74 @@ void pto_primary_ids(const pto_scene* s, const pto_camera* cam, int32_t* ids, fl
 }
 
 /* ============================================================================================ */
+/* Scene::occluded (scene.h:132-149) with occluded_bvh (scene.h:152-190); mode 1 = its linear branch  */
+/* ============================================================================================ */
+int pto_occluded(const pto_scene* s, const float from[3], const float to[3], int mode) {
+    v3 f = vload(from);
+    v3 dir = vsub(vload(to), f);
+    float dist = vlen(dir);
+    dir = vdiv(dir, dist);
+    ray_t r = make_ray(vadd(f, vscale(1e-4f, dir)), dir);                 /* Ray ctor normalises again */
+    const float t_min = 1e-4f, t_max = dist - 1e-4f;
+    hit_t tmp;
+    if (mode == 1 || s->n_nodes == 0) {
+        for (int i = 0; i < s->n_prims; i++)
+            if (prim_intersect(&s->prims[i], &r, t_min, t_max, &tmp)) return 1;
+        return 0;
+    }
+    int stack[64], sp = 0;
+    stack[sp++] = 0;
+    float inv[3] = {1.0f / r.d.e[0], 1.0f / r.d.e[1], 1.0f / r.d.e[2]};
+    while (sp > 0) {
+        const pto_node* nd = &s->nodes[stack[--sp]];
+        float tmin_box = t_min, tmax_box = t_max;
+        for (int a = 0; a < 3; a++) {
+            float t0 = (nd->bmin[a] - r.o.e[a]) * inv[a];
+            float t1 = (nd->bmax[a] - r.o.e[a]) * inv[a];
+            if (inv[a] < 0.0f) { float t = t0; t0 = t1; t1 = t; }
+            tmin_box = t0 > tmin_box ? t0 : tmin_box;
+            tmax_box = t1 < tmax_box ? t1 : tmax_box;
+        }
+        if (tmax_box < tmin_box) continue;
+        if (nd->count > 0) {
+            for (int i = 0; i < nd->count; i++)
+                if (prim_intersect(&s->prims[s->idx[nd->left + i]], &r, t_min, t_max, &tmp)) return 1;
+        } else if (sp < 62) { stack[sp++] = nd->right; stack[sp++] = nd->left; }
+    }
+    return 0;
+}
+
+/* ============================================================================================ */
+/* render_radiosity (integrator.h:460-504): primary visibility, Le + per-primitive radiosity, sqrt    */
+/* `radiosity` = 3 floats per primitive (what the out-of-scope solver stores in the primitives) or NULL */
+/* ============================================================================================ */
+void pto_visibility(const pto_scene* s, const pto_camera* cam, pto_xorwow* rng, int spp, const float* radiosity, uint8_t* rgb8) {
+    int w = cam->width, hgt = cam->height;
+    #pragma omp parallel for schedule(dynamic, 1)
+    for (int y = 0; y < hgt; y++)
+        for (int x = 0; x < w; x++) {
+            int pix = y * w + x;
+            pto_xorwow st = rng[pix];
+            v3 color = V(0, 0, 0);
+            for (int k = 0; k < spp; k++) {
+                float u = (x + pto_uniform(&st)) / (float)w;
+                float v = (y + pto_uniform(&st)) / (float)hgt;
+                ray_t r = camera_ray(cam, u, v);
+                hit_t h;
+                int id = scene_intersect(s, &r, 1e-4f, FLT_MAX, 0, &h, NULL);
+                if (id >= 0) {
+                    color = vadd(color, vload(s->prims[id].Le));
+                    if (radiosity) color = vadd(color, vload(radiosity + 3 * id));
+                    else color = vadd(color, V(0, 0, 0));
+                }
+            }
+            color = vdiv(color, (float)spp);
+            for (int c = 0; c < 3; c++) rgb8[3 * pix + c] = (unsigned char)(255.99f * sqrtf(fminf(color.e[c], 1.0f)));
+            rng[pix] = st;
+        }
+}
+
+/* ============================================================================================ */
 /* sampleCosineHemisphere (integrator.h:62-85), integrator() BSDF branch (integrator.h:189-268)       */
 /* ============================================================================================ */
 static v3 sample_cosine_hemisphere(v3 n, pto_xorwow* rng) {

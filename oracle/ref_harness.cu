@@ -384,6 +384,89 @@ static int cmd_dump(int argc, char** argv) {
     printf("{\"cmd\":\"dump\",\"prims\":%zu,\"nodes\":%zu}\n", hs.prims.size(), hs.nodes.size());
     return 0;
 }
+
+// segs.bin: n records of 6 floats (from.xyz, to.xyz).  Output <prefix>.occ.u8: Scene::occluded(from, to) (scene.h:132-149,
+// BVH any-hit scene.h:152-190) and <prefix>.occ_lin.u8: the same query by linear scan over all primitives.
+static int cmd_occluded(int argc, char** argv) {
+    if (argc < 6) { fprintf(stderr, "occluded <scene> <segs.bin> <n> <out_prefix> [convert_quads]\n"); return 1; }
+    size_t n = (size_t)atoll(argv[4]);
+    std::string prefix = argv[5];
+    bool cq = argc > 6 && atoi(argv[6]) != 0;
+    HostScene hs;
+    if (!load_scene(argv[2], cq, hs)) return 2;
+    std::vector<float> segs(n * 6);
+    FILE* f = fopen(argv[3], "rb");
+    if (!f || fread(segs.data(), sizeof(float), n * 6, f) != n * 6) { fprintf(stderr, "bad segs file\n"); return 2; }
+    fclose(f);
+    Scene scene(hs.prims.data(), (int)hs.prims.size(), hs.nodes.data(), hs.indices.data());
+    Scene flat(hs.prims.data(), (int)hs.prims.size());              // no BVH: occluded() takes its linear branch
+    std::vector<unsigned char> a(n), b(n);
+    size_t diff = 0, occ = 0;
+    for (size_t i = 0; i < n; i++) {
+        Vector3f from(segs[i * 6], segs[i * 6 + 1], segs[i * 6 + 2]), to(segs[i * 6 + 3], segs[i * 6 + 4], segs[i * 6 + 5]);
+        a[i] = scene.occluded(from, to) ? 1 : 0;
+        b[i] = flat.occluded(from, to) ? 1 : 0;
+        diff += a[i] != b[i]; occ += a[i];
+    }
+    write_file(prefix + ".occ.u8", a.data(), n); write_file(prefix + ".occ_lin.u8", b.data(), n);
+    printf("{\"cmd\":\"occluded\",\"n\":%zu,\"occluded\":%zu,\"bvh_vs_linear_mismatch\":%zu}\n", n, occ, diff);
+    return 0;
+}
+
+// One pixel of render_radiosity (integrator.h:460-504) on the host: primary visibility, Le + per-primitive radiosity,
+// sqrt "gamma".  Radiosity comes from the (out-of-scope) solver; here primitive i gets rad[3*i..] from a file.
+static void radiosity_pixel(int x, int y, Sensor* cam, Scene* scene, curandState* rs, int spp, unsigned char* image) {
+    int pixel_index = y * cam->image_width + x;
+    curandState local_rng = rs[pixel_index];
+    Vector3f color(0.0f, 0.0f, 0.0f);
+    for (int s = 0; s < spp; s++) {
+        float u = (x + curand_uniform(&local_rng)) / float(cam->image_width);
+        float v = (y + curand_uniform(&local_rng)) / float(cam->image_height);
+        Ray ray = cam->get_ray(u, v);
+        SurfaceInteractionRecord si;
+        if (scene->intersect(ray, 1e-4f, FLT_MAX, si)) {
+            color += si.Le;
+            if (si.prim_ptr != nullptr) color += si.prim_ptr->getRadiosity();
+            else color += si.radiosity;
+        }
+    }
+    color /= float(spp);
+    color = Vector3f(sqrtf(fminf(color.x(), 1.0f)), sqrtf(fminf(color.y(), 1.0f)), sqrtf(fminf(color.z(), 1.0f)));
+    int idx = 3 * pixel_index;
+    image[idx + 0] = (unsigned char)(255.99f * color.x());
+    image[idx + 1] = (unsigned char)(255.99f * color.y());
+    image[idx + 2] = (unsigned char)(255.99f * color.z());
+    rs[pixel_index] = local_rng;
+}
+
+static int cmd_visibility(int argc, char** argv) {
+    if (argc < 8) { fprintf(stderr, "visibility <scene> <w> <h> <spp> <rad.bin|-> <out_prefix> [convert_quads]\n"); return 1; }
+    int w = atoi(argv[3]), h = atoi(argv[4]), spp = atoi(argv[5]);
+    std::string radf = argv[6], prefix = argv[7];
+    bool cq = argc > 8 && atoi(argv[8]) != 0;
+    HostScene hs;
+    if (!load_scene(argv[2], cq, hs)) return 2;
+    if (radf != "-") {
+        std::vector<float> rad(hs.prims.size() * 3);
+        FILE* f = fopen(radf.c_str(), "rb");
+        if (!f || fread(rad.data(), sizeof(float), rad.size(), f) != rad.size()) { fprintf(stderr, "bad radiosity file\n"); return 2; }
+        fclose(f);
+        for (size_t i = 0; i < hs.prims.size(); i++) hs.prims[i].setRadiosity(Vector3f(rad[3 * i], rad[3 * i + 1], rad[3 * i + 2]));
+    }
+    Sensor cam = make_camera(w, h);
+    size_t npix = (size_t)w * h;
+    Scene scene(hs.prims.data(), (int)hs.prims.size(), hs.nodes.data(), hs.indices.data());
+    std::vector<curandState> rs(npix);
+    for (size_t p = 0; p < npix; p++) curand_init(2023 + p, p, 0, &rs[p]);
+    std::vector<unsigned char> image(npix * 3);
+    for (int y = 0; y < h; y++) for (int x = 0; x < w; x++) radiosity_pixel(x, y, &cam, &scene, rs.data(), spp, image.data());
+    write_file(prefix + ".vis.u8", image.data(), image.size());
+    std::vector<unsigned> st(npix * 6);
+    for (size_t p = 0; p < npix; p++) { for (int k = 0; k < 5; k++) st[p * 6 + k] = rs[p].v[k]; st[p * 6 + 5] = rs[p].d; }
+    write_file(prefix + ".rng.u32", st.data(), st.size() * 4);
+    printf("{\"cmd\":\"visibility\",\"w\":%d,\"h\":%d,\"spp\":%d}\n", w, h, spp);
+    return 0;
+}
 #endif
 
 int main(int argc, char** argv) {
@@ -395,6 +478,8 @@ int main(int argc, char** argv) {
     if (c == "rays") return cmd_rays(argc, argv);
     if (c == "rng") return cmd_rng(argc, argv);
     if (c == "dump") return cmd_dump(argc, argv);
+    if (c == "occluded") return cmd_occluded(argc, argv);
+    if (c == "visibility") return cmd_visibility(argc, argv);
 #endif
     fprintf(stderr, "unknown command %s\n", c.c_str());
     return 1;

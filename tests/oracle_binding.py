@@ -49,6 +49,8 @@ class Oracle:
         L.pto_xorwow_init.argtypes = [C.c_uint64, C.c_uint64, C.c_void_p]
         L.pto_camera_lookat.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.pto_tonemap.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.pto_occluded.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.pto_visibility.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         self.L = L
 
     # scenes ----------------------------------------------------------------------------------
@@ -112,6 +114,25 @@ class Oracle:
             ids[i] = self.L.pto_intersect(s, _p(o), _p(d), C.c_float(t_min), C.c_float(3.4028234663852886e38), mode, C.byref(t), None)
             ts[i] = t.value
         return ids, ts
+
+    def occluded(self, s, segs, mode=0):
+        """Scene::occluded(from, to) for (n, 6) segments; mode 0 = through the BVH2 (as the reference), 1 = linear scan."""
+        segs = np.ascontiguousarray(segs, np.float32).reshape(-1, 6)
+        out = np.empty(len(segs), np.uint8)
+        for i, sg in enumerate(segs):
+            a = np.ascontiguousarray(sg[:3]); b = np.ascontiguousarray(sg[3:])
+            out[i] = self.L.pto_occluded(s, _p(a), _p(b), mode)
+        return out
+
+    def visibility(self, s, w, h, spp, radiosity=None, cam=None, rng=None):
+        """render_radiosity: returns (rgb8[h,w,3], rng) -- rng advanced like the kernel does."""
+        cam = cam or self.camera(w, h)
+        if rng is None:
+            rng = self.render_init(w, h)
+        rgb = np.zeros((h, w, 3), np.uint8)
+        rad = None if radiosity is None else np.ascontiguousarray(radiosity, np.float32)
+        self.L.pto_visibility(s, C.byref(cam), rng, spp, None if rad is None else _p(rad), _p(rgb))
+        return rgb, rng
 
     def primary_ids(self, s, w, h, cam=None):
         cam = cam or self.camera(w, h)

@@ -116,3 +116,21 @@ def test_segments_per_path_statistics(oracle):
     assert abs(st[0] / st[1] - 2.730) < 0.02
     assert abs(st[2] / st[0] - 14.0) < 0.3 and abs(st[3] / st[0] - 15.5) < 0.3    # reference BVH2 work per segment
     oracle.free(s)
+
+
+@pytest.mark.parametrize("tag", ["cbox_cq0", "cbox_quads_cq0", "cbox_quads_cq1"])
+def test_oracle_occluded_and_visibility_match_reference(oracle, tag):
+    """SURVEY.md 8(f4): Scene::occluded (scene.h:132-190) and render_radiosity (integrator.h:460-504) restated in
+    oracle/pt_oracle.c against the reference's own code (tests/golden/f4_vectors.npz, make_golden_f4.py): the any-hit
+    booleans, the visibility image and the RNG states it leaves behind must all be identical."""
+    g = np.load(os.path.join(GOLDEN, "f4_vectors.npz"))
+    name, cq = tag.rsplit("_cq", 1)
+    s = oracle.load_obj(os.path.join(SCENES, name + ".obj"), convert_quads=bool(int(cq)))
+    assert np.array_equal(oracle.occluded(s, g["segs"], mode=0), g[tag + "_occ"])
+    assert np.array_equal(oracle.occluded(s, g["segs"], mode=1), g[tag + "_occ_lin"])
+    for (w, h, spp) in ((48, 36, 3), (64, 40, 1)):
+        rgb, rng = oracle.visibility(s, w, h, spp, radiosity=g[tag + "_rad"])
+        assert np.array_equal(rgb, g[f"{tag}_vis_{w}x{h}_s{spp}"])
+        st = np.frombuffer(rng, np.uint32).reshape(h * w, -1)[:, :6]
+        assert np.array_equal(st, g[f"{tag}_visrng_{w}x{h}_s{spp}"])
+    oracle.free(s)
