@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libptx.so")
 
-CUDA_SOURCES = ["api.cu", "kernels.cu", "bvh_gpu.cu"]
+CUDA_SOURCES = ["api.cu", "kernels.cu", "bvh_gpu.cu", "geometry_gpu.cu"]
 HOST_SOURCES = ["bvh_host.cpp", "image_io.cpp", "loader.cpp", "pbrt_loader.cpp", "rng.cpp", "scene_pack.cpp"]
 
 NVCC_FLAGS = [

@@ -17,6 +17,7 @@
 #include "bvh_gpu.h"
 #include "bvh_host.h"
 #include "kernels.cuh"
+#include "geometry_gpu.h"
 #include "image_io.h"
 #include "loader.h"
 #include "rng.h"
@@ -240,7 +241,7 @@ void free_accel(ptx_scene* s) {
     s->d_nodes = nullptr; s->d_tris = nullptr;
 }
 
-int build_accel(ptx_scene* s, const ptx_build_opts* bo) {
+int build_accel(ptx_scene* s, const ptx_build_opts* bo, const TriIn* d_tris_in = nullptr) {
     ptx_ctx* c = s->ctx;
     PTX_CUDA(c, cudaSetDevice(c->device));
     int builder = bo ? bo->builder : 0;
@@ -255,7 +256,8 @@ int build_accel(ptx_scene* s, const ptx_build_opts* bo) {
     if (builder == 0) {
         // device builder: breadth-first binned SAH + BVH8 collapse, result stays in HBM (bvh_gpu.cu)
         GpuBvhResult g; std::string berr;
-        cudaError_t e = build_bvh8_gpu(c->stream, s->packed.tris.data(), n, max_leaf, kTraversalStack, g, berr);
+        cudaError_t e = d_tris_in ? build_bvh8_gpu(c->stream, d_tris_in, n, max_leaf, kTraversalStack, g, berr, true)   // device-resident soup (geometry_gpu.cu)
+                                  : build_bvh8_gpu(c->stream, s->packed.tris.data(), n, max_leaf, kTraversalStack, g, berr);
         if (e != cudaSuccess) { cudaFree(g.d_nodes); cudaFree(g.d_tris); return fail(c, PTX_ERR_CUDA, "GPU BVH build failed: " + berr); }
         s->d_nodes = g.d_nodes; s->d_tris = g.d_tris;
         s->view.n_nodes = g.n_nodes; s->view.n_tris = g.n_tris;
@@ -289,7 +291,7 @@ int build_accel(ptx_scene* s, const ptx_build_opts* bo) {
     return PTX_OK;
 }
 
-int finish_scene(ptx_ctx* c, ptx_scene* s, const ptx_build_opts* bo, ptx_scene** out) {
+int finish_scene(ptx_ctx* c, ptx_scene* s, const ptx_build_opts* bo, ptx_scene** out, const TriIn* d_tris_in = nullptr) {
     PTX_CUDA(c, cudaSetDevice(c->device));
     size_t np = s->packed.prim_shade.size(), nm = s->packed.materials.size();
     PTX_CUDA(c, cudaMalloc(&s->d_prim_shade, std::max<size_t>(np, 1) * sizeof(f32x4)));
@@ -300,10 +302,38 @@ int finish_scene(ptx_ctx* c, ptx_scene* s, const ptx_build_opts* bo, ptx_scene**
     s->view.n_prims = (uint32_t)np; s->view.n_mats = (uint32_t)(nm / 2);
     s->stats.n_primitives = (int64_t)np; s->stats.n_materials = (int64_t)(nm / 2);
     s->stats.shading_bytes = (int64_t)((np + nm) * sizeof(f32x4));
-    int rc = build_accel(s, bo);
+    int rc = build_accel(s, bo, d_tris_in);
     if (rc != PTX_OK) { ptx_scene_destroy(s); return rc; }
     *out = s;
     return PTX_OK;
+}
+
+// convert-quads / subdivision / packing as CUDA kernels (geometry_gpu.cu); the builder reads the triangle soup where the
+// kernels left it.  Host mirrors (primitive list for ptx_scene_get_primitives, soup for rebuilds) are downloaded afterwards.
+int scene_from_base_gpu(ptx_ctx* c, const std::vector<ptx_primitive>& base, bool convert_quads, int levels, ptx_scene** out) {
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    PackedScene bp;
+    pack_primitives(base.data(), base.size(), bp);             // material table + material index per parsed primitive
+    std::vector<uint32_t> base_mat(base.size());
+    for (size_t i = 0; i < base.size(); i++) base_mat[i] = f2u(bp.prim_shade[i].w);
+    DevGeometry g; std::string gerr;
+    cudaError_t e = preprocess_geometry_gpu(c->stream, base.data(), base_mat.data(), base.size(), convert_quads, levels, g, gerr);
+    if (e != cudaSuccess) { g.release(); return fail(c, e == cudaErrorMemoryAllocation ? PTX_ERR_NOMEM : PTX_ERR_CUDA, "GPU geometry preprocessing failed: " + gerr); }
+    ptx_scene* s = new ptx_scene();
+    s->ctx = c;
+    s->prims.resize(g.n_prims); s->packed.tris.resize(g.n_tris); s->packed.prim_shade.resize(g.n_prims);
+    s->packed.materials = bp.materials;
+    if (g.n_prims) {
+        e = cudaMemcpyAsync(s->prims.data(), g.d_prims, sizeof(ptx_primitive) * g.n_prims, cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(s->packed.tris.data(), g.d_tris, sizeof(TriIn) * g.n_tris, cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(s->packed.prim_shade.data(), g.d_prim_shade, sizeof(f32x4) * g.n_prims, cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) { g.release(); delete s; return cuda_fail(c, e, "scene_from_base_gpu"); }
+    }
+    s->stats.preprocess_ms = g.ms; s->stats.preprocess_on_device = 1;
+    int rc = finish_scene(c, s, nullptr, out, g.d_tris);
+    g.release();
+    return rc;
 }
 
 bool has_suffix(const std::string& s, const char* suf) {
@@ -364,8 +394,13 @@ int ptx_scene_from_triangles(ptx_ctx* c, const float* v, const float* normals, c
 int ptx_scene_load(ptx_ctx* c, const char* path, const ptx_load_opts* opts, ptx_scene** out) {
     if (!c || !path || !out) return fail(c, PTX_ERR_INVALID, "ptx_scene_load: NULL argument");
     std::vector<ptx_primitive> prims; std::string err;
-    int rc = parse_file(path, opts, prims, err);
+    const bool gpu_geometry = opts && (opts->convert_quads || opts->subdivision > 0) && !opts->host_preprocess;
+    ptx_load_opts base_opts{};
+    if (opts) base_opts = *opts;
+    if (gpu_geometry) { base_opts.convert_quads = 0; base_opts.subdivision = 0; }      // the parser only parses
+    int rc = parse_file(path, &base_opts, prims, err);
     if (rc != PTX_OK) return fail(c, rc, err);
+    if (gpu_geometry) return scene_from_base_gpu(c, prims, opts->convert_quads != 0, opts->subdivision, out);
     return ptx_scene_from_primitives(c, prims.data(), (int64_t)prims.size(), nullptr, out);
 }
 

@@ -395,8 +395,8 @@ struct DevBuf {            // frees on scope exit
         if (e_ != cudaSuccess) { err = std::string(#call) + ": " + cudaGetErrorString(e_); return e_; } \
     } while (0)
 
-cudaError_t build_bvh8_gpu(cudaStream_t st, const TriIn* h_tris, size_t n_in, int max_leaf, int max_bvh8_depth, GpuBvhResult& out,
-                           std::string& err) {
+cudaError_t build_bvh8_gpu(cudaStream_t st, const TriIn* tris, size_t n_in, int max_leaf, int max_bvh8_depth, GpuBvhResult& out,
+                           std::string& err, bool tris_on_device) {
     out = GpuBvhResult();
     if (max_leaf < 1 || max_leaf > 3) max_leaf = 3;
     const uint32_t n = (uint32_t)n_in;
@@ -412,13 +412,17 @@ cudaError_t build_bvh8_gpu(cudaStream_t st, const TriIn* h_tris, size_t n_in, in
     }
     const size_t node_cap = 2 * (size_t)n;                    // a binary tree over n primitives has < 2n nodes
     DevBuf d_tris_in, d_boxes0, d_boxes, d_scene, d_keys, d_keys2, d_vals, d_vals2, d_nodes, d_bn, d_prim_node, d_flags, d_scan, d_sc, d_bins, d_tmp;
-    BG_CUDA(d_tris_in.alloc(sizeof(TriIn) * n));
-    BG_CUDA(cudaMemcpyAsync(d_tris_in.p, h_tris, sizeof(TriIn) * n, cudaMemcpyHostToDevice, st));
+    const TriIn* d_in = tris;                                 // device-resident input (geometry_gpu.cu) is used in place
+    if (!tris_on_device) {
+        BG_CUDA(d_tris_in.alloc(sizeof(TriIn) * n));
+        BG_CUDA(cudaMemcpyAsync(d_tris_in.p, tris, sizeof(TriIn) * n, cudaMemcpyHostToDevice, st));
+        d_in = d_tris_in.as<TriIn>();
+    }
     BG_CUDA(d_boxes0.alloc(sizeof(PrimBox) * n));
     BG_CUDA(d_boxes.alloc(sizeof(PrimBox) * n));
     BG_CUDA(d_scene.alloc(sizeof(OrdBox) * 2));
     BG_CUDA(cudaMemsetAsync(d_scene.p, 0, sizeof(OrdBox) * 2, st));      // all-zero = empty box
-    k_prim_setup<<<grid_for(n), kThreads, 0, st>>>(d_tris_in.as<TriIn>(), n, d_boxes0.as<PrimBox>(), d_scene.as<OrdBox>());
+    k_prim_setup<<<grid_for(n), kThreads, 0, st>>>(d_in, n, d_boxes0.as<PrimBox>(), d_scene.as<OrdBox>());
     // ---- Morton order ------------------------------------------------------------------------
     BG_CUDA(d_keys.alloc(4 * (size_t)n)); BG_CUDA(d_keys2.alloc(4 * (size_t)n)); BG_CUDA(d_vals.alloc(4 * (size_t)n)); BG_CUDA(d_vals2.alloc(4 * (size_t)n));
     k_morton<<<grid_for(n), kThreads, 0, st>>>(d_boxes0.as<PrimBox>(), n, d_scene.as<OrdBox>(), d_keys.as<uint32_t>(), d_vals.as<uint32_t>());
@@ -534,7 +538,7 @@ cudaError_t build_bvh8_gpu(cudaStream_t st, const TriIn* h_tris, size_t n_in, in
             err = "BVH8 collapse: capacity exceeded"; return cudaErrorInvalidValue;
         }
         k_collapse_emit<<<grid_for(n_items), kThreads, 0, st>>>(d_nodes.as<Bvh2Node>(), d_items[cur].as<WorkItem>(), n_items, d_ioff.as<uint32_t>(),
-                                                                 d_toff.as<uint32_t>(), node_total, tri_total, d_tris_in.as<TriIn>(), d_tri_order.as<uint32_t>(),
+                                                                 d_toff.as<uint32_t>(), node_total, tri_total, d_in, d_tri_order.as<uint32_t>(),
                                                                  d_out_nodes.as<u32x4>(), out.d_tris, d_items[cur ^ 1].as<WorkItem>(), 1.0f / root_area,
                                                                  d_sah.as<float>());
         BG_CUDA(cudaGetLastError());

@@ -20,9 +20,10 @@ struct GpuBvhResult {
     aabb bounds;
 };
 
-// h_tris: n input triangles on the host.  Returns cudaSuccess or the failing CUDA error; `err` gets the text.
+// tris: n input triangles, on the host (uploaded here) or already on the device (tris_on_device; read in place, e.g. the
+// output of preprocess_geometry_gpu).  Returns cudaSuccess or the failing CUDA error; `err` gets the text.
 // A tree deeper than `max_bvh8_depth` (the traversal stack size) is reported as cudaErrorInvalidValue.
-cudaError_t build_bvh8_gpu(cudaStream_t stream, const TriIn* h_tris, size_t n, int max_leaf, int max_bvh8_depth, GpuBvhResult& out,
-                           std::string& err);
+cudaError_t build_bvh8_gpu(cudaStream_t stream, const TriIn* tris, size_t n, int max_leaf, int max_bvh8_depth, GpuBvhResult& out,
+                           std::string& err, bool tris_on_device = false);
 
 }  // namespace ptx

@@ -71,7 +71,8 @@ typedef struct {
     int32_t subdivision;      /* AppConfig::subdivision_step: 1->4 splits per level (form_factors.h:520-574) */
     int64_t triangle_cap;     /* .pbrt only: 0 = no cap (the reference substitutes a box above 2 M, pbrt_loader.h:205) */
     int32_t mirror_from_mtl;  /* extension: MTL `illum 3|5` => mirror with Kr = Ks.  0 keeps reference semantics */
-    int32_t reserved;
+    int32_t host_preprocess;  /* 1 = run convert_quads / subdivision on the host (cross-check); default 0 = CUDA kernels
+                                 feeding the device BVH builder (ptx_scene_load only; ptx_parse_scene_file is host-only) */
 } ptx_load_opts;
 
 typedef struct {
@@ -92,6 +93,8 @@ typedef struct {
     float build_ms;           /* device time of the last build */
     int32_t builder;
     int32_t max_depth;
+    float preprocess_ms;      /* device time of convert-quads / subdivision / packing when they ran on the GPU, else 0 */
+    int32_t preprocess_on_device;
 } ptx_scene_stats;
 
 /* replaces loadScene/loadOBJ/loadPBRT + RayTracingManager::buildAccelStructure + Scene(...)

@@ -58,6 +58,9 @@
 #include "rendering/render_config.h"
 #include "utils/file_manager.h"
 #include "rendering/integrator.h"
+#ifdef REF_HOST
+#include "rendering/form_factors.h"      // subdivide_primitives (form_factors.h:475-574), host only
+#endif
 
 // ---------------------------------------------------------------------------------------------
 // helpers
@@ -90,6 +93,7 @@ static void split_quads(std::vector<Primitive>& prims) {
     prims.swap(out);
 }
 
+static int g_subdivision = 0;      // `dump ... [convert_quads] [subdivision]`: loadScene order, application_state.h:411-434
 static bool load_scene(const char* path, bool convert_quads, HostScene& hs) {
     Primitive* list = nullptr; int n = 0;
     std::streambuf* old = std::cout.rdbuf(nullptr);   // silence the reference's banners
@@ -104,6 +108,9 @@ static bool load_scene(const char* path, bool convert_quads, HostScene& hs) {
         hs.prims.assign(list, list + n);
         delete[] list;
         if (convert_quads) split_quads(hs.prims);
+#ifdef REF_HOST
+        if (g_subdivision > 0) hs.prims = subdivide_primitives(hs.prims, g_subdivision);
+#endif
         BVHBuilder b(hs.prims.data(), (int)hs.prims.size());
         hs.nodes = b.nodes; hs.indices = b.primitive_indices;
     }
@@ -357,6 +364,7 @@ static int cmd_dump(int argc, char** argv) {
     if (argc < 4) { fprintf(stderr, "dump <scene> <out_prefix> [convert_quads]\n"); return 1; }
     std::string prefix = argv[3];
     bool cq = argc > 4 && atoi(argv[4]) != 0;
+    g_subdivision = argc > 5 ? atoi(argv[5]) : 0;
     HostScene hs;
     if (!load_scene(argv[2], cq, hs)) return 2;
     std::vector<float> rec;

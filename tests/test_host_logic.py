@@ -326,3 +326,26 @@ def test_png_writer_roundtrip(pkg, tmp_path, w, h):
     assert np.array_equal(_decode_png(tmp_path / "b.png"), img[::-1])
     with pytest.raises(pkg.PtxError):
         pkg.write_png_rgb8(tmp_path / "nodir" / "c.png", img)
+
+
+def _assert_prims_equal_reference_dump(prims, ref):
+    """prims: structured array (binding.PRIM_DTYPE); ref: (n, 22) float32 rows of the reference harness dump."""
+    assert len(prims) == len(ref)
+    ty = ref[:, 0].copy().view(np.int32)
+    assert np.array_equal(prims["type"], ty)
+    v = prims["v"][:, :, :3].reshape(len(prims), 12)
+    tri = ty == 0
+    assert np.array_equal(bits(v[tri, :9]), bits(ref[tri, 1:10])) and np.array_equal(bits(v[~tri]), bits(ref[~tri, 1:13]))
+    assert np.array_equal(bits(prims["normal"]), bits(ref[:, 13:16]))
+    assert np.array_equal(bits(prims["bsdf"]), bits(ref[:, 16:19])) and np.array_equal(bits(prims["Le"]), bits(ref[:, 19:22]))
+
+
+@pytest.mark.parametrize("tag", ["cbox_cq0_sub1", "cbox_cq0_sub3", "cbox_quads_cq0_sub2", "cbox_quads_cq1_sub1", "cbox_quads_cq1_sub2"])
+def test_host_subdivision_matches_reference(pkg, tag):
+    """Host convert-quads + subdivision (csrc/loader.cpp) against the reference's convertQuadsToTriangles + subdivide_primitives
+    (tests/golden/f3_vectors.npz): order, vertices and recomputed normals bit for bit."""
+    g = np.load(os.path.join(GOLDEN, "f3_vectors.npz"))
+    name, rest = tag.split("_cq")
+    cq, sub = rest.split("_sub")
+    prims = pkg.parse_scene_file(os.path.join(SCENES, name + ".obj"), convert_quads=bool(int(cq)), subdivision=int(sub))
+    _assert_prims_equal_reference_dump(prims, g[tag])
