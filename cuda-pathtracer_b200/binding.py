@@ -72,7 +72,7 @@ class RenderStats(C.Structure):
 
 
 EXPORTS = [
-    "ptx_ctx_create", "ptx_ctx_destroy", "ptx_last_error", "ptx_sync", "ptx_ctx_device_info", "ptx_version",
+    "ptx_ctx_create", "ptx_ctx_destroy", "ptx_last_error", "ptx_sync", "ptx_ctx_device_info", "ptx_ctx_flush_l2", "ptx_version",
     "ptx_timer_start", "ptx_timer_stop", "ptx_ctx_stream",
     "ptx_scene_load", "ptx_parse_scene_file", "ptx_free_primitives", "ptx_scene_from_primitives", "ptx_scene_from_triangles",
     "ptx_scene_build_accel", "ptx_scene_stats_get", "ptx_scene_get_primitives", "ptx_scene_destroy",
@@ -100,6 +100,7 @@ def lib():
             getattr(L, name).restype = None
             getattr(L, name).argtypes = [C.c_void_p]
         L.ptx_film_set_sample_count.argtypes = [C.c_void_p, C.c_float]
+        L.ptx_ctx_flush_l2.argtypes = [C.c_void_p]
         L.ptx_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_float, C.c_void_p, C.c_void_p]
         L.ptx_trace_occluded.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.ptx_render_visibility.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
@@ -294,6 +295,9 @@ class Context:
         ts = np.empty(len(rays), np.float32)
         _check(lib().ptx_trace_rays(self._h, scene._h, _ptr(rays), len(rays), C.c_float(t_min), _ptr(ids), _ptr(ts)), self._h)
         return ids, ts
+
+    def flush_l2(self):
+        _check(lib().ptx_ctx_flush_l2(self._h), self._h)
 
     def trace_occluded(self, scene, segs):
         """Scene::occluded(from, to) for (n, 6) float32 segments -> uint8[n]."""

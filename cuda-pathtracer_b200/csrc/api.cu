@@ -39,6 +39,7 @@ struct ptx_ctx {
     // wavefront state (grown on demand, reused across renders)
     WaveState ws{};
     uint32_t* d_scratch = nullptr; size_t scratch_words = 0;
+    void* d_flush = nullptr; int flush_value = 0;            // ptx_ctx_flush_l2
     uint32_t pixmap_capacity = 0, progress_capacity = 0;   // entries allocated in ws.slot_pixel / ws.progress
     unsigned long long* h_counters = nullptr;   // pinned
     int slot_key[5] = {-1, -1, -1, -1, -1};     // (w, h, shard_mode, rank, world) the slot map was built for
@@ -129,7 +130,7 @@ void ptx_ctx_destroy(ptx_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     cudaFree(c->ws.A); cudaFree(c->ws.B); cudaFree(c->ws.C); cudaFree(c->ws.D); cudaFree(c->ws.E);
-    cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]); cudaFree(c->ws.slot_pixel); cudaFree(c->ws.progress); cudaFree(c->ws.counters);
+    cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]); cudaFree(c->ws.slot_pixel); cudaFree(c->ws.progress); cudaFree(c->ws.counters); cudaFree(c->d_flush);
     cudaFree(c->d_scratch); cudaFree(c->d_jump);
     cudaFreeHost(c->h_counters);
     for (auto ev : c->stage_events) cudaEventDestroy(ev);
@@ -852,6 +853,16 @@ int ptx_trace_rays(ptx_ctx* c, const ptx_scene* scene, const float* rays_host, s
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     cudaFree(d_rays); cudaFree(d_ids); cudaFree(d_t);
     if (e != cudaSuccess) return cuda_fail(c, e, "ptx_trace_rays");
+    return PTX_OK;
+}
+
+int ptx_ctx_flush_l2(ptx_ctx* c) {
+    if (!c) return fail(nullptr, PTX_ERR_INVALID, "ptx_ctx_flush_l2: ctx is NULL");
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    const size_t bytes = (size_t)256 << 20;                    // 2 x the 126 MB L2
+    if (!c->d_flush) PTX_CUDA(c, cudaMalloc(&c->d_flush, bytes));
+    c->flush_value ^= 0xFF;
+    PTX_CUDA(c, cudaMemsetAsync(c->d_flush, c->flush_value, bytes, c->stream));
     return PTX_OK;
 }
 

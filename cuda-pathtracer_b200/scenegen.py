@@ -143,3 +143,15 @@ def c3_scene(prims, level=9):
     tris = np.concatenate([enc, s1, s2], 0)
     mat = np.concatenate([enc_m, np.full(len(s1), 4, np.uint32), np.full(len(s2), 5, np.uint32)])
     return tris, mat, CORNELL_MATS
+
+
+def c4_prims(prims):
+    """the Cornell box of scenes/cbox_quads.obj with the tall box a mirror (Kr 0.9, the library's mirror
+    extension) and the short box emissive (Ke 2, 2, 2).  `prims` = binding.parse_scene_file(cbox_quads.obj): faces 6-10 are
+    the short box, 11-15 the tall box (scenes/cbox_quads.obj:97-112).  Returns a modified copy."""
+    out = prims.copy()
+    assert len(out) == 16
+    out["Le"][6:11] = (2.0, 2.0, 2.0)
+    out["bsdf"][11:16] = (0.9, 0.9, 0.9)
+    out["material_type"][11:16] = 1
+    return out

@@ -41,6 +41,9 @@ void ptx_ctx_destroy(ptx_ctx* ctx);
 const char* ptx_last_error(const ptx_ctx* ctx);           /* ctx may be NULL: last error of this thread */
 int ptx_sync(ptx_ctx* ctx);                                /* cudaDeviceSynchronize, application.h:199 */
 int ptx_ctx_device_info(const ptx_ctx* ctx, int* sm_count, int* cc_major, int* cc_minor, size_t* total_mem);
+/* benchmarking aid: overwrite a 256 MB scratch buffer on the context's stream so that nothing of the previous frame is
+ * left in the 126 MB L2 (the persistent kernel's per-frame inputs, film + RNG state, are smaller than the L2) */
+int ptx_ctx_flush_l2(ptx_ctx* ctx);
 const char* ptx_version(void);
 /* CUDA-event stopwatch on the ctx stream (what bench.py times steps with) and the raw cudaStream_t */
 int ptx_timer_start(ptx_ctx* ctx);
