@@ -15,5 +15,5 @@ with pkg.Context(0) as ctx:
     cam = pkg.default_camera(1920, 1080)
     film = ctx.create_film(1920, 1080)
     for rep in range(3):
-        st = ctx.render(scene, cam, film, spp=spp, max_depth=8, pipeline=2, rng_mode=rng)
+        st = ctx.render(scene, cam, film, spp=spp, max_depth=8, pipeline=int(sys.argv[4]) if len(sys.argv) > 4 else 3, rng_mode=rng)
         print(st["segments"] / st["render_ms"] / 1e3, "Mseg/s", st["kernel_launches"], "launches")
