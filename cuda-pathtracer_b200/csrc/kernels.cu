@@ -776,8 +776,13 @@ void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, con
                          const RenderParams& rp, int sm_count, int min_blocks) {
     if (rp.spp <= 0 || !rp.n_owned) return;
     const unsigned long long items = rng_mode == 0 ? (unsigned long long)rp.n_owned : rp.total_paths;
-    // resident CTAs: 3 x 256 threads at 80 registers (default), 4 x 256 at 64, or 7 x 128 at 72 (reserved[2] = 4 / 7)
-    const int per_sm = min_blocks == 4 ? 4 : (min_blocks == 7 ? 7 : 3);
+    // resident CTAs: 3 x 256 threads at 80 registers (default), 4 x 256 at 64, or 7 x 128 at 72 (reserved[2] = 4 / 7);
+    // reserved[2] = 1 / 2 launch only 1 / 2 of the three 256-thread CTAs per SM: fewer warps share an SM, so each pixel's
+    // sequential sample chain advances faster (matters when a rank owns few pixels: DESIGN.md section 6)
+    int per_sm = min_blocks == 4 ? 4 : (min_blocks == 7 ? 7 : ((min_blocks == 1 || min_blocks == 2) ? min_blocks : 3));
+    // default: with the sequential RNG and fewer than ~3 pixels per resident lane the frame is bounded by its longest pixel
+    // chain, not by throughput -- two CTAs per SM finish such a frame sooner (C2, 1/8 of the film: 38 vs 43 ms)
+    if (min_blocks == 0 && rng_mode == 0 && (unsigned long long)rp.n_owned < 3ull * (unsigned long long)sm_count * 3ull * kBlock) per_sm = 2;
     const int block = min_blocks == 7 ? 128 : kBlock;
     unsigned g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (items + block - 1) / block);
     if (per_sm == 4) {
