@@ -237,9 +237,11 @@ def run_ours(args, scene_path, w, h, spp, depth):
         loop = pipeline == pkg.PIPELINE_LOOP
         bytes_per_slot_launch = None
         if pipeline == pkg.PIPELINE_PERSIST:
-            # no path state in memory: per owned pixel and frame the compat kernel moves its id 4 + RNG state 24 + 24 + pixel sum 16 + 16 bytes;
+            # no path state in memory: per owned pixel and sample chunk the compat kernel moves its id 4 + RNG state 24 + 24 + pixel sum 16 + 16 bytes;
             # per path the counter-RNG kernel moves its pixel id 4 + three float atomics 12
-            per_item = 84.0 * (w * h / world) if rng_mode == pkg.RNG_XORWOW_COMPAT else 16.0 * st_t["paths"]
+            # (a pixel is handed on between its sample chunks: per chunk pixel id 4 + RNG state 24 + 24 + pixel sum 16 + 16 + progress flag 4 + 4)
+            n_chunks = args.chunks if args.chunks > 0 else min(6, max(1, spp.bit_length()))
+            per_item = 92.0 * n_chunks * (w * h / world) if rng_mode == pkg.RNG_XORWOW_COMPAT else 16.0 * st_t["paths"]
             bytes_per_seg = per_item / max(st_t["segments"], 1)
             kname, k_ms = "k_path_persist<rng> (one launch per frame: extend+shade+regenerate, all state in registers)", st_t["shade_ms"]
         elif loop:
@@ -263,6 +265,14 @@ def run_ours(args, scene_path, w, h, spp, depth):
             bytes_per_seg = n_node * 80 + n_tri * 48
             traversal = {"nodes_per_segment": n_node, "tris_per_segment": n_tri, "node_bytes": 80, "tri_bytes": 48}
         achieved = st_t["segments"] * bytes_per_seg / (k_ms * 1e-3) * 1e-9 if k_ms > 0 else None
+        # measured DRAM bytes per launch of the dominant kernel (ncu capture of this very configuration, profiles/traffic.json)
+        traffic = traffic_src = None
+        tkey = f"{args.workload}/{args.rng}/{args.pipeline}"
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if world == 1 and args.spp == 0 and os.path.exists(tpath):
+            ent = json.load(open(tpath)).get(tkey)
+            if ent:
+                traffic, traffic_src = ent["bytes"], ent["source"]
         out = {
             "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_dev_max / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -276,7 +286,7 @@ def run_ours(args, scene_path, w, h, spp, depth):
                     "ms_per_step": ms_e2e_max / args.steps},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
-                         "traffic": None, "peak_source": peak_src, "bytes_per_segment": bytes_per_seg,
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "bytes_per_segment": bytes_per_seg,
                          "kernel_ms_per_step": k_ms, "kernel_share_of_step": k_ms / st_t["render_ms"] if st_t["render_ms"] else None,
                          "traversal": traversal, "bytes_per_slot_launch": bytes_per_slot_launch},
             "scene": {k: scene_stats[k] for k in ("n_triangles", "n_nodes", "node_bytes", "triangle_bytes", "build_ms", "builder", "max_depth", "sah_cost")},
