@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(HERE, "libptx.so")
 
 RNG_XORWOW_COMPAT, RNG_PHILOX = 0, 1
 SHARD_NONE, SHARD_TILES, SHARD_SAMPLES = 0, 1, 2
-PIPELINE_WAVEFRONT, PIPELINE_FUSED, PIPELINE_LOOP, PIPELINE_PERSIST = 0, 1, 2, 3
+PIPELINE_DEFAULT, PIPELINE_FUSED, PIPELINE_LOOP, PIPELINE_PERSIST, PIPELINE_WAVEFRONT = 0, 1, 2, 3, 4
 
 
 class PtxError(RuntimeError):
@@ -266,7 +266,7 @@ class Context:
 
     # -- rendering ----------------------------------------------------------------------------
     def render(self, scene, camera, film, spp, max_depth=5, rng_mode=RNG_XORWOW_COMPAT, accumulate=False, shard_mode=SHARD_NONE,
-               shard_rank=0, shard_world=1, pipeline=PIPELINE_WAVEFRONT, stage_timing=False, count_work=False, sampling_mode=0, loop_iters=0, loop_min_blocks=0, chunks=0):
+               shard_rank=0, shard_world=1, pipeline=PIPELINE_DEFAULT, stage_timing=False, count_work=False, sampling_mode=0, loop_iters=0, loop_min_blocks=0, chunks=0):
         o = RenderOpts()
         o.spp, o.max_depth, o.rng_mode, o.sampling_mode = int(spp), int(max_depth), int(rng_mode), int(sampling_mode)
         o.accumulate, o.shard_mode, o.shard_rank, o.shard_world = int(accumulate), int(shard_mode), int(shard_rank), int(shard_world)

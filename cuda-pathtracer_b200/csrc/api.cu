@@ -662,7 +662,8 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     rp.total_paths = (unsigned long long)rp.n_owned * (unsigned long long)spp_local;
     rp.n_slots = rng_mode == PTX_RNG_XORWOW_COMPAT ? rp.n_owned : (uint32_t)std::min<unsigned long long>(rp.total_paths, kPhiloxPool);
 
-    const bool persist = opts->pipeline == 3;
+    const int pipeline = opts->pipeline == 0 ? 3 : opts->pipeline;     // 0 = default = the persistent kernel
+    const bool persist = pipeline == 3;
     int rc = ensure_pixmap(c, rp.n_owned, persist ? (uint32_t)w * (uint32_t)h : 0u);
     if (rc == PTX_OK && !persist) rc = ensure_wave_capacity(c, rp.n_slots, rp.n_owned);
     if (rc != PTX_OK) return rc;
@@ -684,8 +685,8 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
 
     CameraView cv = camera_view(*cam, w, h);
     FilmView fv = film->view();
-    const bool fused = opts->pipeline == 1;
-    const bool path_loop = opts->pipeline == 2;
+    const bool fused = pipeline == 1;
+    const bool path_loop = pipeline == 2;
     // bounces per path-loop launch: a compat-mode slot lives for >= spp segments, so long launches waste
     // little on lanes that die early; reserved[1] overrides (tuning / tests)
     int loop_iters = opts->reserved[1] > 0 ? opts->reserved[1] : 2 * std::min(std::max(rp.spp, 16), 256);

@@ -169,13 +169,14 @@ typedef struct {
     int32_t shard_rank, shard_world;
     int32_t rr_start_depth;   /* 0 => 3  (depth > 2, integrator.h:207) */
     float rr_cap;             /* 0 => 0.95 */
-    int32_t pipeline;         /* 0 = wavefront (raygen/extend/shade/compact); 1 = fused bounce kernel (one launch per bounce);
-                                 2 = path loop (state in registers for reserved[1] bounces per launch, default min(max(spp,16),256));
-                                 3 = persistent path loop (one launch per frame; lanes pull pixels / paths from a counter, no path
-                                     state in memory; with the compat RNG a pixel's samples are split into reserved[3] work items,
-                                     default 6: 1/2, 1/4, ... 1/32, 1/32 of spp, handed from lane to lane through the film,
-                                     so the frame's tail is one small chunk, not one pixel).
-                                     reserved[2] = 4 / 7 select the 4 x 256 / 7 x 128 threads-per-SM builds of 2 and 3 */
+    int32_t pipeline;         /* 0 = default (= 3).  3 = persistent path loop: one launch per frame; lanes pull pixels / paths from
+                                     a counter, no path state in memory; with the compat RNG a pixel's samples are split into
+                                     reserved[3] work items (default 6: 1/2, 1/4, ... 1/32, 1/32 of spp) handed from lane to lane
+                                     through the film, so the frame's tail is one small chunk, not one pixel.
+                                 Cross-checks (bit-identical images): 4 = wavefront (raygen / extend / shade / compact kernels),
+                                 1 = fused bounce kernel (one launch per bounce), 2 = path loop with a slot queue (state in
+                                 registers for reserved[1] bounces per launch).
+                                 reserved[2] = 1 / 2 / 4 / 7 select other residency builds of 2 and 3 (CTAs per SM) */
     int32_t reserved[5];
 } ptx_render_opts;
 
