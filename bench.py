@@ -29,6 +29,9 @@ WORKLOADS = {
     "c4": ("generated:c4", 3840, 2160, 4096, 8),        # mirror tall box + emissive short box (scenegen.c4_prims)
     # generated on the box (cuda-pathtracer_b200/scenegen.py): two displaced icospheres, 10 485 772 triangles, Cornell enclosure
     "c3": ("generated:c3_level9", 1920, 1080, 256, 8),
+    # generated on the box as a .pbrt file (scenegen.write_c5_pbrt) and loaded through ptx_scene_load: 4883 instances of a
+    # 20 480-triangle mesh = 100 003 978 triangles, 64 emissive quads.  ~35 s per frame on one GPU: not a default.
+    "c5": ("generated:c5", 3840, 2160, 1024, 8),
 }
 METRIC = "Mpaths*bounces/s"
 
@@ -145,7 +148,13 @@ def run_ours(args, scene_path, w, h, spp, depth):
     if generated:                                   # scene replicated on every GPU (one-time, outside the timed region)
         from cuda_pathtracer_b200 import scenegen
         base = pkg.parse_scene_file(os.path.join(ROOT, "scenes", "cbox_quads.obj"))
-        if scene_path.endswith("c4"):
+        if scene_path.endswith("c5"):
+            pbrt = os.path.join("/tmp", f"c5_rank{rank}.pbrt")
+            scenegen.write_c5_pbrt(pbrt)
+            scene = ctx.load_scene(pbrt, mirror_from_mtl=True)
+            side = 17; room = 4.0 * side                      # camera of the generated file (scenegen.write_c5_pbrt)
+            c5_cam = ((room / 2, room / 2, room * 1.9), (room / 2, room / 2, 0.0), (0.0, 1.0, 0.0), 40.0)
+        elif scene_path.endswith("c4"):
             scene = ctx.scene_from_primitives(scenegen.c4_prims(base), builder=0, max_leaf=args.max_leaf)
         else:
             level = int(scene_path.rsplit("level", 1)[1])
@@ -157,7 +166,7 @@ def run_ours(args, scene_path, w, h, spp, depth):
         if args.max_leaf:
             scene.rebuild(builder=0, max_leaf=args.max_leaf)
     scene_stats = scene.stats()
-    cam = pkg.default_camera(w, h)
+    cam = pkg.look_at_camera(*c5_cam, w, h) if generated and scene_path.endswith("c5") else pkg.default_camera(w, h)
     film = ctx.create_film(w, h)
     film_ptr, film_bytes = film.device_buffer()
     film_tensor = None
@@ -208,7 +217,8 @@ def run_ours(args, scene_path, w, h, spp, depth):
     t0 = time.perf_counter()
     seg_e2e = 0
     for _ in range(args.steps):
-        cam = pkg.default_camera(w, h)                # host camera update + by-value upload, like renderFrame (application.h:161-164)
+        if not (generated and scene_path.endswith("c5")):
+            cam = pkg.default_camera(w, h)            # host camera update + by-value upload, like renderFrame (application.h:161-164)
         st = step(True)
         seg_e2e += st["segments"]
     ctx.sync()

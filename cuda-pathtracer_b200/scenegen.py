@@ -155,3 +155,51 @@ def c4_prims(prims):
     out["bsdf"][11:16] = (0.9, 0.9, 0.9)
     out["material_type"][11:16] = 1
     return out
+
+
+def write_c5_pbrt(path, instances=4883, level=5, n_lights=64, seed=7):
+    """a pbrt-format scene written on the box -- one icosphere mesh (20 * 4^level triangles) declared
+    once with ObjectBegin/ObjectEnd and instanced `instances` times (ObjectInstance under Translate / Scale / Rotate) on a
+    jittered grid inside a large room, plus `n_lights` emissive quads under the ceiling.  The defaults give
+    4883 * 20480 = 100 003 840 instanced triangles; the loader flattens the instances (as the reference's loadPBRT does).
+    Returns the triangle count."""
+    rng = np.random.default_rng(seed)
+    v, f = icosphere_indexed(level)
+    side = int(np.ceil(instances ** (1.0 / 3.0)))
+    room = 4.0 * side
+    with open(path, "w") as fp:
+        fp.write("# generated by cuda-pathtracer_b200/scenegen.py: write_c5_pbrt\n")
+        fp.write(f"LookAt {room / 2} {room / 2} {room * 1.9}  {room / 2} {room / 2} 0  0 1 0\n")
+        fp.write('Camera "perspective" "float fov" [40]\nWorldBegin\n')
+        fp.write('MakeNamedMaterial "grey" "string type" "matte" "rgb Kd" [0.7 0.7 0.7]\n')
+        fp.write('MakeNamedMaterial "chrome" "string type" "mirror" "rgb Kr" [0.9 0.9 0.9]\n')
+        idx_txt = " ".join(str(int(i)) for i in f.ravel())
+        pts_txt = " ".join(repr(float(x)) for x in v.ravel())
+        for name, mat in (("blob", "grey"), ("blob_m", "chrome")):        # an instance keeps the material of its definition
+            fp.write(f'AttributeBegin\n  NamedMaterial "{mat}"\n  ObjectBegin "{name}"\n    Shape "trianglemesh" "integer indices" [{idx_txt}] "point P" [{pts_txt}]\n  ObjectEnd\nAttributeEnd\n')
+        # room: floor, ceiling, back, left, right as two-triangle quads
+        def quad(a, b, c, d):
+            pts = " ".join(repr(float(x)) for p in (a, b, c, d) for x in p)
+            fp.write(f'Shape "trianglemesh" "integer indices" [0 1 2 0 2 3] "point P" [{pts}]\n')
+        R = room
+        fp.write('AttributeBegin\n  NamedMaterial "grey"\n')
+        quad((0, 0, 0), (R, 0, 0), (R, 0, R), (0, 0, R)); quad((0, R, 0), (0, R, R), (R, R, R), (R, R, 0))
+        quad((0, 0, 0), (0, R, 0), (R, R, 0), (R, 0, 0)); quad((0, 0, 0), (0, 0, R), (0, R, R), (0, R, 0)); quad((R, 0, 0), (R, R, 0), (R, R, R), (R, 0, R))
+        fp.write("AttributeEnd\n")
+        g = int(np.ceil(np.sqrt(n_lights)))
+        for k in range(n_lights):
+            cx, cz = (k % g + 0.5) * R / g, (k // g + 0.5) * R / g
+            s = 0.15 * R / g
+            fp.write('AttributeBegin\n  AreaLightSource "diffuse" "rgb L" [12 12 12]\n  Material "matte" "rgb Kd" [0 0 0]\n')
+            quad((cx - s, R - 0.01, cz - s), (cx + s, R - 0.01, cz - s), (cx + s, R - 0.01, cz + s), (cx - s, R - 0.01, cz + s))
+            fp.write("AttributeEnd\n")
+        n = 0
+        for k in range(instances):
+            i, j, l = k % side, (k // side) % side, k // (side * side)
+            c = (np.array([i, j, l]) + 0.5 + rng.uniform(-0.15, 0.15, 3)) * 4.0
+            sc = rng.uniform(0.9, 1.5)
+            fp.write(f'AttributeBegin\n  Translate {c[0]:.6f} {c[1]:.6f} {c[2]:.6f}\n  Rotate {rng.uniform(0, 360):.4f} 0 1 0\n'
+                     f'  Scale {sc:.6f} {sc:.6f} {sc:.6f}\n  ObjectInstance "{"blob_m" if k % 7 == 0 else "blob"}"\nAttributeEnd\n')
+            n += len(f)
+        fp.write("WorldEnd\n")
+    return n + 10 + 2 * n_lights

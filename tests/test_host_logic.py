@@ -349,3 +349,23 @@ def test_host_subdivision_matches_reference(pkg, tag):
     cq, sub = rest.split("_sub")
     prims = pkg.parse_scene_file(os.path.join(SCENES, name + ".obj"), convert_quads=bool(int(cq)), subdivision=int(sub))
     _assert_prims_equal_reference_dump(prims, g[tag])
+
+
+def test_pbrt_loader_generated_instanced_scene(pkg, tmp_path):
+    """A generated scene of the C5 shape (scenegen.write_c5_pbrt: object definitions, 27 instances under Translate / Rotate /
+    Scale, area lights) must flatten to exactly what the reference's loadPBRT produces: count, SHA-256 of every array and
+    every 61st primitive are stored in tests/golden/pbrt_vectors.npz (make_golden_pbrt.py)."""
+    import hashlib
+    from cuda_pathtracer_b200 import scenegen
+    g = np.load(os.path.join(GOLDEN, "pbrt_vectors.npz"))
+    path = tmp_path / "c5_small.pbrt"
+    n = scenegen.write_c5_pbrt(str(path), instances=27, level=3, n_lights=4)
+    pr = pkg.parse_scene_file(path)
+    assert len(pr) == n == int(g["c5_small_count"][0])
+    arrays = {"v": pr["v"][:, :3].reshape(len(pr), 9), "normal": pr["normal"], "bsdf": pr["bsdf"], "Le": pr["Le"]}
+    for k, a in arrays.items():
+        a = np.ascontiguousarray(a)
+        assert np.array_equal(a[::61], g["c5_small_" + k + "_sampled"]), k
+        assert hashlib.sha256(a.tobytes()).digest() == g["c5_small_" + k + "_sha256"].tobytes(), k
+    mir = pkg.parse_scene_file(path, mirror_from_mtl=True)
+    assert (mir["material_type"] == 1).sum() == 4 * 1280          # instances 0, 7, 14, 21 use the mirror definition
