@@ -183,7 +183,7 @@ def run_ours(args, scene_path, w, h, spp, depth):
             torch.cuda.synchronize()
 
     kw = dict(spp=spp, max_depth=depth, rng_mode=rng_mode, pipeline=pipeline, shard_mode=shard_mode, shard_rank=rank, shard_world=world,
-              loop_min_blocks=args.min_blocks, chunks=args.chunks)
+              loop_min_blocks=args.min_blocks, chunks=args.chunks, shade_batch=args.shade_batch)
 
     def step(host_output, stage_timing=False):
         """One frame.  host_output=False: result stays in HBM (device resolve). True: RGB8 image copied to the host."""
@@ -332,6 +332,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--min-blocks", type=int, default=0, help="experiment: occupancy variant of the path-loop kernels (0 = 3x256 threads/SM, 4 = 4x256, 7 = 7x128)")
     ap.add_argument("--chunks", type=int, default=0, help="experiment: work items per pixel of the persistent kernel, compat RNG (0 = default 6, 1 = none)")
+    ap.add_argument("--shade-batch", type=int, default=0, help="experiment: waiting lanes per warp that trigger a shading round (0 = default 12, 1 = at once)")
     ap.add_argument("--max-leaf", type=int, default=0, help="experiment: triangles per BVH8 leaf slot (1..3; 0 = library default)")
     args = ap.parse_args()
     scene, w, h, spp, depth = WORKLOADS[args.workload]

@@ -266,7 +266,7 @@ class Context:
 
     # -- rendering ----------------------------------------------------------------------------
     def render(self, scene, camera, film, spp, max_depth=5, rng_mode=RNG_XORWOW_COMPAT, accumulate=False, shard_mode=SHARD_NONE,
-               shard_rank=0, shard_world=1, pipeline=PIPELINE_DEFAULT, stage_timing=False, count_work=False, sampling_mode=0, loop_iters=0, loop_min_blocks=0, chunks=0):
+               shard_rank=0, shard_world=1, pipeline=PIPELINE_DEFAULT, stage_timing=False, count_work=False, sampling_mode=0, loop_iters=0, loop_min_blocks=0, chunks=0, shade_batch=0):
         o = RenderOpts()
         o.spp, o.max_depth, o.rng_mode, o.sampling_mode = int(spp), int(max_depth), int(rng_mode), int(sampling_mode)
         o.accumulate, o.shard_mode, o.shard_rank, o.shard_world = int(accumulate), int(shard_mode), int(shard_rank), int(shard_world)
@@ -275,6 +275,7 @@ class Context:
         o.reserved[1] = int(loop_iters)
         o.reserved[2] = int(loop_min_blocks)
         o.reserved[3] = int(chunks)
+        o.reserved[4] = int(shade_batch)
         _check(lib().ptx_render(self._h, scene._h, C.byref(camera), film._h, C.byref(o)), self._h)
         return self.render_stats()
 

@@ -676,6 +676,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
         int want = opts->reserved[3] > 0 ? opts->reserved[3] : 6;
         rp.n_chunks = rp.spp > 0 ? std::min(want, log2spp + 1) : 1;
     }
+    rp.shade_batch = opts->reserved[4] > 0 ? opts->reserved[4] : 12;      // lanes of a warp that must be waiting before it shades
     int key[5] = {w, h, shard_mode, rank, world};
     if (memcmp(key, c->slot_key, sizeof key) != 0) {
         launch_slot_pixels(c->stream, c->ws.slot_pixel, w, h, shard_mode, rank, world, rp.n_owned);

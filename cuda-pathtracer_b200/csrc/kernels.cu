@@ -410,6 +410,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
     PhiloxRng pr; pr.blk = Philox4{0u, 0u, 0u, 0u}; pr.lane = 0;
     float fx = 0.f, fy = 0.f;
     bool alive = false, pending = false, dry = rp.spp <= 0;
+    bool waiting = false;                               // the lane's ray is through, its result not shaded yet
     Traversal tr;
     TravStack<24> stk;
     tr.begin(pv.d, FLT_MAX);
@@ -471,10 +472,17 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
         }
         if (!__any_sync(kFull, alive || pending)) break;
         // ---- extend: one wide-node visit (+ its triangles) per lane
-        bool done = false;
-        if (alive) done = tr.template step<false, 24>(scene, stk, pv.o, pv.d, 1e-4f, nullptr);
+        if (alive && !waiting) waiting = tr.template step<false, 24>(scene, stk, pv.o, pv.d, 1e-4f, nullptr);
         __syncwarp();
-        // ---- shade the lanes whose ray is through
+        // ---- shade in batches: a finished ray waits until enough lanes of the warp are through.  Shading + regeneration
+        //      cost about as much as a node visit and run for the whole warp whenever one lane needs them; on a scene with
+        //      n node visits per ray only 32 / n lanes finish per iteration (C2 21, C3 8, a C5-shaped scene 1), so shading at
+        //      once wastes up to 31 / 32 of that block.  Waiting costs the idle lane's share of the node visits instead; the
+        //      minimum of the two is near `shade_batch` = 12 waiting lanes for all three scenes (fewer when few lanes are alive).
+        const int n_wait = __popc(__ballot_sync(kFull, waiting)), n_alive = __popc(__ballot_sync(kFull, alive));
+        if (n_wait == 0 || n_wait < min(rp.shade_batch, (3 * n_alive + 7) >> 3)) continue;
+        const bool done = waiting;
+        waiting = false;
         bool cont = true;
         if (done) {
             uint32_t prim = tr.best == kMiss ? kMiss : __float_as_uint(ldq(scene.tris + (size_t)tr.best * kTriQuads).w);

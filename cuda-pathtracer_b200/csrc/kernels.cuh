@@ -55,6 +55,7 @@ struct RenderParams {
     uint32_t n_owned;         // pixels owned by this rank
     unsigned long long total_paths;   // philox: n_owned * spp
     uint32_t sample_begin;    // philox sample-range sharding: first global sample index
+    int shade_batch;          // persistent kernel: waiting lanes per warp that trigger a shading round (1 = shade at once)
     int n_chunks;             // persistent kernel, compat RNG: work items per pixel (geometric sample ranges, see k_path_persist)
     unsigned long long seed;
 };

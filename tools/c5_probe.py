@@ -9,6 +9,7 @@ from cuda_pathtracer_b200 import scenegen
 inst = int(sys.argv[1]) if len(sys.argv) > 1 else 4883
 level = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 w, h, spp = [int(x) for x in sys.argv[3:6]] if len(sys.argv) > 5 else (1920, 1080, 16)
+batches = [int(x) for x in sys.argv[6].split(',')] if len(sys.argv) > 6 else [0]
 path = "/tmp/c5.pbrt"
 t = time.time(); n = scenegen.write_c5_pbrt(path, inst, level); t_write = time.time() - t
 with pkg.Context(0) as ctx:
@@ -20,9 +21,10 @@ with pkg.Context(0) as ctx:
     out = {"triangles": n, "write_s": round(t_write, 2), "load_s": round(t_load, 2), "build_ms": st["build_ms"], "nodes": st["n_nodes"], "sah": st["sah_cost"],
            "max_depth": st["max_depth"], "node_GB": st["node_bytes"] / 1e9, "tri_GB": st["triangle_bytes"] / 1e9,
            "host_peak_GB": resource.getrusage(resource.RUSAGE_SELF).ru_maxrss / 1e6}
-    for rng in (0, 1):
+    for sb in batches:
+      for rng in (0, 1):
         for rep in range(2):
-            r = ctx.render(scene, cam, film, spp=spp, max_depth=8, rng_mode=rng)
-        out[f"Gseg_s_rng{rng}"] = round(r["segments"] / r["render_ms"] / 1e6, 3); out[f"seg_per_path_rng{rng}"] = r["segments"] / r["paths"]
+            r = ctx.render(scene, cam, film, spp=spp, max_depth=8, rng_mode=rng, shade_batch=sb)
+        out[f"Gseg_s_rng{rng}_sb{sb}"] = round(r["segments"] / r["render_ms"] / 1e6, 3); out[f"seg_per_path_rng{rng}"] = r["segments"] / r["paths"]
     film.write(os.path.join(ROOT, "gpurun_out", "c5.png"))
     print(json.dumps(out))
