@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libptx.so")
+LIB_PATH = os.environ.get("PTX_LIB") or os.path.join(HERE, "libptx.so")      # PTX_LIB: experimental builds (tools/)
 
 RNG_XORWOW_COMPAT, RNG_PHILOX = 0, 1
 SHARD_NONE, SHARD_TILES, SHARD_SAMPLES = 0, 1, 2
