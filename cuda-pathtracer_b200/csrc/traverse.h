@@ -134,7 +134,7 @@ struct Traversal {
         const uint32_t magic = s.byte_magic;
         (void)magic;
 
-        if (ng_y > 0x00FFFFFFu) {
+        {   // on entry the node group always holds a pending inner child (begin() / the pop below guarantee it)
             uint32_t imask = ng_y & 0xFFu;
             uint32_t bit = hi_bit(ng_y);
             ng_y &= ~(1u << bit);
@@ -216,9 +216,6 @@ struct Traversal {
             tg_y = hitmask & 0x00FFFFFFu;
             // (Software prefetch of the hit triangles / the nearest child with prefetch.global.L1 or .L2 was measured on C3
             //  and HALVED throughput -- 3.9 -> 1.7 / 1.5 G segments/s -- so the records are simply loaded when needed.)
-        } else {
-            tg_x = ng_x; tg_y = ng_y;        // a postponed triangle group popped from the stack
-            ng_x = 0; ng_y = 0;
         }
 
         while (tg_y != 0) {
