@@ -133,7 +133,7 @@ def run_ours(args, scene_path, w, h, spp, depth):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     rng_mode = pkg.RNG_PHILOX if args.rng == "philox" else pkg.RNG_XORWOW_COMPAT
-    pipeline = {"fused": pkg.PIPELINE_FUSED, "wavefront": pkg.PIPELINE_WAVEFRONT, "loop": pkg.PIPELINE_LOOP, "persist": pkg.PIPELINE_PERSIST}[args.pipeline]
+    pipeline = {"fused": pkg.PIPELINE_FUSED, "wavefront": pkg.PIPELINE_WAVEFRONT, "loop": pkg.PIPELINE_LOOP, "persist": pkg.PIPELINE_PERSIST, "cta": pkg.PIPELINE_CTA}[args.pipeline]
     shard_mode = pkg.SHARD_NONE if world == 1 else (pkg.SHARD_SAMPLES if rng_mode == pkg.RNG_PHILOX else pkg.SHARD_TILES)
 
     dist = torch = None
@@ -326,7 +326,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rng", default="compat", choices=["compat", "philox"])
-    ap.add_argument("--pipeline", default="persist", choices=["persist", "loop", "fused", "wavefront"])
+    ap.add_argument("--pipeline", default="persist", choices=["persist", "loop", "fused", "wavefront", "cta"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override spp (reduced runs are NOT the headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -663,7 +663,8 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     rp.n_slots = rng_mode == PTX_RNG_XORWOW_COMPAT ? rp.n_owned : (uint32_t)std::min<unsigned long long>(rp.total_paths, kPhiloxPool);
 
     const int pipeline = opts->pipeline == 0 ? 3 : opts->pipeline;     // 0 = default = the persistent kernel
-    const bool persist = pipeline == 3;
+    const bool cta_wave = pipeline == 5;                               // CTA wavefront: same items and hand-off as the persistent kernel
+    const bool persist = pipeline == 3 || cta_wave;
     int rc = ensure_pixmap(c, rp.n_owned, persist ? (uint32_t)w * (uint32_t)h : 0u);
     if (rc == PTX_OK && !persist) rc = ensure_wave_capacity(c, rp.n_slots, rp.n_owned);
     if (rc != PTX_OK) return rc;
@@ -705,7 +706,8 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     PTX_CUDA(c, cudaEventRecord(c->ev0, c->stream));
     if (persist) {      // one launch for the whole frame: items are pulled from CTR_NEXT_PATH, nothing else to drive
         if (rng_mode == PTX_RNG_XORWOW_COMPAT && rp.n_owned) PTX_CUDA(c, cudaMemsetAsync(c->ws.progress, 0, (size_t)w * h * sizeof(uint32_t), c->stream));
-        launch_path_persist(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->reserved[2]);
+        if (cta_wave) launch_path_cta(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->reserved[2]);
+        else launch_path_persist(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->reserved[2]);
         PTX_CUDA(c, cudaGetLastError());
         st.kernel_launches++;
         live0 = 0;

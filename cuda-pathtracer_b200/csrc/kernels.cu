@@ -533,6 +533,360 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
 }
 
 // ---------------------------------------------------------------------------------------------
+// CTA wavefront (pipeline 5): ONE launch per frame like k_path_persist, but a path is no longer tied to a
+// lane.  A CTA keeps P = BLOCK * PPT paths in SHARED memory (SoA, 4-byte columns) and runs them through four
+// phases per iteration, each phase over a dense list of work so that every warp executes it with (nearly) all
+// 32 lanes:
+//   A  node visits   every traversing path visits ONE BVH8 node (thread t always owns paths t, t + BLOCK, ...:
+//                    the traversal cursor and the stack stay in its registers / local memory); the triangles
+//                    the node hit become (path, triangle) TASKS in a shared queue; a path with nothing left to
+//                    visit goes on the `done` list
+//   B  triangle tests one task per lane, result merged with a 64-bit shared atomicMin on { t bits, ~slot }
+//   C  shading        one finished path per lane (emission, Russian roulette, albedo, cosine sample)
+//   D  regeneration   one ended path per lane: next sample of the pixel / commit + hand-off / fetch of the next
+//                    work item (same items, same chunked hand-off protocol as k_path_persist)
+// k_path_persist ran the same four pieces per LANE and paid for the divergence: on C2 the triangle loop ran
+// 5.0 rounds per iteration for 1.9 tests per lane (lane efficiency 0.33), shading and regeneration at 0.35 /
+// 0.32 (ncu r1i).  Here only the last warp of each list is partly filled.
+// Hit-distance ties between two triangles resolve towards the higher slot (k_path_persist: the first tested);
+// everything else -- arithmetic, draw order, items -- is unchanged, so images match pipelines 0-4 bit for bit
+// except at such ties.
+// ---------------------------------------------------------------------------------------------
+enum : uint32_t { PS_FREE = 0, PS_PENDING = 1, PS_NEW = 2, PS_TRAV = 3, PS_ENDED = 4, PS_DRY = 5 };
+
+template <int P, int CAP>
+struct CtaPaths {
+    float o[3][P], d[3][P];
+    unsigned long long key[P];        // { closest t (float bits), ~triangle slot }: smaller is closer; low word 0 = no hit
+    uint32_t tgx[P];                  // base slot of the triangle group the path's tasks refer to
+    float beta[3][P], L[3][P], acc[3][P];
+    uint32_t depth[P], pixel[P], pxy[P], sample[P], chunk[P], status[P];
+    uint32_t rng[6][P];
+    uint16_t tasks[CAP];              // (path << 5) | bit within the triangle group; 0xFFFF = hole
+    uint16_t done[P], regen[P];
+    uint32_t cnt[2][4];               // [iteration parity][tasks, done, regen, -]
+};
+
+constexpr unsigned long long kKeyInit = 0x7F7FFFFF00000000ull;     // FLT_MAX, no hit
+
+template <int RNG, int BLOCK, int PPT, int MINB>
+__global__ void __launch_bounds__(BLOCK, MINB) k_path_cta(WaveState ws, SceneView scene, FilmView film, CameraView cam, RenderParams rp) {
+    constexpr unsigned kFull = 0xFFFFFFFFu;
+    constexpr int P = BLOCK * PPT;
+    constexpr int CAP = 4 * P;
+    static_assert(P <= 2048, "task encoding holds 11 path bits");
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    CtaPaths<P, CAP>& S = *reinterpret_cast<CtaPaths<P, CAP>*>(smem_raw);
+    const int tid = (int)threadIdx.x, lane = tid & 31;
+    const unsigned lt = (1u << lane) - 1u;
+    const uint32_t n_chunks = RNG == 0 ? (uint32_t)rp.n_chunks : 0u;
+    const unsigned long long n_items = RNG == 0 ? (unsigned long long)rp.n_owned * n_chunks : rp.total_paths;
+    uint32_t nseg = 0, npaths = 0;
+    Traversal tr[PPT];
+    TravStack<24> stk[PPT];
+#pragma unroll
+    for (int i = 0; i < PPT; i++) {
+        S.status[tid + i * BLOCK] = rp.spp > 0 ? PS_FREE : PS_DRY;
+        tr[i].begin(v3(0.f, 0.f, 0.f), FLT_MAX);
+    }
+    if (tid < 8) (&S.cnt[0][0])[tid] = 0u;
+    __syncthreads();
+
+    for (uint32_t it = 0;; it++) {
+        uint32_t* cnt = S.cnt[it & 1u];
+        // ================= A: one node visit per traversing path =================
+        bool any_live = false;
+#pragma unroll
+        for (int i = 0; i < PPT; i++) {
+            const int p = tid + i * BLOCK;
+            const uint32_t st = S.status[p];
+            any_live |= st != PS_DRY;
+            uint32_t tg_x = 0, tg_y = 0;
+            bool fin = false;
+            vec3 o = v3(0.f, 0.f, 0.f), d = o;
+            if (st == PS_NEW || st == PS_TRAV) {
+                o = v3(S.o[0][p], S.o[1][p], S.o[2][p]);
+                d = v3(S.d[0][p], S.d[1][p], S.d[2][p]);
+                if (st == PS_NEW) { tr[i].begin(d, FLT_MAX); S.status[p] = PS_TRAV; }
+                tr[i].closest = __uint_as_float(reinterpret_cast<const uint32_t*>(&S.key[p])[1]);
+                tr[i].template visit<false>(scene, stk[i], o, d, 1e-4f, tg_x, tg_y, nullptr);
+                fin = tr[i].next_group(stk[i]);
+            }
+            __syncwarp();
+            // triangle tasks: warp prefix sum of the per-lane counts, one shared atomic per warp
+            const uint32_t n = (uint32_t)__popc(tg_y);
+            uint32_t incl = n;
+#pragma unroll
+            for (int k = 1; k < 32; k <<= 1) {
+                uint32_t v = __shfl_up_sync(kFull, incl, k);
+                if (lane >= k) incl += v;
+            }
+            const uint32_t total = __shfl_sync(kFull, incl, 31);
+            if (total) {
+                uint32_t base = 0;
+                if (lane == 31) base = atomicAdd(&cnt[0], total);
+                base = __shfl_sync(kFull, base, 31);
+                uint32_t pos = base + incl - n;
+                if (n) {
+                    if (pos + n <= (uint32_t)CAP) {
+                        S.tgx[p] = tg_x;
+                        const uint32_t tag = (uint32_t)p << 5;
+                        while (tg_y) {
+                            uint32_t bit = hi_bit(tg_y);
+                            tg_y &= ~(1u << bit);
+                            S.tasks[pos++] = (uint16_t)(tag | bit);
+                        }
+                    } else {
+                        // queue full (a node can hit 24 triangles): test them here, mark the reserved slots as holes
+                        for (; pos < (uint32_t)CAP; pos++) S.tasks[pos] = (uint16_t)0xFFFFu;
+                        unsigned long long k = S.key[p];
+                        float c = __uint_as_float((uint32_t)(k >> 32));
+                        uint32_t best = ~(uint32_t)k;
+                        while (tg_y) {
+                            uint32_t bit = hi_bit(tg_y);
+                            tg_y &= ~(1u << bit);
+                            uint32_t ti = tg_x + bit;
+                            const f32x4* tp = scene.tris + (size_t)ti * kTriQuads;
+                            f32x4 a = ldq(tp + 0), b = ldq(tp + 1), e = ldq(tp + 2);
+                            if (intersect_tri(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(e.x, e.y, e.z), o, d, 1e-4f, c)) best = ti;
+                        }
+                        S.key[p] = ((unsigned long long)__float_as_uint(c) << 32) | (unsigned long long)(~best);
+                    }
+                }
+            }
+            const unsigned mfin = __ballot_sync(kFull, fin);
+            if (mfin) {
+                uint32_t base = 0;
+                const int leader = __ffs(mfin) - 1;
+                if (lane == leader) base = atomicAdd(&cnt[1], (uint32_t)__popc(mfin));
+                base = __shfl_sync(kFull, base, leader);
+                if (fin) S.done[base + (uint32_t)__popc(mfin & lt)] = (uint16_t)p;
+            }
+            const bool idle = st == PS_FREE || st == PS_PENDING;
+            const unsigned midle = __ballot_sync(kFull, idle);
+            if (midle) {
+                uint32_t base = 0;
+                const int leader = __ffs(midle) - 1;
+                if (lane == leader) base = atomicAdd(&cnt[2], (uint32_t)__popc(midle));
+                base = __shfl_sync(kFull, base, leader);
+                if (idle) S.regen[base + (uint32_t)__popc(midle & lt)] = (uint16_t)p;
+            }
+        }
+        if (!__syncthreads_or(any_live ? 1 : 0)) break;
+
+        // ================= B: one triangle test per task =================
+        {
+            const uint32_t nt = min(cnt[0], (uint32_t)CAP);
+            for (uint32_t k = (uint32_t)tid; k < nt; k += BLOCK) {
+                const uint32_t tk = S.tasks[k];
+                if (tk == 0xFFFFu) continue;
+                const int p = (int)(tk >> 5);
+                const uint32_t ti = S.tgx[p] + (tk & 31u);
+                const f32x4* tp = scene.tris + (size_t)ti * kTriQuads;
+                f32x4 a = ldq(tp + 0), b = ldq(tp + 1), e = ldq(tp + 2);
+                vec3 o = v3(S.o[0][p], S.o[1][p], S.o[2][p]);
+                vec3 d = v3(S.d[0][p], S.d[1][p], S.d[2][p]);
+                float c = __uint_as_float(reinterpret_cast<const uint32_t*>(&S.key[p])[1]);
+                if (intersect_tri(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(e.x, e.y, e.z), o, d, 1e-4f, c))
+                    atomicMin(&S.key[p], ((unsigned long long)__float_as_uint(c) << 32) | (unsigned long long)(~ti));
+            }
+        }
+        __syncthreads();
+
+        // ================= C: shade the paths whose traversal is complete =================
+        {
+            const uint32_t nd = cnt[1];
+            for (uint32_t k0 = (uint32_t)(tid & ~31); k0 < nd; k0 += BLOCK) {
+                const uint32_t k = k0 + (uint32_t)lane;
+                const bool act = k < nd;
+                bool ended = false;
+                int p = 0;
+                if (act) {
+                    p = (int)S.done[k];
+                    const unsigned long long key = S.key[p];
+                    const float t = __uint_as_float((uint32_t)(key >> 32));
+                    const uint32_t best = ~(uint32_t)key;
+                    const uint32_t prim = best == kMiss ? kMiss : __float_as_uint(ldq(scene.tris + (size_t)best * kTriQuads).w);
+                    PathVertex pv;
+                    pv.o = v3(S.o[0][p], S.o[1][p], S.o[2][p]);
+                    pv.d = v3(S.d[0][p], S.d[1][p], S.d[2][p]);
+                    pv.beta = v3(S.beta[0][p], S.beta[1][p], S.beta[2][p]);
+                    pv.depth = (int)S.depth[p];
+                    vec3 L = v3(S.L[0][p], S.L[1][p], S.L[2][p]);
+                    nseg++;
+                    bool cont;
+                    if (RNG == 0) {
+                        XorwowRng xr;
+                        xr.st = Xorwow{S.rng[0][p], S.rng[1][p], S.rng[2][p], S.rng[3][p], S.rng[4][p], S.rng[5][p]};
+                        cont = shade_bounce(scene, rp.shade, pv, prim, t, xr, L);
+                        if (prim != kMiss) {
+                            S.rng[0][p] = xr.st.v0; S.rng[1][p] = xr.st.v1; S.rng[2][p] = xr.st.v2;
+                            S.rng[3][p] = xr.st.v3; S.rng[4][p] = xr.st.v4; S.rng[5][p] = xr.st.d;
+                        }
+                    } else {
+                        PhiloxRng pr;
+                        pr.seek(((unsigned long long)S.sample[p] << 32) | S.pixel[p], 1u + (uint32_t)pv.depth, rp.seed);
+                        cont = shade_bounce(scene, rp.shade, pv, prim, t, pr, L);
+                    }
+                    S.L[0][p] = L.x; S.L[1][p] = L.y; S.L[2][p] = L.z;
+                    if (cont) {
+                        S.o[0][p] = pv.o.x; S.o[1][p] = pv.o.y; S.o[2][p] = pv.o.z;
+                        S.d[0][p] = pv.d.x; S.d[1][p] = pv.d.y; S.d[2][p] = pv.d.z;
+                        S.beta[0][p] = pv.beta.x; S.beta[1][p] = pv.beta.y; S.beta[2][p] = pv.beta.z;
+                        S.depth[p] = (uint32_t)pv.depth;
+                        S.key[p] = kKeyInit;
+                        S.status[p] = PS_NEW;
+                    } else {
+                        S.status[p] = PS_ENDED;
+                        ended = true;
+                    }
+                }
+                const unsigned mend = __ballot_sync(kFull, ended);
+                if (mend) {
+                    uint32_t base = 0;
+                    const int leader = __ffs(mend) - 1;
+                    if (lane == leader) base = atomicAdd(&cnt[2], (uint32_t)__popc(mend));
+                    base = __shfl_sync(kFull, base, leader);
+                    if (ended) S.regen[base + (uint32_t)__popc(mend & lt)] = (uint16_t)p;
+                }
+            }
+        }
+        __syncthreads();
+
+        // ================= D: ended / idle paths: next sample, commit + hand-off, next work item =================
+        {
+            const uint32_t nr = cnt[2];
+            if (tid < 4) S.cnt[(it + 1u) & 1u][tid] = 0u;      // the other counter set is idle during this phase
+            for (uint32_t k0 = (uint32_t)(tid & ~31); k0 < nr; k0 += BLOCK) {
+                const uint32_t k = k0 + (uint32_t)lane;
+                const bool act = k < nr;
+                const int p = act ? (int)S.regen[k] : 0;
+                uint32_t st = act ? S.status[p] : PS_DRY;
+                bool want = st == PS_FREE;
+                if (st == PS_ENDED) {
+                    npaths++;
+                    const uint32_t pixel = S.pixel[p];
+                    const vec3 L = v3(S.L[0][p], S.L[1][p], S.L[2][p]);
+                    if (RNG == 0) {
+                        const uint32_t chunk = S.chunk[p];
+                        const uint32_t sample = S.sample[p] + 1u;
+                        const vec3 acc = v3(S.acc[0][p], S.acc[1][p], S.acc[2][p]) + L;
+                        XorwowRng xr;
+                        xr.st = Xorwow{S.rng[0][p], S.rng[1][p], S.rng[2][p], S.rng[3][p], S.rng[4][p], S.rng[5][p]};
+                        if (sample < (chunk + 1u == n_chunks ? (uint32_t)rp.spp : (uint32_t)rp.spp - ((uint32_t)rp.spp >> (chunk + 1u)))) {
+                            const uint32_t pxy = S.pxy[p];
+                            float ju = xr.next(), jv = xr.next();
+                            PathVertex pv;
+                            start_path_xy(cam, (float)(int)(pxy & 0xFFFFu), (float)(int)(pxy >> 16), ju, jv, pv);
+                            S.o[0][p] = pv.o.x; S.o[1][p] = pv.o.y; S.o[2][p] = pv.o.z;
+                            S.d[0][p] = pv.d.x; S.d[1][p] = pv.d.y; S.d[2][p] = pv.d.z;
+                            S.beta[0][p] = 1.0f; S.beta[1][p] = 1.0f; S.beta[2][p] = 1.0f;
+                            S.depth[p] = 0u;
+                            S.L[0][p] = 0.f; S.L[1][p] = 0.f; S.L[2][p] = 0.f;
+                            S.acc[0][p] = acc.x; S.acc[1][p] = acc.y; S.acc[2][p] = acc.z;
+                            S.sample[p] = sample;
+                            S.rng[0][p] = xr.st.v0; S.rng[1][p] = xr.st.v1; S.rng[2][p] = xr.st.v2;
+                            S.rng[3][p] = xr.st.v3; S.rng[4][p] = xr.st.v4; S.rng[5][p] = xr.st.d;
+                            S.key[p] = kKeyInit;
+                            st = PS_NEW;
+                        } else {
+                            film.rngA[pixel] = make_uint4(xr.st.v0, xr.st.v1, xr.st.v2, xr.st.v3);
+                            film.rngB[pixel] = make_uint2(xr.st.v4, xr.st.d);
+                            film.accum[pixel] = make_float4(acc.x, acc.y, acc.z, 0.f);
+                            if (chunk + 1u < n_chunks)                                // release: hand the pixel to whoever holds its next chunk
+                                asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(ws.progress + pixel), "r"(chunk + 1u) : "memory");
+                            want = true;
+                        }
+                    } else {
+                        if (L.x != 0.f || L.y != 0.f || L.z != 0.f) {
+                            float* fa = reinterpret_cast<float*>(film.accum + pixel);
+                            atomicAdd(fa + 0, L.x); atomicAdd(fa + 1, L.y); atomicAdd(fa + 2, L.z);
+                        }
+                        want = true;
+                    }
+                }
+                // ---- fetch: one global atomic per warp
+                const unsigned need = __ballot_sync(kFull, want);
+                if (need) {
+                    unsigned long long base = 0;
+                    const int leader = __ffs(need) - 1;
+                    if (lane == leader) base = atomicAdd(&ws.counters[CTR_NEXT_PATH], (unsigned long long)__popc(need));
+                    base = __shfl_sync(kFull, base, leader);
+                    if (want) {
+                        const unsigned long long item = base + (unsigned long long)__popc(need & lt);
+                        if (item < n_items) {
+                            const uint32_t pixel = ws.slot_pixel[(uint32_t)(item % rp.n_owned)];
+                            const uint32_t px = pixel % (uint32_t)cam.width, py = pixel / (uint32_t)cam.width;
+                            S.pixel[p] = pixel;
+                            S.pxy[p] = px | (py << 16);
+                            if (RNG == 0) {
+                                S.chunk[p] = (uint32_t)(item / rp.n_owned);
+                                st = PS_PENDING;
+                            } else {
+                                const uint32_t sample = (uint32_t)(item / rp.n_owned) + rp.sample_begin;
+                                PhiloxRng pr;
+                                pr.seek(((unsigned long long)sample << 32) | pixel, 0u, rp.seed);
+                                float ju = pr.next(), jv = pr.next();
+                                PathVertex pv;
+                                start_path_xy(cam, (float)(int)px, (float)(int)py, ju, jv, pv);
+                                S.o[0][p] = pv.o.x; S.o[1][p] = pv.o.y; S.o[2][p] = pv.o.z;
+                                S.d[0][p] = pv.d.x; S.d[1][p] = pv.d.y; S.d[2][p] = pv.d.z;
+                                S.beta[0][p] = 1.0f; S.beta[1][p] = 1.0f; S.beta[2][p] = 1.0f;
+                                S.depth[p] = 0u;
+                                S.L[0][p] = 0.f; S.L[1][p] = 0.f; S.L[2][p] = 0.f;
+                                S.sample[p] = sample;
+                                S.key[p] = kKeyInit;
+                                st = PS_NEW;
+                            }
+                        } else st = PS_DRY;
+                    }
+                }
+                // ---- compat: start the chunk once its predecessor has been committed (see k_path_persist)
+                if (RNG == 0 && st == PS_PENDING) {
+                    const uint32_t pixel = S.pixel[p], chunk = S.chunk[p];
+                    bool ready = chunk == 0u;
+                    if (!ready) {
+                        uint32_t seen;
+                        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(ws.progress + pixel) : "memory");
+                        ready = seen == chunk;
+                    }
+                    if (ready) {
+                        uint4 ra; uint2 rb; float4 f;
+                        if (chunk == 0u) { ra = film.rngA[pixel]; rb = film.rngB[pixel]; f = film.accum[pixel]; }
+                        else { ra = __ldcg(film.rngA + pixel); rb = __ldcg(film.rngB + pixel); f = __ldcg(film.accum + pixel); }
+                        XorwowRng xr;
+                        xr.st = Xorwow{ra.x, ra.y, ra.z, ra.w, rb.x, rb.y};
+                        const uint32_t pxy = S.pxy[p];
+                        float ju = xr.next(), jv = xr.next();
+                        PathVertex pv;
+                        start_path_xy(cam, (float)(int)(pxy & 0xFFFFu), (float)(int)(pxy >> 16), ju, jv, pv);
+                        S.o[0][p] = pv.o.x; S.o[1][p] = pv.o.y; S.o[2][p] = pv.o.z;
+                        S.d[0][p] = pv.d.x; S.d[1][p] = pv.d.y; S.d[2][p] = pv.d.z;
+                        S.beta[0][p] = 1.0f; S.beta[1][p] = 1.0f; S.beta[2][p] = 1.0f;
+                        S.depth[p] = 0u;
+                        S.L[0][p] = 0.f; S.L[1][p] = 0.f; S.L[2][p] = 0.f;
+                        S.acc[0][p] = f.x; S.acc[1][p] = f.y; S.acc[2][p] = f.z;
+                        S.sample[p] = (uint32_t)rp.spp - ((uint32_t)rp.spp >> chunk);
+                        S.rng[0][p] = xr.st.v0; S.rng[1][p] = xr.st.v1; S.rng[2][p] = xr.st.v2;
+                        S.rng[3][p] = xr.st.v3; S.rng[4][p] = xr.st.v4; S.rng[5][p] = xr.st.d;
+                        S.key[p] = kKeyInit;
+                        st = PS_NEW;
+                    }
+                }
+                if (act) S.status[p] = st;
+            }
+        }
+        __syncthreads();
+    }
+    nseg = __reduce_add_sync(kFull, nseg);
+    npaths = __reduce_add_sync(kFull, npaths);
+    if (lane == 0) {
+        if (nseg) atomicAdd(&ws.counters[CTR_SEGMENTS], (unsigned long long)nseg);
+        if (npaths) atomicAdd(&ws.counters[CTR_PATHS], (unsigned long long)npaths);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // compact: stable removal of dead slots from the queue.  count -> scan -> scatter -> commit.
 // Each block owns 1024 consecutive queue entries; order is preserved so state accesses stay coalesced.
 // ---------------------------------------------------------------------------------------------
@@ -803,6 +1157,30 @@ void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, con
         if (rng_mode == 0) k_path_persist<0, kBlock, 3><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
         else k_path_persist<1, kBlock, 3><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
     }
+}
+template <int RNG, int BLOCK, int PPT, int MINB>
+static void launch_cta_variant(cudaStream_t st, const WaveState& ws, const SceneView& scene, const FilmView& film, const CameraView& cam,
+                               const RenderParams& rp, int sm_count, unsigned long long items) {
+    constexpr int P = BLOCK * PPT;
+    const size_t smem = sizeof(CtaPaths<P, 4 * P>);
+    auto kern = k_path_cta<RNG, BLOCK, PPT, MINB>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    unsigned g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * MINB, (items + P - 1) / P);
+    kern<<<g, BLOCK, smem, st>>>(ws, scene, film, cam, rp);
+}
+// variant: 0 = 128 threads x 1 path, 8 CTAs / SM (the fastest measured); 1 = 256 threads x 2 paths, 3 CTAs / SM
+void launch_path_cta(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FilmView& film, const CameraView& cam,
+                     const RenderParams& rp, int sm_count, int variant) {
+    if (rp.spp <= 0 || !rp.n_owned) return;
+    const unsigned long long items = rng_mode == 0 ? (unsigned long long)rp.n_owned : rp.total_paths;
+#define PTX_CTA_LAUNCH(B, T, M)                                                                              \
+    do {                                                                                                     \
+        if (rng_mode == 0) launch_cta_variant<0, B, T, M>(st, ws, scene, film, cam, rp, sm_count, items);    \
+        else launch_cta_variant<1, B, T, M>(st, ws, scene, film, cam, rp, sm_count, items);                  \
+    } while (0)
+    if (variant == 1) PTX_CTA_LAUNCH(256, 2, 3);
+    else PTX_CTA_LAUNCH(128, 1, 8);
+#undef PTX_CTA_LAUNCH
 }
 void launch_compact(cudaStream_t st, const WaveState& ws, int q, uint32_t qlen_bound, uint32_t* scratch) {
     if (!qlen_bound) return;

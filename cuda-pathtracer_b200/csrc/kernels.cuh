@@ -74,6 +74,9 @@ void launch_path_loop(cudaStream_t st, int rng_mode, const WaveState& ws, const 
                       const CameraView& cam, const RenderParams& rp, int q, uint32_t qlen_bound, int iters, int min_blocks);
 void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FilmView& film, const CameraView& cam,
                          const RenderParams& rp, int sm_count, int min_blocks);
+// CTA wavefront (pipeline 5): one launch per frame, paths in shared memory, four dense phases per iteration (kernels.cu)
+void launch_path_cta(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FilmView& film, const CameraView& cam,
+                     const RenderParams& rp, int sm_count, int variant);
 // compacts queue[q] -> queue[q^1]; scratch holds per-block counts (>= ceil(qlen_bound/1024)+1 words)
 void launch_compact(cudaStream_t st, const WaveState& ws, int q, uint32_t qlen_bound, uint32_t* scratch);
 void launch_resolve(cudaStream_t st, const FilmView& film, float inv_spp, uint8_t* rgb8, int flip_y);

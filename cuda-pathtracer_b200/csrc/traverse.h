@@ -121,9 +121,12 @@ struct Traversal {
         ng_x = 0; ng_y = 0x80000000u;        // the root as a one-child group
     }
 
-    // returns true when the traversal is complete (closest / best are final)
-    template <bool COUNT, int STACK>
-    PTX_HD bool step(const SceneView& s, TravStack<STACK>& stk, vec3 o, vec3 d, float t_min, TraceCounters* ctr) {
+    // Visit ONE wide node: the nearest pending inner child of the current node group.  Leaves the hit inner children in
+    // (ng_x, ng_y) -- pushing the rest of the old group first -- and returns the hit triangles as (tg_x, tg_y): base slot
+    // and one bit per triangle, nearest first from the top.  step() below and the CTA-wavefront kernel (k_path_cta, which
+    // hands the triangle tests to other lanes) share it.
+    template <bool COUNT, class STK>
+    PTX_HD void visit(const SceneView& s, STK& stk, vec3 o, vec3 d, float t_min, uint32_t& tg_x_out, uint32_t& tg_y_out, TraceCounters* ctr) {
         // octant: bit set where the direction is negative; slot priority = slot ^ octinv
         uint32_t oct = (d.x < 0.0f ? 4u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 1u : 0u);
         uint32_t octinv = 7u - oct;
@@ -217,7 +220,26 @@ struct Traversal {
             // (Software prefetch of the hit triangles / the nearest child with prefetch.global.L1 or .L2 was measured on C3
             //  and HALVED throughput -- 3.9 -> 1.7 / 1.5 G segments/s -- so the records are simply loaded when needed.)
         }
+        tg_x_out = tg_x; tg_y_out = tg_y;
+    }
 
+    // Fetch the next node group from the stack when the current one holds no inner child any more.
+    // Returns true when the traversal is complete (nothing left to visit).
+    template <class STK>
+    PTX_HD bool next_group(STK& stk) {
+        if (ng_y <= 0x00FFFFFFu) {
+            if (sp == 0) return true;
+            sp--;
+            ng_x = stk.x[sp]; ng_y = stk.y[sp];
+        }
+        return false;
+    }
+
+    // returns true when the traversal is complete (closest / best are final)
+    template <bool COUNT, int STACK>
+    PTX_HD bool step(const SceneView& s, TravStack<STACK>& stk, vec3 o, vec3 d, float t_min, TraceCounters* ctr) {
+        uint32_t tg_x, tg_y;
+        visit<COUNT>(s, stk, o, d, t_min, tg_x, tg_y, ctr);
         while (tg_y != 0) {
             uint32_t bit = hi_bit(tg_y);
             tg_y &= ~(1u << bit);
@@ -228,17 +250,12 @@ struct Traversal {
             if (intersect_tri(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), o, d, t_min, closest)) best = ti;
         }
 
-        if (ng_y <= 0x00FFFFFFu) {
-            if (sp == 0) return true;
-            sp--;
-            ng_x = stk.x[sp]; ng_y = stk.y[sp];
-        }
+        return next_group(stk);
         // (Prefetching the node the next step will visit -- prefetch.global.L2 or .L1 on its two cache lines, issued here --
         //  was measured too: C3 6.9 -> 6.2 G, C2 17.6 -> 15.1 G, the C5-shaped scene 1.26 -> 0.86 G.  Like the triangle
         //  prefetch above it only costs; the warps already in flight hide what latency can be hidden.
         //  Staging the next node in a per-lane shared-memory slot with cp.async + wait_group was bit-identical and also slower:
         //  C3 6.9 -> 6.6 G, C2 17.6 -> 16.5 G, C5-shaped 1.26 -> 1.19 G.)
-        return false;
     }
 };
 

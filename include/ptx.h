@@ -175,7 +175,9 @@ typedef struct {
                                      through the film, so the frame's tail is one small chunk, not one pixel.
                                  Cross-checks (bit-identical images): 4 = wavefront (raygen / extend / shade / compact kernels),
                                  1 = fused bounce kernel (one launch per bounce), 2 = path loop with a slot queue (state in
-                                 registers for reserved[1] bounces per launch).
+                                 registers for reserved[1] bounces per launch), 5 = CTA wavefront (paths in shared memory, four
+                                 dense phases per iteration: node visits, triangle tasks, shading, regeneration; identical
+                                 except at exact hit-distance ties; measured slower than 3, kept as an experiment).
                                  reserved[2] = 1 / 2 / 4 / 7 select other residency builds of 2 and 3 (CTAs per SM) */
     int32_t reserved[5];
 } ptx_render_opts;
