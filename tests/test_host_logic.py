@@ -369,3 +369,28 @@ def test_pbrt_loader_generated_instanced_scene(pkg, tmp_path):
         assert hashlib.sha256(a.tobytes()).digest() == g["c5_small_" + k + "_sha256"].tobytes(), k
     mir = pkg.parse_scene_file(path, mirror_from_mtl=True)
     assert (mir["material_type"] == 1).sum() == 4 * 1280          # instances 0, 7, 14, 21 use the mirror definition
+
+
+# ---- C++ shim in the reference's vocabulary (include/ptx/compat.hpp) + headless render loop (examples/) -------------
+def test_cpp_compat_shim_builds_and_mirrors_sensor(pkg, built):
+    """examples/render_loop.cpp is written only against include/ptx/compat.hpp (Sensor, RenderState, SceneState,
+    renderFrame with the reference's names).  It must compile and link against libptx.so, its Sensor must reproduce the
+    reference camera (sensor.h:38-67) bit for bit, and without a GPU the loop must fail loudly (no CPU rendering path)."""
+    import subprocess
+    exe = built.build_example()
+    r = subprocess.run([exe, "--camera", "1920", "1080"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    vals = np.array([float(x) for x in r.stdout.split()], np.float32)
+    c = pkg.default_camera(1920, 1080)
+    want = np.array(list(c.origin) + list(c.lower_left_corner) + list(c.horizontal) + list(c.vertical) + [c.radius], np.float32)
+    assert np.array_equal(bits(vals), bits(want))          # %.9g round-trips a float32
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except Exception:
+        has_gpu = False
+    if not has_gpu:
+        r = subprocess.run([exe, os.path.join(SCENES, "cbox.obj"), "32", "32", "1", "1", "-"], capture_output=True, text=True)
+        assert r.returncode == 3 and "no CPU path" in r.stderr
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 2 and "usage" in r.stderr
