@@ -8,6 +8,7 @@
  *
  * Build: gcc -O2 -ffp-contract=off -fopenmp -shared -fPIC pt_oracle.c -lm   (oracle/Makefile)
  */
+#define _GNU_SOURCE   /* sincosf */
 #include "pt_oracle.h"
 #include <ctype.h>
 #include <float.h>
@@ -238,7 +239,7 @@ pto_scene* pto_scene_new(const pto_prim* prims, int n) {
     if (n > 0) build_rec(s, 0, n);
     return s;
 }
-void pto_scene_free(pto_scene* s) { if (!s) return; free(s->prims); free(s->nodes); free(s->idx); free(s); }
+void pto_scene_free(pto_scene* s) { if (!s) return; free(s->prims); free(s->nodes); free(s->idx); free(s->guide); free(s); }
 int pto_scene_num_prims(const pto_scene* s) { return s->n_prims; }
 int pto_scene_num_nodes(const pto_scene* s) { return s->n_nodes; }
 const pto_prim* pto_scene_prims(const pto_scene* s) { return s->prims; }
@@ -581,7 +582,159 @@ static v3 sample_cosine_hemisphere(v3 n, pto_xorwow* rng) {
     }
     return vunit(vadd(vadd(vscale(x, tangent), vscale(y, bitangent)), vscale(z, n)));
 }
+/* ============================================================================================ */
+/* Grid (rendering/grid.h), PrecomputedCDF (render_config.h:27-34), sampleMIS (integrator.h:112-166)   */
+/* M_PI is the DOUBLE constant of <math.h> here: grid.h:22-24's float fallback never triggers on Linux, */
+/* so every product with M_PI below is evaluated in double and rounded on assignment, as in the C++.    */
+/* ============================================================================================ */
+#define G_RES 16
+#define G_SIZE 256
+#define G_HALF 8
+#define G_INV_RES (1.0f / G_RES)
+#define G_INV_HALF (1.0f / G_HALF)
+#define G_D_THETA ((M_PI * 0.5f) / G_HALF)
+#define G_D_PHI (2.0f * M_PI / G_RES)
+typedef struct {
+    float pdf[G_SIZE], row_sums[G_HALF], marginal_cdf[G_HALF], row_cdfs[G_SIZE];
+    float total_weight;
+    int is_valid;
+} cdf_t;
+
+static void build_cdf(const float* rgb, cdf_t* c) {       /* initFromRadiosity + buildCDFs, grid.h:62-137 */
+    for (int i = 0; i < G_SIZE; i++)
+        c->pdf[i] = 0.2126f * rgb[3 * i] + 0.7152f * rgb[3 * i + 1] + 0.0722f * rgb[3 * i + 2];
+    c->total_weight = 0.0f;
+    for (int v = 0; v < G_HALF; v++) {
+        float row_sum = 0.0f;
+        for (int u = 0; u < G_RES; u++) row_sum += c->pdf[v * G_RES + u];
+        c->row_sums[v] = row_sum;
+        c->total_weight += row_sum;
+    }
+    float running = 0.0f;
+    const float inv_total = (c->total_weight > 1e-6f) ? (1.0f / c->total_weight) : 0.0f;
+    for (int v = 0; v < G_HALF; v++) { running += c->row_sums[v]; c->marginal_cdf[v] = running * inv_total; }
+    c->marginal_cdf[G_HALF - 1] = 1.0f;
+    for (int i = 0; i < G_SIZE; i++) c->row_cdfs[i] = ((i % G_RES) + 1) * G_INV_RES;   /* lower rows: precomputeCDFs :563-568; unused by sampling */
+    for (int v = 0; v < G_HALF; v++) {
+        float row_sum = c->row_sums[v];
+        if (row_sum < 1e-6f) {
+            for (int u = 0; u < G_RES; u++) c->row_cdfs[v * G_RES + u] = (u + 1) * G_INV_RES;
+        } else {
+            float running_row = 0.0f;
+            const float inv_row_sum = 1.0f / row_sum;
+            for (int u = 0; u < G_RES; u++) { running_row += c->pdf[v * G_RES + u]; c->row_cdfs[v * G_RES + u] = running_row * inv_row_sum; }
+            c->row_cdfs[v * G_RES + G_RES - 1] = 1.0f;
+        }
+    }
+    c->is_valid = c->total_weight > 1e-6f;
+}
+void pto_scene_set_grids(pto_scene* s, const float* rgb, float mis_bsdf_fraction) {
+    free(s->guide); s->guide = NULL;
+    s->mis_bsdf_fraction = mis_bsdf_fraction;
+    if (!rgb) return;
+    cdf_t* c = (cdf_t*)malloc(sizeof(cdf_t) * (size_t)(s->n_prims > 0 ? s->n_prims : 1));
+    for (int p = 0; p < s->n_prims; p++) build_cdf(rgb + (size_t)p * G_SIZE * 3, &c[p]);
+    s->guide = c;
+}
+void pto_scene_get_cdf(const pto_scene* s, int prim, float* out) {
+    const cdf_t* c = &((const cdf_t*)s->guide)[prim];
+    memcpy(out, c->pdf, sizeof c->pdf); memcpy(out + 256, c->row_sums, sizeof c->row_sums);
+    memcpy(out + 264, c->marginal_cdf, sizeof c->marginal_cdf); memcpy(out + 272, c->row_cdfs, sizeof c->row_cdfs);
+    out[528] = c->total_weight; out[529] = (float)c->is_valid;
+}
+static void build_frame(v3 n, v3* t, v3* b) {             /* grid.h:300-309 */
+    if (n.e[2] < -0.9999999f) { *t = V(0.0f, -1.0f, 0.0f); *b = V(-1.0f, 0.0f, 0.0f); return; }
+    const float a = 1.0f / (1.0f + n.e[2]);
+    const float c = -n.e[0] * n.e[1] * a;
+    *t = V(1.0f - n.e[0] * n.e[0] * a, c, -n.e[0]);
+    *b = V(c, 1.0f - n.e[1] * n.e[1] * a, -n.e[1]);
+}
+static int linear_search_cdf(const float* cdf, int size, float xi) {   /* grid.h:248-255 */
+    xi = fminf(fmaxf(xi, 0.0f), 0.999999f);
+    for (int i = 0; i < size; i++) if (xi < cdf[i]) return i;
+    return size - 1;
+}
+static float pdf_for_cell(const cdf_t* c, int theta_idx, int phi_idx) {   /* grid.h:258-274 */
+    float cell_value = c->pdf[theta_idx * G_RES + phi_idx];
+    if (cell_value < 1e-8f) return 1e-6f;
+    float cell_prob = cell_value / fmaxf(c->total_weight, 1e-6f);
+    float theta_center = (theta_idx + 0.5f) * G_INV_HALF * (M_PI * 0.5f);
+    float sin_theta = fmaxf(sinf(theta_center), 0.01f);
+    float solid_angle = sin_theta * G_D_THETA * G_D_PHI;
+    return cell_prob / fmaxf(solid_angle, 1e-6f);
+}
+static v3 grid_sample(const cdf_t* c, v3 normal, pto_xorwow* rng, float* out_pdf) {   /* Grid::sample, grid.h:143-190 (valid grids only) */
+    float xi1 = pto_uniform(rng);
+    float xi2 = pto_uniform(rng);
+    int theta_idx = linear_search_cdf(c->marginal_cdf, G_HALF, xi1);
+    int phi_idx = linear_search_cdf(&c->row_cdfs[theta_idx * G_RES], G_RES, xi2);
+    float jitter_theta = pto_uniform(rng);
+    float jitter_phi = pto_uniform(rng);
+    float theta = (theta_idx + jitter_theta) * G_INV_HALF * (M_PI * 0.5f);
+    theta = fminf(theta, (float)(M_PI * 0.5f - 0.01f));
+    float phi = (phi_idx + jitter_phi) * G_INV_RES * 2.0f * M_PI;
+    float sin_t, cos_t, sin_p, cos_p;
+    sincosf(theta, &sin_t, &cos_t);
+    sincosf(phi, &sin_p, &cos_p);
+    v3 local = V(sin_t * cos_p, sin_t * sin_p, cos_t);
+    v3 tangent, bitangent;
+    build_frame(normal, &tangent, &bitangent);
+    v3 world = vunit(vadd(vadd(vscale(local.e[0], tangent), vscale(local.e[1], bitangent)), vscale(local.e[2], normal)));
+    *out_pdf = pdf_for_cell(c, theta_idx, phi_idx);
+    return world;
+}
+static float grid_compute_pdf(const cdf_t* c, v3 dir, v3 normal) {       /* Grid::computePDF, grid.h:200-216 + worldToSpherical :312-325 */
+    v3 tangent, bitangent;
+    build_frame(normal, &tangent, &bitangent);
+    float lx = vdot(dir, tangent), ly = vdot(dir, bitangent), lz = vdot(dir, normal);
+    float theta = acosf(fminf(fmaxf(lz, -1.0f), 1.0f));
+    float phi = atan2f(ly, lx);
+    if (phi < 0.0f) phi += 2.0f * M_PI;
+    if (theta > M_PI * 0.5f) return 0.0f;
+    int theta_idx = (int)(theta * (2.0f / M_PI) * G_HALF);
+    int phi_idx = (int)(phi * (0.5f / M_PI) * G_RES);
+    theta_idx = theta_idx < 0 ? 0 : (theta_idx > G_HALF - 1 ? G_HALF - 1 : theta_idx);
+    phi_idx = phi_idx < 0 ? 0 : (phi_idx > G_RES - 1 ? G_RES - 1 : phi_idx);
+    return pdf_for_cell(c, theta_idx, phi_idx);
+}
+static float mis_power(float a, float b) {                                /* integrator.h:90-95 */
+    if (a <= 0.0f) return 0.0f;
+    float a2 = a * a, b2 = b * b;
+    return a2 / (a2 + b2);
+}
+static v3 sample_cosine_hemisphere(v3 n, pto_xorwow* rng);
+static v3 sample_mis(const cdf_t* c, v3 normal, pto_xorwow* rng, float* weight, float bsdf_prob) {   /* integrator.h:112-166 */
+    const float BSDF_PROB = fmaxf(fminf(bsdf_prob, 0.99f), 0.01f);
+    const float GRID_PROB = 1.0f - BSDF_PROB;
+    float xi = pto_uniform(rng);
+    v3 dir;
+    float pdf_grid, pdf_bsdf, mis_w;
+    if (xi < BSDF_PROB) {
+        dir = sample_cosine_hemisphere(normal, rng);
+        float cos_theta = fmaxf(vdot(dir, normal), 0.0f);
+        pdf_bsdf = cos_theta / M_PI;
+        pdf_grid = grid_compute_pdf(c, dir, normal);
+        mis_w = mis_power(pdf_bsdf, pdf_grid);
+        *weight = pdf_bsdf > 1e-6f ? mis_w / BSDF_PROB : 0.0f;
+    } else {
+        dir = grid_sample(c, normal, rng, &pdf_grid);
+        float cos_theta = fmaxf(vdot(dir, normal), 0.0f);
+        pdf_bsdf = cos_theta / M_PI;
+        mis_w = mis_power(pdf_grid, pdf_bsdf);
+        if (pdf_grid > 1e-6f && cos_theta > 0.0f) {
+            float w = mis_w * cos_theta / (M_PI * pdf_grid * GRID_PROB);
+            *weight = fminf(w, 10.0f);
+        } else *weight = 0.0f;
+    }
+    return dir;
+}
+
+/* mode: SamplingMode (render_config.h:41-47).  0 = BSDF, 3 = MIS, anything else = pure grid sampling (integrator.h:226-262) */
+static v3 integrate_mode(const pto_scene* s, ray_t r, int max_depth, pto_xorwow* rng, int mode, uint64_t* stats);
 static v3 integrate(const pto_scene* s, ray_t r, int max_depth, pto_xorwow* rng, uint64_t* stats) {
+    return integrate_mode(s, r, max_depth, rng, 0, stats);
+}
+static v3 integrate_mode(const pto_scene* s, ray_t r, int max_depth, pto_xorwow* rng, int mode, uint64_t* stats) {
     v3 L = V(0, 0, 0), beta = V(1.0f, 1.0f, 1.0f);
     for (int depth = 0; depth < max_depth; depth++) {
         hit_t h;
@@ -601,7 +754,20 @@ static v3 integrate(const pto_scene* s, ray_t r, int max_depth, pto_xorwow* rng,
         if (vlen(beta) < 1e-5f) break;
         v3 n = vload(p->n);
         v3 ns = vdot(r.d, n) < 0 ? n : vneg(n);
-        v3 next = sample_cosine_hemisphere(ns, rng);
+        v3 next;
+        const cdf_t* c = (mode != 0 && s->guide) ? &((const cdf_t*)s->guide)[id] : NULL;
+        if (c && c->is_valid) {                                                   /* has_grid && grid.isValid() */
+            float weight;
+            if (mode == 3) next = sample_mis(c, ns, rng, &weight, s->mis_bsdf_fraction);
+            else {
+                float grid_pdf;
+                next = grid_sample(c, ns, rng, &grid_pdf);
+                float cos_theta = fmaxf(vdot(next, ns), 0.0f);
+                weight = cos_theta / (M_PI * fmaxf(grid_pdf, 1e-6f));
+                weight = fminf(fmaxf(weight, 0.0f), 10.0f);
+            }
+            beta = V(beta.e[0] * weight, beta.e[1] * weight, beta.e[2] * weight);   /* operator*=(T), vector.h */
+        } else next = sample_cosine_hemisphere(ns, rng);
         r = make_ray(vadd(h.p, vscale(1e-4f, ns)), next);
     }
     return L;
@@ -650,6 +816,37 @@ void pto_render(const pto_scene* s, const pto_camera* cam, pto_xorwow* rng, int 
                 color = vdiv(color, (float)spp);
                 if (linear) vstore(linear + 3 * pix, color);
                 if (rgb8) pto_tonemap(color.e, 1, rgb8 + 3 * pix);
+            }
+        #pragma omp critical(pto_stats)
+        for (int k = 0; k < 4; k++) tot[k] += loc[k];
+    }
+    if (stats) for (int k = 0; k < 4; k++) stats[k] += tot[k];
+}
+void pto_render_guided(const pto_scene* s, const pto_camera* cam, pto_xorwow* rng, int spp, int max_depth, int mode,
+                       float* linear, uint64_t* stats, int threads) {
+    int w = cam->width, hgt = cam->height;
+    uint64_t tot[4] = {0, 0, 0, 0};
+#ifdef _OPENMP
+    if (threads > 0) omp_set_num_threads(threads); else omp_set_num_threads(omp_get_num_procs());
+#endif
+    #pragma omp parallel
+    {
+        uint64_t loc[4] = {0, 0, 0, 0};
+        #pragma omp for schedule(dynamic, 1)
+        for (int y = 0; y < hgt; y++)
+            for (int x = 0; x < w; x++) {
+                int pix = y * w + x;
+                pto_xorwow* st = &rng[pix];
+                v3 color = V(0, 0, 0);
+                for (int sidx = 0; sidx < spp; sidx++) {
+                    float u = (x + pto_uniform(st)) / (float)w;
+                    float v = (y + pto_uniform(st)) / (float)hgt;
+                    ray_t r = camera_ray(cam, u, v);
+                    color = vadd(color, integrate_mode(s, r, max_depth, st, mode, loc));
+                    loc[1]++;
+                }
+                color = vdiv(color, (float)spp);
+                if (linear) vstore(linear + 3 * pix, color);
             }
         #pragma omp critical(pto_stats)
         for (int k = 0; k < 4; k++) tot[k] += loc[k];

@@ -475,6 +475,64 @@ static int cmd_visibility(int argc, char** argv) {
     printf("{\"cmd\":\"visibility\",\"w\":%d,\"h\":%d,\"spp\":%d}\n", w, h, spp);
     return 0;
 }
+
+// Grid-guided / MIS sampling (integrator.h:226-262, grid.h, sampleMIS integrator.h:112-166) on the host.  The per-primitive
+// 16x16 radiosity grids come from the (out-of-scope) radiosity solver; here they are read from a file
+// ([n_prims][256][3] floats).  scene.precomputed_cdfs stays NULL, so the reference builds each CDF with its OWN code
+// (initGridFromPrimitive -> Grid::initFromRadiosity -> buildCDFs, grid.h:62-137), the same arithmetic SceneState::
+// precomputeCDFs (application_state.h:492-585, needs GL headers) performs once per solve.
+static int cmd_guided(int argc, char** argv) {
+    if (argc < 11) { fprintf(stderr, "guided <scene> <w> <h> <spp> <depth> <mode 0..4> <bsdf_fraction> <grids.f32> <out_prefix> [convert_quads]\n"); return 1; }
+    int w = atoi(argv[3]), h = atoi(argv[4]), spp = atoi(argv[5]), depth = atoi(argv[6]), mode = atoi(argv[7]);
+    float frac = (float)atof(argv[8]);
+    std::string gridf = argv[9], prefix = argv[10];
+    bool cq = argc > 11 && atoi(argv[11]) != 0;
+    HostScene hs;
+    if (!load_scene(argv[2], cq, hs)) return 2;
+    {
+        std::vector<float> g(hs.prims.size() * GRID_SIZE * 3);
+        FILE* f = fopen(gridf.c_str(), "rb");
+        if (!f || fread(g.data(), sizeof(float), g.size(), f) != g.size()) { fprintf(stderr, "bad grid file\n"); return 2; }
+        fclose(f);
+        for (size_t i = 0; i < hs.prims.size(); i++) {
+            Vector3f* dst = hs.prims[i].type == PRIM_TRIANGLE ? hs.prims[i].tri.radiosity_grid : hs.prims[i].quad.radiosity_grid;
+            for (int c = 0; c < GRID_SIZE; c++) dst[c] = Vector3f(g[(i * GRID_SIZE + c) * 3], g[(i * GRID_SIZE + c) * 3 + 1], g[(i * GRID_SIZE + c) * 3 + 2]);
+        }
+    }
+    Sensor cam = make_camera(w, h);
+    size_t npix = (size_t)w * h;
+    Scene scene(hs.prims.data(), (int)hs.prims.size(), hs.nodes.data(), hs.indices.data());
+    scene.mis_bsdf_fraction = frac;
+    std::vector<curandState> rs(npix);
+    for (size_t p = 0; p < npix; p++) curand_init(2023 + p, p, 0, &rs[p]);
+    std::vector<float> linear(npix * 3);
+    #pragma omp parallel for schedule(dynamic, 1)
+    for (int y = 0; y < h; y++)
+        for (int x = 0; x < w; x++) {
+            int pixel_index = y * w + x;
+            curandState* local_rng = &rs[pixel_index];
+            Vector3f color(0.0f, 0.0f, 0.0f);
+            for (int s = 0; s < spp; s++) {                                   // the sample loop of render, integrator.h:382-392
+                float u = (x + curand_uniform(local_rng)) / float(w);
+                float v = (y + curand_uniform(local_rng)) / float(h);
+                Ray ray = cam.get_ray(u, v);
+                Vector3f sample_color(0.0f, 0.0f, 0.0f);
+                integrator(&scene, ray, sample_color, depth, local_rng, (SamplingMode)mode);
+                color += sample_color;
+            }
+            color /= float(spp);
+            linear[pixel_index * 3 + 0] = color.r(); linear[pixel_index * 3 + 1] = color.g(); linear[pixel_index * 3 + 2] = color.b();
+        }
+    write_file(prefix + ".linear.f32", linear.data(), linear.size() * sizeof(float));
+    std::vector<unsigned> st(npix * 6);
+    for (size_t p = 0; p < npix; p++) { for (int k = 0; k < 5; k++) st[p * 6 + k] = rs[p].v[k]; st[p * 6 + 5] = rs[p].d; }
+    write_file(prefix + ".rng.u32", st.data(), st.size() * 4);
+    double mean[3] = {0, 0, 0};
+    for (size_t i = 0; i < npix; i++) for (int c = 0; c < 3; c++) mean[c] += linear[i * 3 + c];
+    printf("{\"cmd\":\"guided\",\"w\":%d,\"h\":%d,\"spp\":%d,\"depth\":%d,\"mode\":%d,\"mean\":[%.9g,%.9g,%.9g]}\n", w, h, spp, depth, mode,
+           mean[0] / npix, mean[1] / npix, mean[2] / npix);
+    return 0;
+}
 #endif
 
 int main(int argc, char** argv) {
@@ -488,6 +546,7 @@ int main(int argc, char** argv) {
     if (c == "dump") return cmd_dump(argc, argv);
     if (c == "occluded") return cmd_occluded(argc, argv);
     if (c == "visibility") return cmd_visibility(argc, argv);
+    if (c == "guided") return cmd_guided(argc, argv);
 #endif
     fprintf(stderr, "unknown command %s\n", c.c_str());
     return 1;

@@ -51,6 +51,9 @@ class Oracle:
         L.pto_tonemap.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.pto_occluded.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.pto_visibility.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.pto_scene_set_grids.argtypes = [C.c_void_p, C.c_void_p, C.c_float]
+        L.pto_render_guided.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        L.pto_scene_get_cdf.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         self.L = L
 
     # scenes ----------------------------------------------------------------------------------
@@ -151,6 +154,26 @@ class Oracle:
         stats = (C.c_uint64 * 4)()
         self.L.pto_render(s, C.byref(cam), rng, spp, max_depth, _p(lin), _p(rgb), stats, threads)
         return lin, rgb, list(stats)
+
+    def set_grids(self, s, grids_rgb, mis_bsdf_fraction=0.5):
+        """grids_rgb: (n_prims, 256, 3) radiosity grids or None (precomputeCDFs, application_state.h:492-585)."""
+        g = None if grids_rgb is None else np.ascontiguousarray(grids_rgb, np.float32)
+        self.L.pto_scene_set_grids(s, None if g is None else _p(g), C.c_float(mis_bsdf_fraction))
+
+    def cdf(self, s, prim):
+        out = np.empty(530, np.float32)
+        self.L.pto_scene_get_cdf(s, int(prim), _p(out))
+        return out
+
+    def render_guided(self, s, w, h, spp, max_depth, mode, cam=None, rng=None, threads=0):
+        """`render` with SamplingMode `mode` (0 BSDF, 3 MIS, 1/2/4 pure grid).  Returns (linear, stats, rng)."""
+        cam = cam or self.camera(w, h)
+        if rng is None:
+            rng = self.render_init(w, h, threads)
+        lin = np.zeros((h, w, 3), np.float32)
+        stats = (C.c_uint64 * 4)()
+        self.L.pto_render_guided(s, C.byref(cam), rng, spp, max_depth, int(mode), _p(lin), stats, threads)
+        return lin, list(stats), rng
 
     def render_init(self, w, h, threads=0):
         rng = (XW * (w * h))()

@@ -134,3 +134,46 @@ def test_oracle_occluded_and_visibility_match_reference(oracle, tag):
         st = np.frombuffer(rng, np.uint32).reshape(h * w, -1)[:, :6]
         assert np.array_equal(st, g[f"{tag}_visrng_{w}x{h}_s{spp}"])
     oracle.free(s)
+
+
+# ---- grid-guided / MIS sampling: oracle pinned to the reference's integrator + Grid ----------
+GUIDED = json.load(open(os.path.join(GOLDEN, "guided_vectors.json")))
+
+
+def synthetic_grids(n_prims):
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden_guided", os.path.join(GOLDEN, "make_golden_guided.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m.synthetic_grids(n_prims)
+
+
+@pytest.mark.parametrize("tag", sorted(GUIDED))
+def test_guided_sampling_matches_reference_bit_for_bit(oracle, tag):
+    """pto_render_guided (Grid::sample / computePDF / sampleMIS / the mode switch of integrator()) against the reference's
+    own code run on the host (tests/golden/make_golden_guided.py): radiance AND final RNG states identical bit for bit,
+    i.e. every draw, every branch and every double promotion of M_PI matches."""
+    m = GUIDED[tag]
+    gold = np.load(os.path.join(GOLDEN, "guided_vectors.npz"))
+    s = oracle.load_obj(os.path.join(SCENES, m["scene"]), m["convert_quads"])
+    oracle.set_grids(s, synthetic_grids(m["n_prims"]), m["bsdf_fraction"])
+    lin, stats, rng = oracle.render_guided(s, m["w"], m["h"], m["spp"], m["depth"], m["mode"])
+    st = np.frombuffer(bytes(rng), np.uint32).reshape(-1, 6)
+    assert np.array_equal(st, gold[tag + "_rng"])
+    assert np.array_equal(bits(lin), bits(gold[tag + "_linear"]))
+    assert stats[1] == m["w"] * m["h"] * m["spp"]
+    oracle.free(s)
+
+
+def test_guided_modes_without_grids_equal_bsdf_sampling(oracle):
+    """No radiosity data => initGridFromPrimitive finds all-zero grids => cosine fallback (integrator.h:258-261): every
+    mode reproduces SAMPLING_BSDF exactly."""
+    s = oracle.load_obj(os.path.join(SCENES, "cbox.obj"), 0)
+    ref, _, _ = oracle.render(s, 24, 20, 4, 5)
+    for mode in (1, 3):
+        lin, _, _ = oracle.render_guided(s, 24, 20, 4, 5, mode)
+        assert np.array_equal(bits(lin), bits(ref))
+    oracle.set_grids(s, np.zeros((oracle.num_prims(s) if hasattr(oracle, "num_prims") else 32, 256, 3), np.float32))
+    lin, _, _ = oracle.render_guided(s, 24, 20, 4, 5, 3)
+    assert np.array_equal(bits(lin), bits(ref))
+    oracle.free(s)
