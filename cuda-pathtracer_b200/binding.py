@@ -15,6 +15,7 @@ LIB_PATH = os.environ.get("PTX_LIB") or os.path.join(HERE, "libptx.so")      # P
 RNG_XORWOW_COMPAT, RNG_PHILOX = 0, 1
 SHARD_NONE, SHARD_TILES, SHARD_SAMPLES = 0, 1, 2
 PIPELINE_DEFAULT, PIPELINE_FUSED, PIPELINE_LOOP, PIPELINE_PERSIST, PIPELINE_WAVEFRONT, PIPELINE_CTA = 0, 1, 2, 3, 4, 5
+SAMPLING_BSDF, SAMPLING_FORMFACTOR, SAMPLING_RADIOSITY, SAMPLING_MIS, SAMPLING_TOPK = 0, 1, 2, 3, 4
 
 
 class PtxError(RuntimeError):
@@ -76,6 +77,7 @@ EXPORTS = [
     "ptx_timer_start", "ptx_timer_stop", "ptx_ctx_stream",
     "ptx_scene_load", "ptx_parse_scene_file", "ptx_free_primitives", "ptx_scene_from_primitives", "ptx_scene_from_triangles",
     "ptx_scene_build_accel", "ptx_scene_stats_get", "ptx_scene_get_primitives", "ptx_scene_destroy",
+    "ptx_scene_set_radiosity_grids", "ptx_scene_get_guide_records",
     "ptx_camera_set", "ptx_camera_update", "ptx_camera_orbit", "ptx_camera_default",
     "ptx_film_create", "ptx_film_reset", "ptx_film_clear", "ptx_film_resolve_rgb8", "ptx_film_read_linear", "ptx_film_write", "ptx_write_png_rgb8",
     "ptx_film_device_buffer", "ptx_film_set_sample_count", "ptx_film_destroy",
@@ -110,6 +112,8 @@ def lib():
         L.ptx_scene_from_triangles.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t,
                                                C.c_void_p, C.c_void_p]
         L.ptx_scene_get_primitives.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        L.ptx_scene_set_radiosity_grids.argtypes = [C.c_void_p, C.c_void_p, C.c_float]
+        L.ptx_scene_get_guide_records.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]
         L.ptx_scene_load.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_void_p]
         L.ptx_parse_scene_file.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ptx_film_write.argtypes = [C.c_void_p, C.c_char_p]
@@ -334,6 +338,19 @@ class Scene:
     def rebuild(self, builder=0, sah_bins=0, max_leaf=0):
         bo = BuildOpts(int(builder), int(sah_bins), int(max_leaf), 0)
         _check(lib().ptx_scene_build_accel(self._h, C.byref(bo)), self.ctx._h)
+
+    def set_radiosity_grids(self, grids_rgb, mis_bsdf_fraction=0.5):
+        """grids_rgb: (n_primitives, 256, 3) float32 radiosity grids (precomputeCDFs input) or None to remove them."""
+        g = None if grids_rgb is None else np.ascontiguousarray(grids_rgb, np.float32)
+        if g is not None and g.size != self.stats()["n_primitives"] * 768:
+            raise ValueError("radiosity grids must hold n_primitives * 256 * 3 floats")
+        _check(lib().ptx_scene_set_radiosity_grids(self._h, None if g is None else _ptr(g), C.c_float(mis_bsdf_fraction)), self.ctx._h)
+
+    def guide_records(self, first=0, n=None):
+        n = self.stats()["n_primitives"] - first if n is None else n
+        out = np.empty((n, 272), np.float32)
+        _check(lib().ptx_scene_get_guide_records(self._h, int(first), int(n), _ptr(out)), self.ctx._h)
+        return out
 
     def primitives(self):
         n = _check(lib().ptx_scene_get_primitives(self._h, None, 0))

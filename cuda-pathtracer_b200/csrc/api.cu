@@ -55,6 +55,7 @@ struct ptx_scene {
     u32x4* d_nodes = nullptr; f32x4* d_tris = nullptr; f32x4* d_prim_shade = nullptr; f32x4* d_materials = nullptr;
     SceneView view{};
     ptx_scene_stats stats{};
+    float* d_guide = nullptr;                    // grid-guided sampling: kGuideFloats floats per primitive (shade.h)
 };
 
 struct ptx_film {
@@ -428,8 +429,41 @@ void ptx_scene_destroy(ptx_scene* s) {
     cudaSetDevice(s->ctx->device);
     cudaStreamSynchronize(s->ctx->stream);
     free_accel(s);
-    cudaFree(s->d_prim_shade); cudaFree(s->d_materials);
+    cudaFree(s->d_prim_shade); cudaFree(s->d_materials); cudaFree(s->d_guide);
     delete s;
+}
+
+// SceneState::precomputeCDFs (application_state.h:492-585) + Scene::mis_bsdf_fraction (scene.h:215)
+int ptx_scene_set_radiosity_grids(ptx_scene* s, const float* rgb_host, float mis_bsdf_fraction) {
+    if (!s) return fail(nullptr, PTX_ERR_INVALID, "ptx_scene_set_radiosity_grids: scene is NULL");
+    ptx_ctx* c = s->ctx;
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+    s->view.mis_bsdf_fraction = mis_bsdf_fraction;
+    if (s->d_guide) { cudaFree(s->d_guide); s->d_guide = nullptr; s->view.guide = nullptr; }
+    if (!rgb_host) return PTX_OK;
+    const size_t n = s->view.n_prims;
+    if (!n) return PTX_OK;
+    float* d_rgb = nullptr;
+    PTX_CUDA(c, cudaMalloc(&d_rgb, n * 768 * sizeof(float)));
+    cudaError_t e = cudaMalloc(&s->d_guide, n * kGuideFloats * sizeof(float));
+    if (e != cudaSuccess) { cudaFree(d_rgb); s->d_guide = nullptr; return cuda_fail(c, e, "cudaMalloc(guide)"); }
+    e = cudaMemcpyAsync(d_rgb, rgb_host, n * 768 * sizeof(float), cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) { launch_build_guide(c->stream, d_rgb, n, s->d_guide); e = cudaGetLastError(); }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d_rgb);
+    if (e != cudaSuccess) { cudaFree(s->d_guide); s->d_guide = nullptr; return cuda_fail(c, e, "guide build"); }
+    s->view.guide = s->d_guide;
+    return PTX_OK;
+}
+int ptx_scene_get_guide_records(const ptx_scene* s, int64_t first, int64_t n, float* out_host) {
+    if (!s || !out_host || first < 0 || n < 0 || (uint64_t)(first + n) > s->view.n_prims) return fail(s ? s->ctx : nullptr, PTX_ERR_INVALID, "ptx_scene_get_guide_records: bad argument");
+    if (!s->d_guide) return fail(s->ctx, PTX_ERR_INVALID, "ptx_scene_get_guide_records: the scene has no radiosity grids");
+    ptx_ctx* c = s->ctx;
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+    PTX_CUDA(c, cudaMemcpy(out_host, s->d_guide + (size_t)first * kGuideFloats, (size_t)n * kGuideFloats * sizeof(float), cudaMemcpyDeviceToHost));
+    return PTX_OK;
 }
 
 
@@ -630,8 +664,13 @@ constexpr uint32_t kPhiloxPool = 1u << 22;   // slots in flight in counter-RNG m
 int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_film* film, const ptx_render_opts* opts) {
     if (!c || !scene || !cam || !film || !opts) return fail(c, PTX_ERR_INVALID, "ptx_render: NULL argument");
     if (scene->ctx != c || film->ctx != c) return fail(c, PTX_ERR_INVALID, "ptx_render: scene/film belong to another context");
-    if (opts->sampling_mode != PTX_SAMPLING_BSDF)
-        return fail(c, PTX_ERR_UNSUPPORTED, "only SAMPLING_BSDF is supported (grid/MIS modes need the radiosity solver)");
+    if (opts->sampling_mode < PTX_SAMPLING_BSDF || opts->sampling_mode > PTX_SAMPLING_TOPK) return fail(c, PTX_ERR_INVALID, "ptx_render: bad sampling_mode");
+    // grid / MIS modes: like the reference they fall back to cosine sampling when the scene carries no radiosity grids
+    const bool guided = opts->sampling_mode != PTX_SAMPLING_BSDF && scene->view.guide != nullptr;
+    if (guided && opts->rng_mode != PTX_RNG_XORWOW_COMPAT)
+        return fail(c, PTX_ERR_UNSUPPORTED, "grid / MIS sampling runs with the reference's per-pixel XORWOW streams only (rng_mode = PTX_RNG_XORWOW_COMPAT)");
+    if (guided && opts->pipeline != 0 && opts->pipeline != 3)
+        return fail(c, PTX_ERR_UNSUPPORTED, "grid / MIS sampling is implemented in the persistent kernel only (pipeline 0 / 3)");
     if (opts->spp < 0) return fail(c, PTX_ERR_INVALID, "ptx_render: spp < 0");
     int rng_mode = opts->rng_mode;
     if (rng_mode != PTX_RNG_XORWOW_COMPAT && rng_mode != PTX_RNG_PHILOX) return fail(c, PTX_ERR_INVALID, "ptx_render: bad rng_mode");
@@ -647,6 +686,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     rp.shade.max_depth = opts->max_depth > 0 ? opts->max_depth : 5;
     rp.shade.rr_start_depth = opts->rr_start_depth > 0 ? opts->rr_start_depth : 3;
     rp.shade.rr_cap = opts->rr_cap > 0.f ? opts->rr_cap : 0.95f;
+    rp.shade.sampling_mode = guided ? opts->sampling_mode : 0;
     rp.seed = film->seed_base;
     int spp_local = opts->spp;
     if (!opts->accumulate) film->sample_base = 0;

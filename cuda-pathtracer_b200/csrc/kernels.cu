@@ -378,6 +378,12 @@ __global__ void __launch_bounds__(kBlock, MINB) k_path_loop(WaveState ws, SceneV
     }
 }
 
+// guide records (shade.h) from per-primitive 16 x 16 RGB radiosity grids: SceneState::precomputeCDFs on the device
+__global__ void __launch_bounds__(kBlock) k_build_guide(const float* __restrict__ rgb, size_t n_prims, float* __restrict__ out) {
+    size_t p = (size_t)blockIdx.x * kBlock + threadIdx.x;
+    if (p < n_prims) build_guide_record(rgb + p * 768, out + p * kGuideFloats);
+}
+
 // ---------------------------------------------------------------------------------------------
 // persistent path loop (pipeline 3): ONE launch per frame, one resident CTA set (SMs x MINB), no path
 // state in memory at all.  A lane pulls a work item from a global counter, carries it to the end in
@@ -391,7 +397,7 @@ __global__ void __launch_bounds__(kBlock, MINB) k_path_loop(WaveState ws, SceneV
 // ends (ncu r1h: lane efficiency 0.53 in the second launch of a 128-spp frame).  Lanes only idle in the
 // tail of the frame, when the counter has run dry.
 // ---------------------------------------------------------------------------------------------
-template <int RNG, int BLOCK, int MINB>
+template <int RNG, int BLOCK, int MINB, bool GUIDED = false>
 __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, SceneView scene, FilmView film, CameraView cam, RenderParams rp) {
     constexpr unsigned kFull = 0xFFFFFFFFu;
     const int lane = (int)(threadIdx.x & 31);
@@ -487,7 +493,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
         if (done) {
             uint32_t prim = tr.best == kMiss ? kMiss : __float_as_uint(ldq(scene.tris + (size_t)tr.best * kTriQuads).w);
             nseg++;
-            if (RNG == 0) cont = shade_bounce(scene, rp.shade, pv, prim, tr.closest, xr, L);
+            if (RNG == 0) cont = shade_bounce<XorwowRng, GUIDED>(scene, rp.shade, pv, prim, tr.closest, xr, L);
             else {
                 pr.seek(((unsigned long long)sample << 32) | pixel, 1u + (uint32_t)pv.depth, rp.seed);
                 cont = shade_bounce(scene, rp.shade, pv, prim, tr.closest, pr, L);
@@ -1147,6 +1153,12 @@ void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, con
     if (min_blocks == 0 && rng_mode == 0 && (unsigned long long)rp.n_owned < 3ull * (unsigned long long)sm_count * 3ull * kBlock) per_sm = 2;
     const int block = min_blocks == 7 ? 128 : kBlock;
     unsigned g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (items + block - 1) / block);
+    if (rng_mode == 0 && rp.shade.sampling_mode != 0 && scene.guide != nullptr) {
+        // grid / MIS sampling (compat RNG only): the instantiation whose shading honours the per-primitive guide records
+        g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * std::min(per_sm, 3), (items + kBlock - 1) / kBlock);
+        k_path_persist<0, kBlock, 3, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+        return;
+    }
     if (per_sm == 4) {
         if (rng_mode == 0) k_path_persist<0, kBlock, 4><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
         else k_path_persist<1, kBlock, 4><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
@@ -1181,6 +1193,10 @@ void launch_path_cta(cudaStream_t st, int rng_mode, const WaveState& ws, const S
     if (variant == 1) PTX_CTA_LAUNCH(256, 2, 3);
     else PTX_CTA_LAUNCH(128, 1, 8);
 #undef PTX_CTA_LAUNCH
+}
+void launch_build_guide(cudaStream_t st, const float* rgb, size_t n_prims, float* out) {
+    if (!n_prims) return;
+    k_build_guide<<<blocks_for(n_prims, kBlock), kBlock, 0, st>>>(rgb, n_prims, out);
 }
 void launch_compact(cudaStream_t st, const WaveState& ws, int q, uint32_t qlen_bound, uint32_t* scratch) {
     if (!qlen_bound) return;

@@ -45,6 +45,9 @@ struct SceneView {
     uint32_t n_nodes, n_tris, n_prims, n_mats;
     // 0x3F800000 (1.0f), read by the kernels as a constant-bank operand of PRMT: see Traversal::step (traverse.h)
     uint32_t byte_magic = 0x3F800000u;   // PRMT source for the byte -> float trick in traverse.h (kept out of the immediate field)
+    // grid-guided sampling (shade.h): kGuideFloats floats per reference primitive, or nullptr; Scene::mis_bsdf_fraction
+    const float* guide = nullptr;
+    float mis_bsdf_fraction = 0.5f;
 };
 
 // Camera in the reference's Sensor terms (rendering/sensor.h:92-95): what get_ray needs.

@@ -27,7 +27,7 @@ typedef enum {
     PTX_ERR_IO = -2,          /* file missing / unreadable / no primitives (loadOBJ returns false) */
     PTX_ERR_CUDA = -3,        /* CUDA runtime error; text in ptx_last_error */
     PTX_ERR_NO_DEVICE = -4,   /* no CUDA device: the product has no CPU path */
-    PTX_ERR_UNSUPPORTED = -5, /* e.g. sampling modes that need the (out-of-scope) radiosity solver */
+    PTX_ERR_UNSUPPORTED = -5, /* a combination of options that is not implemented (e.g. grid sampling with the counter RNG) */
     PTX_ERR_NOMEM = -6
 } ptx_status;
 
@@ -118,6 +118,16 @@ int ptx_scene_build_accel(ptx_scene* scene, const ptx_build_opts* opts);     /* 
 int ptx_scene_stats_get(const ptx_scene* scene, ptx_scene_stats* out);
 int ptx_scene_get_primitives(const ptx_scene* scene, ptx_primitive* out, int64_t capacity);   /* returns the count (>= 0) */
 void ptx_scene_destroy(ptx_scene* scene);
+/* Grid-guided sampling data: SceneState::precomputeCDFs (application_state.h:492-585).  rgb_host = per reference primitive
+ * (ptx_scene_get_primitives numbering) the 16 x 16 RGB grid the radiosity solver leaves in Triangle/Quad::radiosity_grid
+ * (triangle.h:108, quad.h:143; row = theta band, rows 0..7 = upper hemisphere, column = phi band), n_primitives * 256 * 3
+ * floats.  A CUDA kernel turns them into luminance pdf + marginal / conditional CDFs (Grid::initFromRadiosity + buildCDFs,
+ * grid.h:62-137) and ptx_render's grid / MIS sampling modes read them.  The solver itself is outside this library.
+ * NULL removes the data.  mis_bsdf_fraction = Scene::mis_bsdf_fraction (scene.h:215; the reference's default is 0.5). */
+int ptx_scene_set_radiosity_grids(ptx_scene* scene, const float* rgb_host, float mis_bsdf_fraction);
+/* the records built from them, 272 floats per primitive: pdf[8][16], row_cdfs[8][16], marginal_cdf[8], total_weight,
+ * is_valid (as uint32), 6 x padding (parity tests) */
+int ptx_scene_get_guide_records(const ptx_scene* scene, int64_t first, int64_t n, float* out_host);
 
 /* ---- camera: the reference's Sensor (rendering/sensor.h:14-101), same field names ------------ */
 typedef struct {
@@ -156,14 +166,17 @@ void ptx_film_destroy(ptx_film* film);
 
 /* ---- render: renderFrame (application.h:157-216) -> render<<<>>> (integrator.h:371-408) ------- */
 enum { PTX_RNG_XORWOW_COMPAT = 0, PTX_RNG_PHILOX = 1 };
-enum { PTX_SAMPLING_BSDF = 0 };             /* SamplingMode::SAMPLING_BSDF; grid/MIS modes need the radiosity solver */
+/* SamplingMode (rendering/render_config.h:41-47).  integrator.h:226-262: BSDF = cosine lobe; MIS = one-sample MIS between
+ * the hit primitive's grid and the cosine lobe (sampleMIS, integrator.h:112-166); the other three = the grid alone.  Without
+ * grids (ptx_scene_set_radiosity_grids) or on a primitive whose grid is empty every mode falls back to the cosine lobe. */
+enum { PTX_SAMPLING_BSDF = 0, PTX_SAMPLING_FORMFACTOR = 1, PTX_SAMPLING_RADIOSITY = 2, PTX_SAMPLING_MIS = 3, PTX_SAMPLING_TOPK = 4 };
 enum { PTX_SHARD_NONE = 0, PTX_SHARD_TILES = 1, PTX_SHARD_SAMPLES = 2 };
 
 typedef struct {
     int32_t spp;              /* AppConfig::spp */
     int32_t max_depth;        /* reference hard-codes 5 (integrator.h:389); 0 => 5 */
     int32_t rng_mode;         /* PTX_RNG_* ; compat reproduces curand_init(2023+pix, pix, 0) streams */
-    int32_t sampling_mode;    /* PTX_SAMPLING_BSDF only */
+    int32_t sampling_mode;    /* PTX_SAMPLING_*; the grid / MIS modes need rng_mode = PTX_RNG_XORWOW_COMPAT and pipeline 0 / 3 */
     int32_t accumulate;       /* 0: each call is an independent frame like the reference; 1: progressive */
     int32_t shard_mode;       /* PTX_SHARD_* */
     int32_t shard_rank, shard_world;

@@ -49,7 +49,8 @@ struct Vector3f {
     float z() const { return e[2]; }
 };
 
-enum SamplingMode { SAMPLING_BSDF = 0, SAMPLING_GRID = 1, SAMPLING_MIS = 2 };   // rendering/render_config.h
+// rendering/render_config.h:41-47
+enum SamplingMode { SAMPLING_BSDF = 0, SAMPLING_FORMFACTOR = 1, SAMPLING_RADIOSITY = 2, SAMPLING_MIS = 3, SAMPLING_TOPK = 4 };
 
 using Primitive = ptx_primitive;       // one reference Primitive minus its radiosity payload (primitive.h:21-29)
 
@@ -198,6 +199,12 @@ struct SceneState {
         num_primitives = (int)st.n_primitives;
         num_bvh_nodes = (int)st.n_nodes;
         return true;
+    }
+    // SceneState::precomputeCDFs (application_state.h:492-585): the radiosity solver's per-primitive 16 x 16 RGB grids
+    // (Triangle/Quad::radiosity_grid, num_primitives * 256 * 3 floats) become the CDFs the grid / MIS sampling modes read;
+    // mis_bsdf_fraction = Scene::mis_bsdf_fraction (scene.h:215).  nullptr removes them.
+    bool precomputeCDFs(const float* radiosity_grids_rgb, float mis_bsdf_fraction = 0.5f) {
+        return scene && ptx_scene_set_radiosity_grids(scene, radiosity_grids_rgb, mis_bsdf_fraction) == PTX_OK;
     }
     // the host primitive list in the reference's numbering (what the radiosity solver reads as h_primitives)
     int getPrimitives(Primitive* out, int capacity) const { return (int)ptx_scene_get_primitives(scene, out, capacity); }

@@ -113,7 +113,7 @@ void emu_render(const EmuScene* s, const CameraView* cam, int spp, int max_depth
                 uint8_t* rgb8, uint64_t* segments) {
     std::vector<uint32_t> tables((size_t)kXorwowJumps * kXorwowJumpWords);
     xorwow_build_jump_tables(tables.data());
-    ShadeParams sp = {max_depth, 3, 0.95f};
+    ShadeParams sp = {max_depth, 3, 0.95f, 0};
     uint64_t seg = 0;
     g_render_ctr = TraceCounters{0, 0};
     for (int y = 0; y < cam->height; y++)
@@ -140,6 +140,47 @@ void emu_render(const EmuScene* s, const CameraView* cam, int spp, int max_depth
             color = div_scalar(color, (float)spp);
             if (linear) st3(linear + 3 * pix, color);
             if (rgb8) { rgb8[3 * pix] = tonemap_channel(color.x); rgb8[3 * pix + 1] = tonemap_channel(color.y); rgb8[3 * pix + 2] = tonemap_channel(color.z); }
+        }
+    if (segments) *segments = seg;
+}
+
+// grid-guided / MIS modes (shade.h guided_direction) on the CPU: guide records built by build_guide_record from
+// n_prims x 256 x 3 radiosity floats, then the render loop above with shade_bounce<.., GUIDED = true>
+void emu_build_guide(const float* rgb, int64_t n_prims, float* out) {
+    for (int64_t p = 0; p < n_prims; p++) build_guide_record(rgb + p * 768, out + p * kGuideFloats);
+}
+void emu_render_guided(const EmuScene* s, const CameraView* cam, int spp, int max_depth, uint64_t seed_base, int mode, float mis_bsdf_fraction,
+                       const float* guide, float* linear, uint32_t* rng_out, uint64_t* segments) {
+    std::vector<uint32_t> tables((size_t)kXorwowJumps * kXorwowJumpWords);
+    xorwow_build_jump_tables(tables.data());
+    ShadeParams sp = {max_depth, 3, 0.95f, mode};
+    SceneView view = s->view;
+    view.guide = guide; view.mis_bsdf_fraction = mis_bsdf_fraction;
+    uint64_t seg = 0;
+    for (int y = 0; y < cam->height; y++)
+        for (int x = 0; x < cam->width; x++) {
+            int pix = y * cam->width + x;
+            uint32_t st6[6];
+            emu_xorwow_init(seed_base + (uint64_t)pix, (uint64_t)pix, tables.data(), st6);
+            XorwowRng rng; rng.st = Xorwow{st6[0], st6[1], st6[2], st6[3], st6[4], st6[5]};
+            vec3 color = mk3(0, 0, 0);
+            for (int k = 0; k < spp; k++) {
+                float u = (x + rng.next()) / (float)cam->width;
+                float v = (y + rng.next()) / (float)cam->height;
+                PathVertex pv; camera_ray(*cam, u, v, pv.o, pv.d);
+                pv.beta = mk3(1, 1, 1); pv.depth = 0;
+                vec3 L = mk3(0, 0, 0);
+                for (;;) {
+                    float th; seg++;
+                    uint32_t tri = trace_closest<32, false>(view, pv.o, pv.d, 1e-4f, FLT_MAX, th, nullptr);
+                    uint32_t prim = tri == kMiss ? kMiss : f2u(view.tris[(size_t)tri * kTriQuads].w);
+                    if (!shade_bounce<XorwowRng, true>(view, sp, pv, prim, th, rng, L)) break;
+                }
+                color = color + L;
+            }
+            color = div_scalar(color, (float)spp);
+            if (linear) st3(linear + 3 * pix, color);
+            if (rng_out) { uint32_t* o = rng_out + 6 * (size_t)pix; o[0] = rng.st.v0; o[1] = rng.st.v1; o[2] = rng.st.v2; o[3] = rng.st.v3; o[4] = rng.st.v4; o[5] = rng.st.d; }
         }
     if (segments) *segments = seg;
 }

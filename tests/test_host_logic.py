@@ -394,3 +394,60 @@ def test_cpp_compat_shim_builds_and_mirrors_sensor(pkg, built):
         assert r.returncode == 3 and "no CPU path" in r.stderr
     r = subprocess.run([exe], capture_output=True, text=True)
     assert r.returncode == 2 and "usage" in r.stderr
+
+
+# ---- grid-guided / MIS sampling core (shade.h guided_direction, build_guide_record), compiled for the CPU ------------
+def _guided_meta():
+    import json
+    return json.load(open(os.path.join(GOLDEN, "guided_vectors.json")))
+
+
+def _synthetic_grids(n):
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden_guided", os.path.join(GOLDEN, "make_golden_guided.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m.synthetic_grids(n)
+
+
+def test_guide_records_match_reference_cdfs(emu, oracle):
+    """build_guide_record (the body of the k_build_guide kernel) against the oracle's restatement of Grid::initFromRadiosity
+    + buildCDFs, itself pinned through the reference's rendered images: pdf, conditional CDFs, marginal CDF, total weight
+    and validity bit for bit, including empty grids, empty rows and empty cells."""
+    emu.emu_build_guide.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
+    s = oracle.load_obj(os.path.join(SCENES, "cbox.obj"), 0)
+    grids = _synthetic_grids(32)
+    oracle.set_grids(s, grids, 0.5)
+    rec = np.zeros((32, 272), np.float32)
+    emu.emu_build_guide(P(grids), 32, P(rec))
+    for p in range(32):
+        c = oracle.cdf(s, p)                           # pdf[256] row_sums[8] marginal[8] row_cdfs[256] total valid
+        assert np.array_equal(bits(rec[p, 0:128]), bits(c[0:128]))
+        assert np.array_equal(bits(rec[p, 128:256]), bits(c[272:400]))
+        assert np.array_equal(bits(rec[p, 256:264]), bits(c[264:272]))
+        assert bits(rec[p, 264:265])[0] == bits(c[528:529])[0]
+        assert rec[p, 265:266].view(np.uint32)[0] == int(c[529])
+    assert {int(v) for v in rec[:, 265].view(np.uint32)} == {0, 1}
+    oracle.free(s)
+
+
+@pytest.mark.parametrize("tag", sorted(_guided_meta()))
+def test_guided_core_bit_exact_vs_reference(pkg, emu, tag):
+    """The device shading core with grid / MIS sampling, compiled for the host, against the reference's own integrator run
+    on the host (tests/golden/guided_vectors.npz): radiance and final RNG states bit for bit."""
+    emu.emu_build_guide.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
+    emu.emu_render_guided.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_float, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p]
+    m = _guided_meta()[tag]
+    gold = np.load(os.path.join(GOLDEN, "guided_vectors.npz"))
+    s = emu.emu_scene_load(os.path.join(SCENES, m["scene"]).encode(), int(m["convert_quads"]), 0, 3)
+    grids = _synthetic_grids(m["n_prims"])
+    rec = np.zeros((m["n_prims"], 272), np.float32)
+    emu.emu_build_guide(P(grids), m["n_prims"], P(rec))
+    w, h = m["w"], m["h"]
+    cv = cam_view(pkg, w, h)
+    lin = np.zeros((h, w, 3), np.float32); st = np.zeros((h * w, 6), np.uint32); seg = C.c_uint64()
+    emu.emu_render_guided(s, C.byref(cv), m["spp"], m["depth"], 2023, m["mode"], C.c_float(m["bsdf_fraction"]), P(rec), P(lin), P(st), C.byref(seg))
+    assert np.array_equal(st, gold[tag + "_rng"])
+    assert np.array_equal(bits(lin), bits(gold[tag + "_linear"]))
+    emu.emu_scene_free(s)
