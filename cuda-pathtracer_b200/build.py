@@ -1,4 +1,4 @@
-"""Build recipe for libptx.so (the C-ABI library) -- explicit nvcc for sm_100a, built in-tree.
+"""Build recipe for libptx.so (the C-ABI library) -- explicit nvcc for sm_100a (one object per source, then a link), built in-tree.
 
 `python cuda-pathtracer_b200/build.py` or `__graft_entry__.build()`.
 """
@@ -27,27 +27,48 @@ def _newer_than_lib(paths):
     return any(os.path.getmtime(p) > t for p in paths)
 
 
+def _compile_one(nvcc, src, obj, verbose):
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas=-v"] if verbose else []) + ["-c", "-o", obj, src]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    return src, r
+
+
 def build_lib(force=False, verbose=False):
+    """One object per source (compiled in parallel, rebuilt only when the source or any header is newer), then one link."""
+    from concurrent.futures import ThreadPoolExecutor
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     srcs = [os.path.join(CSRC, s) for s in CUDA_SOURCES + HOST_SOURCES if os.path.exists(os.path.join(CSRC, s))]
-    deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
-    deps.append(os.path.join(HERE, "..", "include", "ptx.h"))
-    if not force and not _newer_than_lib(deps):
+    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
+    headers.append(os.path.join(HERE, "..", "include", "ptx.h"))
+    if not force and not _newer_than_lib(srcs + headers):
         return LIB
     if not os.path.exists(nvcc):
         if os.path.exists(LIB):
             return LIB          # GPU box: use the prebuilt library that travelled with the snapshot
         raise RuntimeError("nvcc not found and no prebuilt libptx.so")
-    cmd = [nvcc] + NVCC_FLAGS + ["-shared", "-o", LIB] + srcs
+    objdir = os.path.join(HERE, "build")
+    os.makedirs(objdir, exist_ok=True)
+    hdr_time = max(os.path.getmtime(h) for h in headers)
+    todo, objs = [], []
+    for src in srcs:
+        obj = os.path.join(objdir, os.path.basename(src) + ".o")
+        objs.append(obj)
+        if force or not os.path.exists(obj) or os.path.getmtime(obj) < max(os.path.getmtime(src), hdr_time):
+            todo.append((src, obj))
+    with ThreadPoolExecutor(max_workers=max(1, min(len(todo), os.cpu_count() or 4))) as ex:
+        for src, r in ex.map(lambda so: _compile_one(nvcc, so[0], so[1], verbose), todo):
+            if r.returncode != 0:
+                sys.stderr.write(r.stdout + r.stderr)
+                raise RuntimeError(f"nvcc failed compiling {os.path.basename(src)}")
+            if verbose:
+                print(r.stderr)
+    cmd = [nvcc] + NVCC_FLAGS + ["-shared", "-o", LIB] + objs
     if verbose:
-        cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd))
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
-        raise RuntimeError("nvcc failed building libptx.so")
-    if verbose:
-        print(r.stderr)
+        raise RuntimeError("nvcc failed linking libptx.so")
     return LIB
 
 
