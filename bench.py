@@ -276,13 +276,14 @@ def run_ours(args, scene_path, w, h, spp, depth):
             traversal = {"nodes_per_segment": n_node, "tris_per_segment": n_tri, "node_bytes": 80, "tri_bytes": 48}
         achieved = st_t["segments"] * bytes_per_seg / (k_ms * 1e-3) * 1e-9 if k_ms > 0 else None
         # measured DRAM bytes per launch of the dominant kernel (ncu capture of this very configuration, profiles/traffic.json)
-        traffic = traffic_src = None
+        traffic = traffic_src = issue = None
         tkey = f"{args.workload}/{args.rng}/{args.pipeline}"
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if world == 1 and args.spp == 0 and os.path.exists(tpath):
             ent = json.load(open(tpath)).get(tkey)
             if ent:
                 traffic, traffic_src = ent["bytes"], ent["source"]
+                issue = ent.get("issue")
         out = {
             "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_dev_max / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -298,7 +299,9 @@ def run_ours(args, scene_path, w, h, spp, depth):
             "roofline": {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "bytes_per_segment": bytes_per_seg,
                          "kernel_ms_per_step": k_ms, "kernel_share_of_step": k_ms / st_t["render_ms"] if st_t["render_ms"] else None,
-                         "traversal": traversal, "bytes_per_slot_launch": bytes_per_slot_launch},
+                         "traversal": traversal, "bytes_per_slot_launch": bytes_per_slot_launch,
+                         # not part of the contract: what ncu says about the bound that really limits this kernel (issue slots)
+                         "issue": issue},
             "scene": {k: scene_stats[k] for k in ("n_triangles", "n_nodes", "node_bytes", "triangle_bytes", "build_ms", "builder", "max_depth", "sah_cost")},
         }
         if world == 1 and not args.no_cpu_baseline and generated:
