@@ -472,7 +472,8 @@ int ptx_scene_get_guide_records(const ptx_scene* s, int64_t first, int64_t n, fl
 // ---------------------------------------------------------------------------------------------
 int ptx_film_create(ptx_ctx* c, int width, int height, ptx_film** out) {
     if (!c || !out || width <= 0 || height <= 0) return fail(c, PTX_ERR_INVALID, "ptx_film_create: bad argument");
-    if ((long long)width * height > 0x7FFFFFFFll) return fail(c, PTX_ERR_INVALID, "ptx_film_create: image too large");
+    if ((long long)width * height > 0x7FFFFFFFll || width > 65535 || height > 65535)      // div_exact_pos (common.h) covers coordinates up to 65536
+        return fail(c, PTX_ERR_INVALID, "ptx_film_create: image too large (at most 65535 x 65535 and 2^31 - 1 pixels)");
     PTX_CUDA(c, cudaSetDevice(c->device));
     ptx_film* f = new ptx_film();
     f->ctx = c; f->w = width; f->h = height;

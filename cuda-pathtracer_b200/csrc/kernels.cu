@@ -241,8 +241,8 @@ __global__ void __launch_bounds__(kBlock) k_shade(WaveState ws, SceneView scene,
 // to the pixel sum when the path ends (`color += integrator(...)`, integrator.h:387-390).
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void start_path_xy(const CameraView& cam, float fx, float fy, float ju, float jv, PathVertex& pv) {
-    float u = (fx + ju) / (float)cam.width;                  // integrator.h:384-385
-    float v = (fy + jv) / (float)cam.height;
+    float u = div_exact_pos(fx + ju, (float)cam.width);      // integrator.h:384-385
+    float v = div_exact_pos(fy + jv, (float)cam.height);
     camera_ray(cam, u, v, pv.o, pv.d);
     pv.beta = mk3(1.0f, 1.0f, 1.0f);
     pv.depth = 0;

@@ -49,7 +49,7 @@ PTX_HD vec3 cosine_hemisphere(vec3 n, float u, float v) {
         tangent = mk3(0.0f, -1.0f, 0.0f);
         bitangent = mk3(-1.0f, 0.0f, 0.0f);
     } else {
-        float a = 1.0f / (1.0f + n.z);
+        float a = rcp_exact(1.0f + n.z);
         float b = -n.x * n.y * a;
         tangent = mk3(1.0f - n.x * n.x * a, b, -n.x);
         bitangent = mk3(b, 1.0f - n.y * n.y * a, -n.y);

@@ -68,7 +68,7 @@ PTX_HD bool intersect_tri(vec3 v0, vec3 e1, vec3 e2, vec3 o, vec3 d, float t_min
     // accepted t is bit-identical), with the rejections collected into one predicate.  With ~12 of 32 lanes active
     // an early exit almost never frees the warp, while its three nested divergent branches cost BSSY/BSYNC pairs
     // and keep ptxas from overlapping the two cross products (ncu r1i: branch_resolving 0.66 per issue).
-    float f = 1.0f / a;
+    float f = rcp_exact(a);
     vec3 s = o - v0;
     float u = f * dot(s, h);
     vec3 q = cross(s, e1);

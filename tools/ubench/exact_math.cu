@@ -1,0 +1,73 @@
+// tools/ubench/exact_math.cu -- exhaustive check of the branch-free "exact" reciprocal / square root / division used by the
+// kernels (csrc/common.h) against CUDA's correctly rounded intrinsics, over EVERY float32 bit pattern.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -I cuda-pathtracer_b200/csrc -o /tmp/exact_math tools/ubench/exact_math.cu && /tmp/exact_math
+// Prints, per function, the number of inputs inside the documented domain and how many of them differ (must be 0), and
+// what happens outside the domain.
+#include <cstdint>
+#include <cstdio>
+#include <cuda_runtime.h>
+
+#include "common.h"
+
+using namespace ptx;
+
+__device__ bool same(float a, float b) { return __float_as_uint(a) == __float_as_uint(b) || (a != a && b != b); }
+
+// counters: [0] in-domain inputs, [1] in-domain mismatches, [2] out-of-domain inputs, [3] out-of-domain mismatches
+__global__ void k_rcp(unsigned long long* c) {
+    unsigned long long in = 0, bad = 0, out = 0, obad = 0;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < (1ull << 32); i += (unsigned long long)gridDim.x * blockDim.x) {
+        float x = __uint_as_float((uint32_t)i);
+        uint32_t e = ((uint32_t)i >> 23) & 0xFFu;
+        bool dom = e >= 1u && e <= 252u;                        // 2^-126 <= |x| < 2^126
+        bool ok = same(rcp_exact(x), __frcp_rn(x));
+        if (dom) { in++; bad += !ok; } else { out++; obad += !ok; }
+    }
+    atomicAdd(c + 0, in); atomicAdd(c + 1, bad); atomicAdd(c + 2, out); atomicAdd(c + 3, obad);
+}
+__global__ void k_sqrt(unsigned long long* c) {
+    unsigned long long in = 0, bad = 0, out = 0, obad = 0;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < (1ull << 32); i += (unsigned long long)gridDim.x * blockDim.x) {
+        float x = __uint_as_float((uint32_t)i);
+        bool dom = (uint32_t)i == 0u || ((uint32_t)i >= 0x0D000000u && (uint32_t)i <= 0x7F7FFFFFu);   // +0 and [2^-101, FLT_MAX]
+        bool ok = same(sqrt_exact(x), __fsqrt_rn(x));
+        if (dom) { in++; bad += !ok; } else { out++; obad += !ok; }
+    }
+    atomicAdd(c + 0, in); atomicAdd(c + 1, bad); atomicAdd(c + 2, out); atomicAdd(c + 3, obad);
+}
+// division a / b for the camera jitter (start_path_xy): b = an image dimension, a = pixel coordinate + jitter in [0, 65536]
+__global__ void k_div(unsigned long long* c, float b) {
+    unsigned long long in = 0, bad = 0, out = 0, obad = 0;
+    const uint32_t lo = __float_as_uint(9.094947017729282e-13f), hi = __float_as_uint(65536.0f);      // 2^-40 .. 2^16
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i <= hi; i += (unsigned long long)gridDim.x * blockDim.x) {
+        float a = __uint_as_float((uint32_t)i);                  // every float in [0, 65536]
+        bool ok = same(div_exact_pos(a, b), __fdiv_rn(a, b));
+        if ((uint32_t)i >= lo) { in++; bad += !ok; } else { out++; obad += !ok; }
+    }
+    atomicAdd(c + 0, in); atomicAdd(c + 1, bad); atomicAdd(c + 2, out); atomicAdd(c + 3, obad);
+}
+
+int main() {
+    unsigned long long* d; cudaMalloc(&d, 64);
+    unsigned long long h[4];
+    auto run = [&](const char* name, auto launch) {
+        cudaMemset(d, 0, 64); launch(); cudaDeviceSynchronize();
+        cudaMemcpy(h, d, 32, cudaMemcpyDeviceToHost);
+        printf("%-28s in-domain %llu mismatches %llu | out-of-domain %llu mismatches %llu\n", name, h[0], h[1], h[2], h[3]);
+        return h[1];
+    };
+    unsigned long long fails = 0;
+    fails += run("rcp_exact vs __frcp_rn", [&] { k_rcp<<<148 * 8, 256>>>(d); });
+    fails += run("sqrt_exact vs __fsqrt_rn", [&] { k_sqrt<<<148 * 8, 256>>>(d); });
+    const int dims[] = {1, 2, 3, 7, 8, 36, 37, 40, 48, 54, 64, 91, 96, 100, 256, 480, 512, 640, 720, 800, 1000, 1024, 1080, 1085, 1200, 1920, 2048, 2160, 3840, 4096, 7680, 8192, 16384, 32768, 65535};
+    unsigned long long tot = 0, bad = 0, otot = 0, obad = 0;
+    for (int w : dims) {
+        cudaMemset(d, 0, 64); k_div<<<148 * 8, 256>>>(d, (float)w); cudaDeviceSynchronize();
+        cudaMemcpy(h, d, 32, cudaMemcpyDeviceToHost); tot += h[0]; bad += h[1]; otot += h[2]; obad += h[3];
+    }
+    printf("%-28s in-domain %llu mismatches %llu | out-of-domain %llu mismatches %llu (a: every float in [2^-40, 65536] / below; b: %zu image dimensions)\n",
+           "div_exact_pos vs __fdiv_rn", tot, bad, otot, obad, sizeof dims / sizeof dims[0]);
+    fails += bad;
+    printf(fails ? "FAILED\n" : "ALL EXACT\n");
+    return fails ? 1 : 0;
+}
