@@ -169,7 +169,8 @@ struct Traversal {
 #pragma unroll
             for (int half = 0; half < 2; half++) {
                 uint32_t meta4 = half ? n1.w : n1.z;
-                if (meta4 == 0u) continue;                 // four empty slots (small nodes fill the low slots first)
+                if (meta4 == 0u) continue;                 // four empty slots (small nodes fill the low slots first); dropping the
+                                                           // branch was measured neutral (C2 18.88 -> 18.90 G, 8 bytes of spills)
                 uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
                 uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
                 uint32_t m4 = meta4 ^ (octinv4 & inner_mask4 & 0x07070707u);   // per byte: bits 7..5 unary count, 4..0 bit index
