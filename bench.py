@@ -110,7 +110,7 @@ def run_reference(args, scene_path, w, h, spp, depth):
     ms = sum(t_ms) / len(t_ms)
     value = w * h * sample_spp * seg_per_path / (ms * 1e-3) * 1e-6
     sample = f"{w}x{h}, {sample_spp} of {spp} spp per step, depth {depth}"
-    print(json.dumps({
+    emit(({
         "impl": "reference", "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload_desc, "sample": sample, "segments_per_path": seg_per_path},
@@ -316,13 +316,27 @@ def run_ours(args, scene_path, w, h, spp, depth):
                                        "kind": "reference", "sample": f"{w}x{h}, {cb_spp} of {spp} spp, depth {depth}, oracle/_ref/ref_host (reference headers, host build, OpenMP rows)"}
             except Exception as e:       # noqa: BLE001
                 out["cpu_baseline"] = {"value": None, "error": str(e)[:200]}
-        print(json.dumps(out))
+        emit(out)
     film.close(); scene.close(); ctx.close()
     if world > 1:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(obj):
+    """The ONE JSON line of the contract, written to the process's real stdout (see main())."""
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (json.dumps(obj) + "\n").encode())
+
+
 def main():
+    # Native libraries print banners on fd 1 (NCCL: "NCCL version ..." at the first communicator).  The contract is one JSON
+    # line on stdout, so fd 1 is pointed at stderr for the whole run and the line goes to a saved copy of the real stdout.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -345,7 +359,7 @@ def main():
     scene_path = os.path.join(ROOT, "scenes", scene)
     if args.impl == "reference" and scene.startswith("generated:"):
         if int(os.environ.get("RANK", "0")) == 0:
-            print(json.dumps({"impl": "reference", "unavailable": "reference cannot hold this scene (4 364 B per primitive, single-thread BVH build); see BASELINE.md"}))
+            emit({"impl": "reference", "unavailable": "reference cannot hold this scene (4 364 B per primitive, single-thread BVH build); see BASELINE.md"})
         return
     if args.impl == "reference":
         run_reference(args, scene_path, w, h, spp, depth)
