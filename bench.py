@@ -72,9 +72,15 @@ class ClockSampler(threading.Thread):
 
 
 def ref_host_run(scene, w, h, spp, depth, frames, threads=0):
+    """threads = 0: every host core this process may use -- stated explicitly, because torchrun exports OMP_NUM_THREADS=1
+    to its workers and the reference arm must not be slowed down by the launcher."""
     exe = os.path.join(ROOT, "oracle", "_ref", "ref_host")
+    if threads <= 0:
+        threads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    env = dict(os.environ)
+    env["OMP_NUM_THREADS"] = str(threads)
     r = subprocess.run([exe, "render", scene, str(w), str(h), str(spp), str(depth), str(frames), "-", "0", str(threads)],
-                       capture_output=True, text=True, check=True)
+                       capture_output=True, text=True, check=True, env=env)
     return json.loads(r.stdout.strip().splitlines()[-1])
 
 
