@@ -38,7 +38,7 @@ PTX_HD vec3 cosine_hemisphere(vec3 n, float u, float v) {
     float phi = (float)(2.0 * 3.14159265358979323846 * (double)v);   // `2.0f * M_PI * v` is double on Linux
     float sn, cs;
 #if defined(__CUDA_ARCH__)
-    sincosf(phi, &sn, &cs);
+    sincos_small(phi, sn, cs);          // == sincosf(phi, ...) for phi in (0, 2 pi], see common.h
 #else
     sn = sinf(phi); cs = cosf(phi);
 #endif

@@ -47,6 +47,19 @@ __global__ void k_div(unsigned long long* c, float b) {
     atomicAdd(c + 0, in); atomicAdd(c + 1, bad); atomicAdd(c + 2, out); atomicAdd(c + 3, obad);
 }
 
+// sincos_small against sincosf for every float32 in [0, 8] (the azimuth 2 pi v lies in (0, 2 pi])
+__global__ void k_sincos(unsigned long long* c) {
+    unsigned long long in = 0, bad = 0;
+    const uint32_t hi = __float_as_uint(8.0f);
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i <= hi; i += (unsigned long long)gridDim.x * blockDim.x) {
+        float x = __uint_as_float((uint32_t)i), s0, c0, s1, c1;
+        sincosf(x, &s0, &c0);
+        sincos_small(x, s1, c1);
+        in++; bad += !(same(s0, s1) && same(c0, c1));
+    }
+    atomicAdd(c + 0, in); atomicAdd(c + 1, bad);
+}
+
 int main() {
     unsigned long long* d; cudaMalloc(&d, 64);
     unsigned long long h[4];
@@ -68,6 +81,10 @@ int main() {
     printf("%-28s in-domain %llu mismatches %llu | out-of-domain %llu mismatches %llu (a: every float in [2^-40, 65536] / below; b: %zu image dimensions)\n",
            "div_exact_pos vs __fdiv_rn", tot, bad, otot, obad, sizeof dims / sizeof dims[0]);
     fails += bad;
+    cudaMemset(d, 0, 64); k_sincos<<<148 * 8, 256>>>(d); cudaDeviceSynchronize();
+    cudaMemcpy(h, d, 32, cudaMemcpyDeviceToHost);
+    printf("%-28s in-domain %llu mismatches %llu | (every float in [0, 8], both outputs)\n", "sincos_small vs sincosf", h[0], h[1]);
+    fails += h[1];
     printf(fails ? "FAILED\n" : "ALL EXACT\n");
     return fails ? 1 : 0;
 }
