@@ -256,7 +256,7 @@ def run_ours(args, scene_path, w, h, spp, depth):
             # no path state in memory: per owned pixel and sample chunk the compat kernel moves its id 4 + RNG state 24 + 24 + pixel sum 16 + 16 bytes;
             # per path the counter-RNG kernel moves its pixel id 4 + three float atomics 12
             # (a pixel is handed on between its sample chunks: per chunk pixel id 4 + RNG state 24 + 24 + pixel sum 16 + 16 + progress flag 4 + 4)
-            n_chunks = args.chunks if args.chunks > 0 else min(6, max(1, spp.bit_length()))
+            n_chunks = compat_chunk_count(spp, args.chunks, (w * h / world) / (ctx.device_info()["sm_count"] * 768.0))
             per_item = 92.0 * n_chunks * (w * h / world) if rng_mode == pkg.RNG_XORWOW_COMPAT else 16.0 * st_t["paths"]
             bytes_per_seg = per_item / max(st_t["segments"], 1)
             kname, k_ms = "k_path_persist<rng> (one launch per frame: extend+shade+regenerate, all state in registers)", st_t["shade_ms"]
@@ -334,6 +334,24 @@ _REAL_STDOUT = None
 def emit(obj):
     """The ONE JSON line of the contract, written to the process's real stdout (see main())."""
     os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (json.dumps(obj) + "\n").encode())
+
+
+def compat_chunk_count(spp, override, pixels_per_lane):
+    """Work items per pixel of the compat-RNG persistent kernel (the rule of csrc/api.cu ptx_render: U equal parts, the last one
+    halved down to spp / 32; U = 2 with >= 8 pixels per resident lane, else 8).  Only used for the algorithmic-bytes estimate."""
+    if spp <= 0:
+        return 1
+    if override > 0:
+        return min(override, spp.bit_length())
+    u = -override if override < 0 else (2 if pixels_per_lane >= 8.0 else 8)
+    u = max(1, min(u, spp, 32))
+    n, at = max(u, 1), spp * (u - 1) // u
+    left, floor_sz = spp - at, max(1, spp // 32)
+    while left > floor_sz and left // 2 >= 1:
+        at += left - left // 2
+        left = spp - at
+        n += 1
+    return n
 
 
 def main():

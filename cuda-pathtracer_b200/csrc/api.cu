@@ -710,13 +710,36 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     if (rc == PTX_OK && !persist) rc = ensure_wave_capacity(c, rp.n_slots, rp.n_owned);
     if (rc != PTX_OK) return rc;
     // compat RNG: a pixel's samples form one sequential chain; the persistent kernel splits it into n_chunks work items
-    // (1/2, 1/4, ... of the samples, the pixel's RNG state and running sum handed on through the film between them), so
-    // the tail of the frame is bounded by the small last chunk instead of a whole pixel.  reserved[3] overrides the count.
+    // (the pixel's RNG state and running sum handed on through the film between them), handed out chunk-major.  The
+    // boundaries: U equal parts, the last of them halved again and again down to spp / 32, so the tail of the frame is
+    // bounded by a 1/32 pixel.  U = 2 (1/2, 1/4, ... : 6 items per pixel) costs the fewest hand-offs and is right when every
+    // lane gets many pixels; with few pixels per lane (a tile-sharded 1080p frame on 8 GPUs: 2.3) a pixel whose first half
+    // starts late cannot finish its remaining half inside the frame, and more, smaller parts keep all chains moving in
+    // step.  reserved[3] overrides: n > 0 = n halving chunks, n < 0 = U = -n.
     {
-        int log2spp = 0;
-        while ((rp.spp >> (log2spp + 1)) > 0) log2spp++;
-        int want = opts->reserved[3] > 0 ? opts->reserved[3] : 6;
-        rp.n_chunks = rp.spp > 0 ? std::min(want, log2spp + 1) : 1;
+        const uint32_t spp = (uint32_t)std::max(rp.spp, 0);
+        const uint32_t floor_sz = std::max(1u, spp / 32u);
+        int U = 2;
+        if (opts->reserved[3] < 0) U = -opts->reserved[3];
+        else if (opts->reserved[3] == 0) {
+            const double per_lane = (double)rp.n_owned / ((double)c->prop.multiProcessorCount * 768.0);
+            U = per_lane >= 8.0 ? 2 : 8;      // C2 on one rank of 1 / 2 / 4 / 8: 18 / 9 / 4.6 / 2.3 pixels per lane (tools/shard_probe.py)
+        }
+        U = (int)std::min<uint32_t>((uint32_t)std::max(U, 1), std::max(1u, std::min(spp, 32u)));
+        int n = 0;
+        rp.chunk_start[0] = 0;
+        if (opts->reserved[3] > 0) {
+            int log2spp = 0;
+            while ((spp >> (log2spp + 1)) > 0) log2spp++;
+            const int want = std::min(opts->reserved[3], log2spp + 1);
+            for (n = 1; n < want; n++) rp.chunk_start[n] = spp - (spp >> n);
+        } else if (spp > 0) {
+            for (n = 1; n < U; n++) rp.chunk_start[n] = (uint32_t)((unsigned long long)spp * (unsigned)n / (unsigned)U);
+            uint32_t at = rp.chunk_start[U - 1], left = spp - at;
+            while (left > floor_sz && left / 2u >= 1u && n < kMaxChunks - 1) { at += left - left / 2u; left = spp - at; rp.chunk_start[n++] = at; }
+        } else n = 1;
+        rp.n_chunks = std::max(n, 1);
+        for (int i = rp.n_chunks; i <= kMaxChunks; i++) rp.chunk_start[i] = spp;
     }
     rp.shade_batch = opts->reserved[4] > 0 ? opts->reserved[4] : 12;      // lanes of a warp that must be waiting before it shades
     int key[5] = {w, h, shard_mode, rank, world};

@@ -402,8 +402,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
     constexpr unsigned kFull = 0xFFFFFFFFu;
     const int lane = (int)(threadIdx.x & 31);
     // compat: item = (chunk c, owned pixel k), chunk-major, so chunk c of a pixel is handed out long after chunk c-1.
-    // Chunk c covers samples [spp - (spp >> c), spp - (spp >> (c+1))), the last one runs to spp: halves, then quarters, ...
-    // so most samples pay no hand-off and the frame's tail is bounded by the small last chunks.
+    // Chunk c covers samples [chunk_start[c], chunk_start[c+1]) -- the host picks the boundaries (api.cu: equal parts whose last
+    // one is halved down to spp / 32), so most samples pay no hand-off and the frame's tail is bounded by the small last chunks.
     const uint32_t n_chunks = RNG == 0 ? (uint32_t)rp.n_chunks : 0u;
     const unsigned long long n_items = RNG == 0 ? (unsigned long long)rp.n_owned * n_chunks : rp.total_paths;
     uint32_t nseg = 0, npaths = 0;
@@ -467,7 +467,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
                 else { ra = __ldcg(film.rngA + pixel); rb = __ldcg(film.rngB + pixel); f = __ldcg(film.accum + pixel); }   // L2: L1 may hold a stale line
                 xr.st = Xorwow{ra.x, ra.y, ra.z, ra.w, rb.x, rb.y};
                 acc = v3(f.x, f.y, f.z);
-                sample = (uint32_t)rp.spp - ((uint32_t)rp.spp >> chunk);
+                sample = rp.chunk_start[chunk];
                 fx = (float)(int)(pixel % (uint32_t)cam.width); fy = (float)(int)(pixel / (uint32_t)cam.width);
                 float ju = xr.next(), jv = xr.next();
                 start_path_xy(cam, fx, fy, ju, jv, pv);
@@ -507,7 +507,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
                 acc = acc + L;
                 L = v3(0.f, 0.f, 0.f);
                 sample++;
-                if (sample < (chunk + 1u == n_chunks ? (uint32_t)rp.spp : (uint32_t)rp.spp - ((uint32_t)rp.spp >> (chunk + 1u)))) {
+                if (sample < rp.chunk_start[chunk + 1u]) {
                     float ju = xr.next(), jv = xr.next();
                     start_path_xy(cam, fx, fy, ju, jv, pv);
                     cont = true;
@@ -779,7 +779,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_cta(WaveState ws, SceneVie
                         const vec3 acc = v3(S.acc[0][p], S.acc[1][p], S.acc[2][p]) + L;
                         XorwowRng xr;
                         xr.st = Xorwow{S.rng[0][p], S.rng[1][p], S.rng[2][p], S.rng[3][p], S.rng[4][p], S.rng[5][p]};
-                        if (sample < (chunk + 1u == n_chunks ? (uint32_t)rp.spp : (uint32_t)rp.spp - ((uint32_t)rp.spp >> (chunk + 1u)))) {
+                        if (sample < rp.chunk_start[chunk + 1u]) {
                             const uint32_t pxy = S.pxy[p];
                             float ju = xr.next(), jv = xr.next();
                             PathVertex pv;
@@ -872,7 +872,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_cta(WaveState ws, SceneVie
                         S.depth[p] = 0u;
                         S.L[0][p] = 0.f; S.L[1][p] = 0.f; S.L[2][p] = 0.f;
                         S.acc[0][p] = f.x; S.acc[1][p] = f.y; S.acc[2][p] = f.z;
-                        S.sample[p] = (uint32_t)rp.spp - ((uint32_t)rp.spp >> chunk);
+                        S.sample[p] = rp.chunk_start[chunk];
                         S.rng[0][p] = xr.st.v0; S.rng[1][p] = xr.st.v1; S.rng[2][p] = xr.st.v2;
                         S.rng[3][p] = xr.st.v3; S.rng[4][p] = xr.st.v4; S.rng[5][p] = xr.st.d;
                         S.key[p] = kKeyInit;

@@ -48,6 +48,7 @@ struct FilmView {
     int width, height;
 };
 
+constexpr int kMaxChunks = 40;
 struct RenderParams {
     ShadeParams shade;
     int spp;
@@ -56,7 +57,8 @@ struct RenderParams {
     unsigned long long total_paths;   // philox: n_owned * spp
     uint32_t sample_begin;    // philox sample-range sharding: first global sample index
     int shade_batch;          // persistent kernel: waiting lanes per warp that trigger a shading round (1 = shade at once)
-    int n_chunks;             // persistent kernel, compat RNG: work items per pixel (geometric sample ranges, see k_path_persist)
+    int n_chunks;             // persistent kernel, compat RNG: work items per pixel (consecutive sample ranges, see k_path_persist)
+    uint32_t chunk_start[kMaxChunks + 1];   // chunk c covers samples [chunk_start[c], chunk_start[c + 1]); chunk_start[n_chunks] = spp
     unsigned long long seed;
 };
 

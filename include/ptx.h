@@ -184,8 +184,10 @@ typedef struct {
     float rr_cap;             /* 0 => 0.95 */
     int32_t pipeline;         /* 0 = default (= 3).  3 = persistent path loop: one launch per frame; lanes pull pixels / paths from
                                      a counter, no path state in memory; with the compat RNG a pixel's samples are split into
-                                     reserved[3] work items (default 6: 1/2, 1/4, ... 1/32, 1/32 of spp) handed from lane to lane
-                                     through the film, so the frame's tail is one small chunk, not one pixel.
+                                     work items handed from lane to lane through the film, so the frame's tail is one small
+                                     chunk, not one pixel (default: 1/2, 1/4, ... 1/32, 1/32 of spp, or eight equal parts with
+                                     the last one halved down to 1/32 when a rank owns few pixels per resident lane;
+                                     reserved[3] = n > 0: n halving chunks, n < 0: -n equal parts).
                                  Cross-checks (bit-identical images): 4 = wavefront (raygen / extend / shade / compact kernels),
                                  1 = fused bounce kernel (one launch per bounce), 2 = path loop with a slot queue (state in
                                  registers for reserved[1] bounces per launch), 5 = CTA wavefront (paths in shared memory, four
