@@ -18,7 +18,7 @@ with pkg.Context(0) as ctx:
             for rep in range(3):
                 film.reset()
                 st = ctx.render(scene, cam, film, spp=spp, max_depth=depth, rng_mode=0, shard_mode=pkg.SHARD_TILES if world > 1 else pkg.SHARD_NONE,
-                                shard_rank=r, shard_world=world, chunks=chunks)
+                                shard_rank=r, shard_world=world, chunks=chunks, loop_min_blocks=int(os.environ.get('MINB', '0')))
                 best = st if best is None or st["render_ms"] < best["render_ms"] else best
             rows.append((round(best["render_ms"], 2), best["segments"]))
         tot = sum(s for _, s in rows)
