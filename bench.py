@@ -338,12 +338,12 @@ def emit(obj):
 
 def compat_chunk_count(spp, override, pixels_per_lane):
     """Work items per pixel of the compat-RNG persistent kernel (the rule of csrc/api.cu ptx_render: U equal parts, the last one
-    halved down to spp / 32; U = 2 with >= 8 pixels per resident lane, else 8).  Only used for the algorithmic-bytes estimate."""
+    halved down to spp / 32; U = 2 with >= 8 pixels per resident lane or spp < 512, else 8).  Only used for the algorithmic-bytes estimate."""
     if spp <= 0:
         return 1
     if override > 0:
         return min(override, spp.bit_length())
-    u = -override if override < 0 else (2 if pixels_per_lane >= 8.0 else 8)
+    u = -override if override < 0 else (2 if (pixels_per_lane >= 8.0 or spp < 512) else 8)
     u = max(1, min(u, spp, 32))
     n, at = max(u, 1), spp * (u - 1) // u
     left, floor_sz = spp - at, max(1, spp // 32)

@@ -723,7 +723,9 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
         if (opts->reserved[3] < 0) U = -opts->reserved[3];
         else if (opts->reserved[3] == 0) {
             const double per_lane = (double)rp.n_owned / ((double)c->prop.multiProcessorCount * 768.0);
-            U = per_lane >= 8.0 ? 2 : 8;      // C2 on one rank of 1 / 2 / 4 / 8: 18 / 9 / 4.6 / 2.3 pixels per lane (tools/shard_probe.py)
+            // C2 on one rank of 1 / 2 / 4 / 8: 18 / 9 / 4.6 / 2.3 pixels per lane (tools/shard_probe.py).  Parts shorter than 64
+            // samples cost more in hand-offs than they gain (C1, 64 spp: 13.8 -> 12.2 G with eight parts)
+            U = (per_lane >= 8.0 || spp < 512u) ? 2 : 8;
         }
         U = (int)std::min<uint32_t>((uint32_t)std::max(U, 1), std::max(1u, std::min(spp, 32u)));
         int n = 0;

@@ -186,7 +186,7 @@ typedef struct {
                                      a counter, no path state in memory; with the compat RNG a pixel's samples are split into
                                      work items handed from lane to lane through the film, so the frame's tail is one small
                                      chunk, not one pixel (default: 1/2, 1/4, ... 1/32, 1/32 of spp, or eight equal parts with
-                                     the last one halved down to 1/32 when a rank owns few pixels per resident lane;
+                                     the last one halved down to 1/32 when a rank owns few pixels per resident lane and spp >= 512;
                                      reserved[3] = n > 0: n halving chunks, n < 0: -n equal parts).
                                  Cross-checks (bit-identical images): 4 = wavefront (raygen / extend / shade / compact kernels),
                                  1 = fused bounce kernel (one launch per bounce), 2 = path loop with a slot queue (state in

@@ -21,7 +21,7 @@ with pkg.Context(0) as ctx:
         best = None
         for rep in range(4):
             film.reset()
-            st = ctx.render(scene, cam, film, spp=spp, max_depth=depth, rng_mode=rng, loop_min_blocks=int(os.environ.get("MINB", "0")), shade_batch=int(os.environ.get("BATCH", "0")))
+            st = ctx.render(scene, cam, film, spp=spp, max_depth=depth, rng_mode=rng, loop_min_blocks=int(os.environ.get("MINB", "0")), shade_batch=int(os.environ.get("BATCH", "0")), chunks=int(os.environ.get("CHUNKS", "0")))
             best = st if best is None or st["render_ms"] < best["render_ms"] else best
         print(json.dumps(dict(minb=os.environ.get("MINB", "0"), batch=os.environ.get("BATCH", "0"), lib=os.path.basename(pkg.LIB_PATH), scene=which, rng=rng, ms=round(best["render_ms"], 3), segments=best["segments"],
                               Gseg_s=round(best["segments"] / best["render_ms"] / 1e6, 3), mean=float(film.linear().mean()))), flush=True)
