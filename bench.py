@@ -275,9 +275,10 @@ def run_ours(args, scene_path, w, h, spp, depth):
         if scene_stats["node_bytes"] + scene_stats["triangle_bytes"] > 126e6:
             # scene larger than L2: the bound is node + triangle fetch traffic; N_node, N_tri per segment
             # measured by the instrumented extend kernel on a 2-spp frame outside the timed region
-            kwc = dict(kw); kwc.update(spp=2, pipeline=pkg.PIPELINE_WAVEFRONT)
+            # (the whole frame, unsharded: a 2-spp frame split into sample ranges leaves most ranks without a sample)
+            kwc = dict(kw); kwc.update(spp=2, pipeline=pkg.PIPELINE_WAVEFRONT, shard_mode=pkg.SHARD_NONE, shard_rank=0, shard_world=1)
             st_c = ctx.render(scene, cam, film, count_work=True, **kwc)
-            n_node, n_tri = st_c["node_visits"] / st_c["segments"], st_c["tri_tests"] / st_c["segments"]
+            n_node, n_tri = st_c["node_visits"] / max(st_c["segments"], 1), st_c["tri_tests"] / max(st_c["segments"], 1)
             bytes_per_seg = n_node * 80 + n_tri * 48
             traversal = {"nodes_per_segment": n_node, "tris_per_segment": n_tri, "node_bytes": 80, "tri_bytes": 48}
         achieved = st_t["segments"] * bytes_per_seg / (k_ms * 1e-3) * 1e-9 if k_ms > 0 else None
