@@ -397,7 +397,7 @@ __global__ void __launch_bounds__(kBlock) k_build_guide(const float* __restrict_
 // ends (ncu r1h: lane efficiency 0.53 in the second launch of a 128-spp frame).  Lanes only idle in the
 // tail of the frame, when the counter has run dry.
 // ---------------------------------------------------------------------------------------------
-template <int RNG, int BLOCK, int MINB, bool GUIDED = false>
+template <int RNG, int BLOCK, int MINB, bool GUIDED = false, bool PAIR = false>
 __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, SceneView scene, FilmView film, CameraView cam, RenderParams rp) {
     constexpr unsigned kFull = 0xFFFFFFFFu;
     const int lane = (int)(threadIdx.x & 31);
@@ -478,7 +478,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
         }
         if (!__any_sync(kFull, alive || pending)) break;
         // ---- extend: one wide-node visit (+ its triangles) per lane
-        if (alive && !waiting) waiting = tr.template step<false, 24>(scene, stk, pv.o, pv.d, 1e-4f, nullptr);
+        if (alive && !waiting) waiting = tr.template step<false, 24, PAIR>(scene, stk, pv.o, pv.d, 1e-4f, nullptr);
         __syncwarp();
         // ---- shade in batches: a finished ray waits until enough lanes of the warp are through.  Shading + regeneration
         //      cost about as much as a node visit and run for the whole warp whenever one lane needs them; on a scene with
@@ -1147,6 +1147,11 @@ void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, con
     // resident CTAs: 3 x 256 threads at 80 registers (default), 4 x 256 at 64, or 7 x 128 at 72 (reserved[2] = 4 / 7);
     // reserved[2] = 1 / 2 launch only 1 / 2 of the three 256-thread CTAs per SM: fewer warps share an SM, so each pixel's
     // sequential sample chain advances faster (matters when a rank owns few pixels: DESIGN.md section 6)
+    // bits 4-5 of reserved[2]: 1 = force the two-records-per-round triangle loop, 2 = force one record per round; 0 = by scene
+    // size (worth it where the records come from L2 / HBM, not on cache-resident scenes: traverse.h, Traversal::step)
+    const int pair_opt = (min_blocks >> 4) & 3;
+    min_blocks &= 15;
+    const bool pair = pair_opt == 1 || (pair_opt == 0 && scene.n_tris > 1024u);      // C3 at 41 K / 655 K / 10.5 M triangles: +2.3 / +2.7 / +6.1 %; C2 (32): -0.6 %
     int per_sm = min_blocks == 4 ? 4 : (min_blocks == 7 ? 7 : ((min_blocks == 1 || min_blocks == 2) ? min_blocks : 3));
     // default: with the sequential RNG and fewer than ~3 pixels per resident lane the frame is bounded by its longest pixel
     // chain, not by throughput -- two CTAs per SM finish such a frame sooner (C2, 1/8 of the film: 38 vs 43 ms)
@@ -1165,6 +1170,9 @@ void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, con
     } else if (per_sm == 7) {
         if (rng_mode == 0) k_path_persist<0, 128, 7><<<g, 128, 0, st>>>(ws, scene, film, cam, rp);
         else k_path_persist<1, 128, 7><<<g, 128, 0, st>>>(ws, scene, film, cam, rp);
+    } else if (pair) {
+        if (rng_mode == 0) k_path_persist<0, kBlock, 3, false, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+        else k_path_persist<1, kBlock, 3, false, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
     } else {
         if (rng_mode == 0) k_path_persist<0, kBlock, 3><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
         else k_path_persist<1, kBlock, 3><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);

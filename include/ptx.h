@@ -193,7 +193,9 @@ typedef struct {
                                  registers for reserved[1] bounces per launch), 5 = CTA wavefront (paths in shared memory, four
                                  dense phases per iteration: node visits, triangle tasks, shading, regeneration; identical
                                  except at exact hit-distance ties; measured slower than 3, kept as an experiment).
-                                 reserved[2] = 1 / 2 / 4 / 7 select other residency builds of 2 and 3 (CTAs per SM) */
+                                 reserved[2] = 1 / 2 / 4 / 7 select other residency builds of 2 and 3 (CTAs per SM); + 16 / + 32 force
+                                 the persistent kernel's triangle loop to two records / one record per round (default: two when the
+                                 scene has more than 1024 triangles; identical images either way) */
     int32_t reserved[5];
 } ptx_render_opts;
 

@@ -24,7 +24,7 @@ with pkg.Context(0) as ctx:
     for sb in batches:
       for rng in (0, 1):
         for rep in range(2):
-            r = ctx.render(scene, cam, film, spp=spp, max_depth=8, rng_mode=rng, shade_batch=sb)
+            r = ctx.render(scene, cam, film, spp=spp, max_depth=8, rng_mode=rng, shade_batch=sb, loop_min_blocks=int(os.environ.get("MINB", "0")))
         out[f"Gseg_s_rng{rng}_sb{sb}"] = round(r["segments"] / r["render_ms"] / 1e6, 3); out[f"seg_per_path_rng{rng}"] = r["segments"] / r["paths"]
     film.write(os.path.join(ROOT, "gpurun_out", "c5.png"))
     print(json.dumps(out))
