@@ -491,7 +491,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
         waiting = false;
         bool cont = true;
         if (done) {
-            uint32_t prim = tr.best == kMiss ? kMiss : __float_as_uint(ldq(scene.tris + (size_t)tr.best * kTriQuads).w);
+            uint32_t prim = tr.bestw;      // kMiss when nothing was hit
             nseg++;
             if (RNG == 0) cont = shade_bounce<XorwowRng, GUIDED>(scene, rp.shade, pv, prim, tr.closest, xr, L);
             else {

@@ -109,11 +109,12 @@ struct Traversal {
     int sp;
     float closest;
     uint32_t best;                 // triangle slot (index into tris) of the closest accepted hit, or kMiss
+    uint32_t bestw;                // its primitive id (word 3 of the record), kept so that shading need not fetch the record again
     uint32_t ng_x, ng_y;           // node group: base index, (hit bits 31..24 | imask 7..0)
     float idx, idy, idz;           // 1/d with zero components replaced by +-2^-80
 
     PTX_HD void begin(vec3 d, float t_max) {
-        sp = 0; closest = t_max; best = kMiss;
+        sp = 0; closest = t_max; best = kMiss; bestw = kMiss;
         const float ooeps = 8.271806e-25f;   // 2^-80: keeps 1/d finite for axis-parallel rays
         idx = rcp_fast(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
         idy = rcp_fast(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
@@ -264,8 +265,8 @@ struct Traversal {
                 float t1 = closest, t2 = closest;
                 const bool h1 = intersect_tri(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), o, d, t_min, t1);
                 const bool h2 = intersect_tri(mk3(a2.x, a2.y, a2.z), mk3(b2.x, b2.y, b2.z), mk3(c2.x, c2.y, c2.z), o, d, t_min, t2);
-                if (h1) { closest = t1; best = ti; }
-                if (h2 && t2 < closest) { closest = t2; best = ti2; }
+                if (h1) { closest = t1; best = ti; bestw = f2u(a.w); }
+                if (h2 && t2 < closest) { closest = t2; best = ti2; bestw = f2u(a2.w); }
             }
         } else
         while (tg_y != 0) {
@@ -275,7 +276,7 @@ struct Traversal {
             const f32x4* tp = s.tris + (size_t)ti * kTriQuads;
             f32x4 a = ldq(tp + 0), b = ldq(tp + 1), c = ldq(tp + 2);
             if (COUNT) ctr->tris++;
-            if (intersect_tri(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), o, d, t_min, closest)) best = ti;
+            if (intersect_tri(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), o, d, t_min, closest)) { best = ti; bestw = f2u(a.w); }
         }
 
         return next_group(stk);
