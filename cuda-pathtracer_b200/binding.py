@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("PTX_LIB") or os.path.join(HERE, "libptx.so")      # P
 
 RNG_XORWOW_COMPAT, RNG_PHILOX = 0, 1
 SHARD_NONE, SHARD_TILES, SHARD_SAMPLES = 0, 1, 2
-PIPELINE_DEFAULT, PIPELINE_FUSED, PIPELINE_LOOP, PIPELINE_PERSIST, PIPELINE_WAVEFRONT, PIPELINE_CTA = 0, 1, 2, 3, 4, 5
+PIPELINE_DEFAULT, PIPELINE_FUSED, PIPELINE_LOOP, PIPELINE_PERSIST, PIPELINE_WAVEFRONT, PIPELINE_CTA, PIPELINE_FLAT = 0, 1, 2, 3, 4, 5, 6
 SAMPLING_BSDF, SAMPLING_FORMFACTOR, SAMPLING_RADIOSITY, SAMPLING_MIS, SAMPLING_TOPK = 0, 1, 2, 3, 4
 
 
@@ -50,7 +50,8 @@ class SceneStats(C.Structure):
     _fields_ = [("n_primitives", C.c_int64), ("n_triangles", C.c_int64), ("n_nodes", C.c_int64), ("n_materials", C.c_int64),
                 ("node_bytes", C.c_int64), ("triangle_bytes", C.c_int64), ("shading_bytes", C.c_int64),
                 ("bounds_min", C.c_float * 3), ("bounds_max", C.c_float * 3), ("sah_cost", C.c_float), ("build_ms", C.c_float),
-                ("builder", C.c_int32), ("max_depth", C.c_int32), ("preprocess_ms", C.c_float), ("preprocess_on_device", C.c_int32)]
+                ("builder", C.c_int32), ("max_depth", C.c_int32), ("preprocess_ms", C.c_float), ("preprocess_on_device", C.c_int32),
+                ("flat_units", C.c_int32), ("reserved", C.c_int32)]
 
 
 class Camera(C.Structure):

@@ -12,7 +12,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libptx.so")
 
 CUDA_SOURCES = ["api.cu", "kernels.cu", "bvh_gpu.cu", "geometry_gpu.cu"]
-HOST_SOURCES = ["bvh_host.cpp", "image_io.cpp", "loader.cpp", "pbrt_loader.cpp", "rng.cpp", "scene_pack.cpp"]
+HOST_SOURCES = ["bvh_host.cpp", "flat_host.cpp", "image_io.cpp", "loader.cpp", "pbrt_loader.cpp", "rng.cpp", "scene_pack.cpp"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -16,6 +16,7 @@
 #include "../../include/ptx.h"
 #include "bvh_gpu.h"
 #include "bvh_host.h"
+#include "flat_host.h"
 #include "kernels.cuh"
 #include "geometry_gpu.h"
 #include "image_io.h"
@@ -56,6 +57,8 @@ struct ptx_scene {
     SceneView view{};
     ptx_scene_stats stats{};
     float* d_guide = nullptr;                    // grid-guided sampling: kGuideFloats floats per primitive (shade.h)
+    FlatHost flat;                               // tiny scenes: the planar-unit list of flat.h (empty when the scene does not qualify)
+    f32x4* d_flat_recs = nullptr;
 };
 
 struct ptx_film {
@@ -239,8 +242,11 @@ int ptx_camera_default(ptx_camera* cam, int width, int height) {
 namespace {
 
 void free_accel(ptx_scene* s) {
-    cudaFree(s->d_nodes); cudaFree(s->d_tris);
-    s->d_nodes = nullptr; s->d_tris = nullptr;
+    cudaFree(s->d_nodes); cudaFree(s->d_tris); cudaFree(s->d_flat_recs);
+    s->d_nodes = nullptr; s->d_tris = nullptr; s->d_flat_recs = nullptr;
+    // nothing may traverse a scene whose rebuild failed half-way (ptx_render / ptx_trace_* check n_nodes)
+    s->view.nodes = nullptr; s->view.tris = nullptr; s->view.n_nodes = 0; s->view.n_tris = 0;
+    s->flat.units.clear(); s->flat.recs.clear();
 }
 
 int build_accel(ptx_scene* s, const ptx_build_opts* bo, const TriIn* d_tris_in = nullptr) {
@@ -282,10 +288,17 @@ int build_accel(ptx_scene* s, const ptx_build_opts* bo, const TriIn* d_tris_in =
         s->view.n_tris = (uint32_t)r.tri_src.size();
         sah = r.sah_cost; depth = r.max_depth; bounds = r.bounds;
     }
+    // tiny scenes also get the flat unit list (flat.h); the BVH8 stays for the queries and as the cross-check
+    if (n <= 2 * (size_t)kFlatUnits && build_flat_units(s->packed.tris.data(), n, s->flat)) {
+        const size_t bytes = s->flat.recs.size() * sizeof(f32x4);
+        PTX_CUDA(c, cudaMalloc(&s->d_flat_recs, bytes));
+        PTX_CUDA(c, cudaMemcpyAsync(s->d_flat_recs, s->flat.recs.data(), bytes, cudaMemcpyHostToDevice, c->stream));
+    }
     PTX_CUDA(c, cudaEventRecord(c->ev1, c->stream));
     PTX_CUDA(c, cudaStreamSynchronize(c->stream));
     float ms = 0.f; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
     s->view.nodes = s->d_nodes; s->view.tris = s->d_tris;
+    s->stats.flat_units = (int32_t)s->flat.units.size();
     s->stats.n_nodes = s->view.n_nodes; s->stats.n_triangles = s->view.n_tris;
     s->stats.node_bytes = (int64_t)node_bytes; s->stats.triangle_bytes = (int64_t)tri_bytes;
     s->stats.sah_cost = sah; s->stats.max_depth = depth; s->stats.builder = builder; s->stats.build_ms = ms;
@@ -703,9 +716,15 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     rp.total_paths = (unsigned long long)rp.n_owned * (unsigned long long)spp_local;
     rp.n_slots = rng_mode == PTX_RNG_XORWOW_COMPAT ? rp.n_owned : (uint32_t)std::min<unsigned long long>(rp.total_paths, kPhiloxPool);
 
-    const int pipeline = opts->pipeline == 0 ? 3 : opts->pipeline;     // 0 = default = the persistent kernel
+    if (!scene->view.nodes) return fail(c, PTX_ERR_INVALID, "ptx_render: the scene has no acceleration structure (a rebuild failed)");
+    // 0 = default: the flat-list kernel when the scene is tiny enough to have one (flat.h), else the persistent BVH8 kernel
+    const bool has_flat = !scene->flat.units.empty() && scene->d_flat_recs != nullptr;
+    if (opts->pipeline == 6 && (!has_flat || guided))
+        return fail(c, PTX_ERR_UNSUPPORTED, "pipeline 6 (flat unit list) needs a scene of at most 20 planar units and BSDF sampling");
+    const int pipeline = opts->pipeline == 0 ? ((has_flat && !guided) ? 6 : 3) : opts->pipeline;
     const bool cta_wave = pipeline == 5;                               // CTA wavefront: same items and hand-off as the persistent kernel
-    const bool persist = pipeline == 3 || cta_wave;
+    const bool flat = pipeline == 6;
+    const bool persist = pipeline == 3 || cta_wave || flat;
     int rc = ensure_pixmap(c, rp.n_owned, persist ? (uint32_t)w * (uint32_t)h : 0u);
     if (rc == PTX_OK && !persist) rc = ensure_wave_capacity(c, rp.n_slots, rp.n_owned);
     if (rc != PTX_OK) return rc;
@@ -772,7 +791,20 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     PTX_CUDA(c, cudaEventRecord(c->ev0, c->stream));
     if (persist) {      // one launch for the whole frame: items are pulled from CTR_NEXT_PATH, nothing else to drive
         if (rng_mode == PTX_RNG_XORWOW_COMPAT && rp.n_owned) PTX_CUDA(c, cudaMemsetAsync(c->ws.progress, 0, (size_t)w * h * sizeof(uint32_t), c->stream));
-        if (cta_wave) launch_path_cta(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->reserved[2]);
+        if (flat) {
+            FlatScene fs{};
+            memcpy(fs.u, scene->flat.units.data(), scene->flat.units.size() * sizeof(FlatUnit));
+            fs.recs = scene->d_flat_recs;
+            fs.n_units = (uint32_t)scene->flat.units.size();
+            float scale = scene->flat.scale;                               // rays start at the camera or on the scene
+            for (int k = 0; k < 3; k++) scale = std::max(scale, std::fabs(cam->origin[k]));
+            flat_margins(scale, fs.m0, fs.m1);
+            int per_sm = opts->reserved[2] & 15;
+            // sequential RNG and fewer than ~3 pixels per resident lane: the frame is bounded by its longest pixel chain, and
+            // fewer warps per SM advance every chain faster (launch_path_persist has the same rule)
+            if (per_sm == 0 && rng_mode == 0 && (unsigned long long)rp.n_owned < 3ull * (unsigned long long)c->prop.multiProcessorCount * 768ull) per_sm = 2;
+            launch_path_flat(c->stream, rng_mode, c->ws, scene->view, fs, fv, cv, rp, c->prop.multiProcessorCount, per_sm);
+        } else if (cta_wave) launch_path_cta(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->reserved[2]);
         else launch_path_persist(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->reserved[2]);
         PTX_CUDA(c, cudaGetLastError());
         st.kernel_launches++;

@@ -2,6 +2,7 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3
 #include "kernels.cuh"
 #include "traverse.h"
+#include "flat.h"
 
 namespace ptx {
 
@@ -16,6 +17,30 @@ __device__ __forceinline__ vec3 v3(float x, float y, float z) { return mk3(x, y,
 __device__ __forceinline__ void warp_count_add(unsigned long long* ctr, bool pred) {
     unsigned m = __ballot_sync(0xFFFFFFFFu, pred);
     if ((threadIdx.x & 31) == 0 && m) atomicAdd(ctr, (unsigned long long)__popc(m));
+}
+
+// Pixel hand-off between the sample chunks of one pixel (compat RNG, k_path_persist / k_path_flat): the lane that finished
+// chunk c stores the pixel's RNG state and running sum, then RELEASES progress[pixel] = c + 1; the lane holding chunk c + 1
+// polls the flag and reads the state.
+//   st_progress : st.release.gpu -- orders the state stores before the flag.
+//   ld_progress : ld.acquire.gpu on the flag.  With the acquire the state loads that follow are ordered after the flag
+//                 load by the PTX memory model itself (release/acquire pattern on one location, morally strong), not by a
+//                 control dependency plus the observation that .cg loads bypass L1 (round 1).  An acquire LOAD is not a
+//                 fence: ptxas emits LDG.E.STRONG.GPU + a CCTL-free ordering, the SM's L1 (which holds the BVH) is left
+//                 alone -- the -20 % measured in round 1 was `fence.acq_rel.gpu` (profiles/r2_handoff_acquire.txt has the
+//                 three variants side by side).  The state itself is still read with .cg loads (L2 is the point of
+//                 coherence; an L1 line filled before the hand-off could be stale).
+__device__ __forceinline__ uint32_t ld_progress(const uint32_t* p) {
+    uint32_t v;
+#if defined(PTX_HANDOFF_RELAXED)
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+#else
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+#endif
+    return v;
+}
+__device__ __forceinline__ void st_progress(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -454,14 +479,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
         if (RNG == 0 && pending) {
             bool ready = chunk == 0u;
             if (!ready) {
-                uint32_t seen;                                                // relaxed gpu-scope load (served by L2)
-                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(ws.progress + pixel) : "memory");
-                ready = seen == chunk;
+                ready = ld_progress(ws.progress + pixel) == chunk;            // acquire load of the hand-off flag (served by L2)
             }
             if (ready) {
-                // The loads below are issued only after the flag value is known (control dependency) and go to L2 (.cg), where
-                // the previous owner's release made its stores visible.  No acquire fence on purpose: a gpu-scope fence
-                // invalidates the SM's whole L1 (CCTL.IVALL), which holds the BVH -- measured -20 % on C2.
+                // The flag was read with ld.acquire (ld_progress): the loads below are ordered after it and see what the previous
+                // owner stored before its release.  They go to L2 (.cg) because an L1 line filled earlier could be stale; no
+                // gpu-scope FENCE on purpose: that invalidates the SM's whole L1 (CCTL.IVALL), which holds the BVH (-20 % on C2).
                 uint4 ra; uint2 rb; float4 f;
                 if (chunk == 0u) { ra = film.rngA[pixel]; rb = film.rngB[pixel]; f = film.accum[pixel]; }
                 else { ra = __ldcg(film.rngA + pixel); rb = __ldcg(film.rngB + pixel); f = __ldcg(film.accum + pixel); }   // L2: L1 may hold a stale line
@@ -515,8 +538,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
                     film.rngA[pixel] = make_uint4(xr.st.v0, xr.st.v1, xr.st.v2, xr.st.v3);
                     film.rngB[pixel] = make_uint2(xr.st.v4, xr.st.d);
                     film.accum[pixel] = make_float4(acc.x, acc.y, acc.z, 0.f);
-                    if (chunk + 1u < n_chunks)                                // release: hand the pixel to whoever holds its next chunk
-                        asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(ws.progress + pixel), "r"(chunk + 1u) : "memory");
+                    if (chunk + 1u < n_chunks) st_progress(ws.progress + pixel, chunk + 1u);   // release: hand the pixel to whoever holds its next chunk
                     alive = false;
                 }
             } else {
@@ -529,6 +551,126 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
         }
         __syncwarp();
         if (done && cont) tr.begin(pv.d, FLT_MAX);
+    }
+    nseg = __reduce_add_sync(kFull, nseg);
+    npaths = __reduce_add_sync(kFull, npaths);
+    if (lane == 0) {
+        if (nseg) atomicAdd(&ws.counters[CTR_SEGMENTS], (unsigned long long)nseg);
+        if (npaths) atomicAdd(&ws.counters[CTR_PATHS], (unsigned long long)npaths);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// persistent path loop for TINY scenes (pipeline 6; the default when the scene has a flat unit list, flat.h): the work
+// items, the chunked pixel hand-off, shading and regeneration of k_path_persist, but the closest hit comes from
+// flat_closest() -- one straight-line pass over <= 20 planar units whose constants are kernel-parameter (constant-bank)
+// operands, then one exact quad / triangle-pair test.  Every lane finishes a segment per iteration, so there is no
+// traversal state, no stack, no waiting list: all 32 lanes shade together (k_path_persist: 21 of 32 per iteration on the
+// Cornell box, and its triangle loop ran at lane efficiency 0.38).  Same hits as the BVH8 path bit for bit (flat.h).
+// ---------------------------------------------------------------------------------------------
+template <int RNG, int BLOCK, int MINB>
+__global__ void __launch_bounds__(BLOCK, MINB) k_path_flat(WaveState ws, SceneView scene, const __grid_constant__ FlatScene fs, FilmView film,
+                                                         CameraView cam, RenderParams rp) {
+    constexpr unsigned kFull = 0xFFFFFFFFu;
+    const int lane = (int)(threadIdx.x & 31);
+    const uint32_t n_chunks = RNG == 0 ? (uint32_t)rp.n_chunks : 0u;
+    const unsigned long long n_items = RNG == 0 ? (unsigned long long)rp.n_owned * n_chunks : rp.total_paths;
+    uint32_t nseg = 0, npaths = 0;
+    PathVertex pv;
+    pv.o = pv.d = pv.beta = v3(0.f, 0.f, 0.f); pv.depth = 0;
+    vec3 L = v3(0.f, 0.f, 0.f), acc = v3(0.f, 0.f, 0.f);
+    uint32_t pixel = 0, sample = 0, chunk = 0;
+    XorwowRng xr; xr.st = Xorwow{0u, 0u, 0u, 0u, 0u, 0u};
+    PhiloxRng pr; pr.blk = Philox4{0u, 0u, 0u, 0u}; pr.lane = 0;
+    float fx = 0.f, fy = 0.f;
+    bool alive = false, pending = false, dry = rp.spp <= 0;
+    for (;;) {
+        // ---- fetch: every lane without work asks for an item; one atomic per warp
+        const bool want = !alive && !pending && !dry;
+        const unsigned need = __ballot_sync(kFull, want);
+        if (need) {
+            unsigned long long base = 0;
+            const int leader = __ffs(need) - 1;
+            if (lane == leader) base = atomicAdd(&ws.counters[CTR_NEXT_PATH], (unsigned long long)__popc(need));
+            base = __shfl_sync(kFull, base, leader);
+            if (want) {
+                const unsigned long long item = base + (unsigned long long)__popc(need & ((1u << lane) - 1u));
+                if (item < n_items) {
+                    pixel = ws.slot_pixel[(uint32_t)(item % rp.n_owned)];
+                    if (RNG == 0) {
+                        chunk = (uint32_t)(item / rp.n_owned);
+                        pending = true;
+                    } else {
+                        sample = (uint32_t)(item / rp.n_owned) + rp.sample_begin;
+                        pr.seek(((unsigned long long)sample << 32) | pixel, 0u, rp.seed);
+                        float ju = pr.next(), jv = pr.next();
+                        start_path_xy(cam, (float)(int)(pixel % (uint32_t)cam.width), (float)(int)(pixel / (uint32_t)cam.width), ju, jv, pv);
+                        L = v3(0.f, 0.f, 0.f);
+                        alive = true;
+                    }
+                } else dry = true;
+            }
+        }
+        // ---- compat: start the chunk once its predecessor has been committed (protocol: see k_path_persist)
+        if (RNG == 0 && pending) {
+            bool ready = chunk == 0u;
+            if (!ready) ready = ld_progress(ws.progress + pixel) == chunk;
+            if (ready) {
+                uint4 ra; uint2 rb; float4 f;
+                if (chunk == 0u) { ra = film.rngA[pixel]; rb = film.rngB[pixel]; f = film.accum[pixel]; }
+                else { ra = __ldcg(film.rngA + pixel); rb = __ldcg(film.rngB + pixel); f = __ldcg(film.accum + pixel); }
+                xr.st = Xorwow{ra.x, ra.y, ra.z, ra.w, rb.x, rb.y};
+                acc = v3(f.x, f.y, f.z);
+                sample = rp.chunk_start[chunk];
+                fx = (float)(int)(pixel % (uint32_t)cam.width); fy = (float)(int)(pixel / (uint32_t)cam.width);
+                float ju = xr.next(), jv = xr.next();
+                start_path_xy(cam, fx, fy, ju, jv, pv);
+                L = v3(0.f, 0.f, 0.f);
+                pending = false; alive = true;
+            }
+        }
+        if (!__any_sync(kFull, alive || pending)) break;
+        // ---- extend: the whole segment
+        float t_hit = FLT_MAX; uint32_t prim = kMiss;
+        if (alive) flat_closest<false>(fs, pv.o, pv.d, 1e-4f, t_hit, prim, nullptr);
+        __syncwarp();
+        // ---- shade every live lane
+        bool cont = true;
+        if (alive) {
+            nseg++;
+            if (RNG == 0) cont = shade_bounce(scene, rp.shade, pv, prim, t_hit, xr, L);
+            else {
+                pr.seek(((unsigned long long)sample << 32) | pixel, 1u + (uint32_t)pv.depth, rp.seed);
+                cont = shade_bounce(scene, rp.shade, pv, prim, t_hit, pr, L);
+            }
+        }
+        __syncwarp();
+        // ---- path ended: commit it; compat lanes go on with the pixel's next sample
+        if (alive && !cont) {
+            npaths++;
+            if (RNG == 0) {
+                acc = acc + L;
+                L = v3(0.f, 0.f, 0.f);
+                sample++;
+                if (sample < rp.chunk_start[chunk + 1u]) {
+                    float ju = xr.next(), jv = xr.next();
+                    start_path_xy(cam, fx, fy, ju, jv, pv);
+                } else {
+                    film.rngA[pixel] = make_uint4(xr.st.v0, xr.st.v1, xr.st.v2, xr.st.v3);
+                    film.rngB[pixel] = make_uint2(xr.st.v4, xr.st.d);
+                    film.accum[pixel] = make_float4(acc.x, acc.y, acc.z, 0.f);
+                    if (chunk + 1u < n_chunks) st_progress(ws.progress + pixel, chunk + 1u);
+                    alive = false;
+                }
+            } else {
+                if (L.x != 0.f || L.y != 0.f || L.z != 0.f) {
+                    float* fa = reinterpret_cast<float*>(film.accum + pixel);
+                    atomicAdd(fa + 0, L.x); atomicAdd(fa + 1, L.y); atomicAdd(fa + 2, L.z);
+                }
+                alive = false;
+            }
+        }
+        __syncwarp();
     }
     nseg = __reduce_add_sync(kFull, nseg);
     npaths = __reduce_add_sync(kFull, npaths);
@@ -1176,6 +1318,22 @@ void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, con
     } else {
         if (rng_mode == 0) k_path_persist<0, kBlock, 3><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
         else k_path_persist<1, kBlock, 3><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+    }
+}
+void launch_path_flat(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FlatScene& fs, const FilmView& film,
+                      const CameraView& cam, const RenderParams& rp, int sm_count, int per_sm) {
+    if (rp.spp <= 0 || !rp.n_owned) return;
+    const unsigned long long items = rng_mode == 0 ? (unsigned long long)rp.n_owned : rp.total_paths;
+    if (per_sm != 2 && per_sm != 4) per_sm = 3;
+    // few pixels per resident lane (a tile-sharded frame on many GPUs): fewer warps per SM, so every pixel's sequential
+    // sample chain advances faster (see launch_path_persist)
+    unsigned g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (items + kBlock - 1) / kBlock);
+    if (per_sm == 4) {
+        if (rng_mode == 0) k_path_flat<0, kBlock, 4><<<g, kBlock, 0, st>>>(ws, scene, fs, film, cam, rp);
+        else k_path_flat<1, kBlock, 4><<<g, kBlock, 0, st>>>(ws, scene, fs, film, cam, rp);
+    } else {
+        if (rng_mode == 0) k_path_flat<0, kBlock, 3><<<g, kBlock, 0, st>>>(ws, scene, fs, film, cam, rp);
+        else k_path_flat<1, kBlock, 3><<<g, kBlock, 0, st>>>(ws, scene, fs, film, cam, rp);
     }
 }
 template <int RNG, int BLOCK, int PPT, int MINB>

@@ -17,6 +17,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include "flat.h"
 #include "layout.h"
 #include "shade.h"
 
@@ -76,6 +77,9 @@ void launch_path_loop(cudaStream_t st, int rng_mode, const WaveState& ws, const 
                       const CameraView& cam, const RenderParams& rp, int q, uint32_t qlen_bound, int iters, int min_blocks);
 void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FilmView& film, const CameraView& cam,
                          const RenderParams& rp, int sm_count, int min_blocks);
+// tiny scenes (pipeline 6): the persistent loop with flat_closest() instead of the BVH8 traversal (flat.h); per_sm = resident CTAs per SM (2, 3, 4)
+void launch_path_flat(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FlatScene& fs, const FilmView& film,
+                      const CameraView& cam, const RenderParams& rp, int sm_count, int per_sm);
 // CTA wavefront (pipeline 5): one launch per frame, paths in shared memory, four dense phases per iteration (kernels.cu)
 void launch_path_cta(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FilmView& film, const CameraView& cam,
                      const RenderParams& rp, int sm_count, int variant);

@@ -116,9 +116,13 @@ struct Traversal {
     PTX_HD void begin(vec3 d, float t_max) {
         sp = 0; closest = t_max; best = kMiss; bestw = kMiss;
         const float ooeps = 8.271806e-25f;   // 2^-80: keeps 1/d finite for axis-parallel rays
-        idx = rcp_fast(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
-        idy = rcp_fast(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
-        idz = rcp_fast(fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
+        // The sign of the substitute follows `d < 0`, the very test visit() orders the slab planes by: copysign() made 1/d
+        // negative for d = -0.0f while visit() took the component for positive, so entry and exit plane were swapped and a
+        // ray with a negative-zero component missed everything (1 segment in 1.5e7 on the Cornell box; found by comparing
+        // with flat_closest, tests/test_host_logic.py::test_negative_zero_direction).
+        idx = rcp_fast(fabsf(d.x) > ooeps ? d.x : (d.x < 0.0f ? -ooeps : ooeps));
+        idy = rcp_fast(fabsf(d.y) > ooeps ? d.y : (d.y < 0.0f ? -ooeps : ooeps));
+        idz = rcp_fast(fabsf(d.z) > ooeps ? d.z : (d.z < 0.0f ? -ooeps : ooeps));
         ng_x = 0; ng_y = 0x80000000u;        // the root as a one-child group
     }
 

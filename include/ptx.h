@@ -98,6 +98,9 @@ typedef struct {
     int32_t max_depth;
     float preprocess_ms;      /* device time of convert-quads / subdivision / packing when they ran on the GPU, else 0 */
     int32_t preprocess_on_device;
+    int32_t flat_units;       /* > 0: the scene is tiny enough for the flat unit list (<= 20 planar quads / triangle pairs):
+                                 ptx_render's default pipeline then runs without a tree (pipeline 6) */
+    int32_t reserved;
 } ptx_scene_stats;
 
 /* replaces loadScene/loadOBJ/loadPBRT + RayTracingManager::buildAccelStructure + Scene(...)

@@ -4,10 +4,13 @@
 // It is never linked into libptx.so; the product path always runs CUDA kernels.
 #include <cstdint>
 #include <cstring>
+#include <cstdio>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
 #include "../cuda-pathtracer_b200/csrc/bvh_host.h"
+#include "../cuda-pathtracer_b200/csrc/flat_host.h"
 #include "../cuda-pathtracer_b200/csrc/loader.h"
 #include "../cuda-pathtracer_b200/csrc/rng.h"
 #include "../cuda-pathtracer_b200/csrc/scene_pack.h"
@@ -20,6 +23,8 @@ struct EmuScene {
     PackedScene packed;
     Bvh8Result bvh;
     SceneView view;
+    FlatHost flat;          // tiny scenes: the unit list of flat.h (empty otherwise)
+    FlatScene fs;
 };
 
 static void finish(EmuScene* s, int max_leaf) {
@@ -34,6 +39,12 @@ static void finish(EmuScene* s, int max_leaf) {
     s->view.n_tris = (uint32_t)s->bvh.tri_src.size();
     s->view.n_prims = (uint32_t)s->packed.prim_shade.size();
     s->view.n_mats = (uint32_t)(s->packed.materials.size() / 2);
+    memset(&s->fs, 0, sizeof s->fs);
+    if (build_flat_units(s->packed.tris.data(), s->packed.tris.size(), s->flat)) {
+        memcpy(s->fs.u, s->flat.units.data(), s->flat.units.size() * sizeof(FlatUnit));
+        s->fs.recs = s->flat.recs.data();
+        s->fs.n_units = (uint32_t)s->flat.units.size();
+    }
 }
 
 extern "C" {
@@ -89,6 +100,26 @@ void emu_primary_ids(const EmuScene* s, const CameraView* cam, int32_t* prim, fl
         }
 }
 
+// tiny scenes: the flat unit list (flat.h).  Returns the unit count (0 = the scene does not qualify).
+int emu_flat_units(const EmuScene* s, float* units_out /* 16 floats per unit, may be NULL */) {
+    if (units_out) memcpy(units_out, s->flat.units.data(), s->flat.units.size() * sizeof(FlatUnit));
+    return (int)s->fs.n_units;
+}
+// closest hits through flat_closest; ctr3 = { rays, rays that needed the every-candidate path, exact unit tests }
+void emu_trace_flat(const EmuScene* s, const float* rays, int64_t n, float t_min, float scale, int32_t* prim, float* t, uint64_t* ctr3) {
+    FlatScene fs = s->fs;
+    flat_margins(scale > 0.f ? scale : s->flat.scale, fs.m0, fs.m1);
+    FlatCounters c = {0, 0, 0};
+    for (int64_t i = 0; i < n; i++) {
+        vec3 o = ld3(rays + 6 * i), d = unit(ld3(rays + 6 * i + 3));
+        float th; uint32_t w;
+        flat_closest<true>(fs, o, d, t_min, th, w, &c);
+        prim[i] = w == kMiss ? -1 : (int32_t)w;
+        t[i] = w == kMiss ? -1.0f : th;
+    }
+    if (ctr3) { ctr3[0] = c.rays; ctr3[1] = c.slow; ctr3[2] = c.unit_tests; }
+}
+
 void emu_jump_tables(uint32_t* out) { xorwow_build_jump_tables(out); }
 void emu_xorwow_init(uint64_t seed, uint64_t subsequence, const uint32_t* tables, uint32_t* out6) {
     Xorwow s = xorwow_seed(seed);
@@ -109,8 +140,26 @@ int64_t emu_scene_nodes(const EmuScene* s, uint32_t* out, int64_t cap_nodes) {  
     for (int64_t i = 0; i < n && i < cap_nodes; i++) memcpy(out + 20 * i, s->bvh.nodes.data() + kNodeQuads * i, 80);
     return n;
 }
+static void emu_render_impl(const EmuScene* s, const CameraView* cam, int spp, int max_depth, uint64_t seed_base, float* linear,
+                            uint8_t* rgb8, uint64_t* segments, bool use_flat, uint64_t* flat_ctr3);
 void emu_render(const EmuScene* s, const CameraView* cam, int spp, int max_depth, uint64_t seed_base, float* linear,
                 uint8_t* rgb8, uint64_t* segments) {
+    emu_render_impl(s, cam, spp, max_depth, seed_base, linear, rgb8, segments, false, nullptr);
+}
+// the same loop with flat_closest instead of the BVH8 traversal (tiny scenes); margins from the scene and camera extent like ptx_render
+void emu_render_flat(const EmuScene* s, const CameraView* cam, int spp, int max_depth, uint64_t seed_base, float* linear,
+                     uint8_t* rgb8, uint64_t* segments, uint64_t* flat_ctr3) {
+    emu_render_impl(s, cam, spp, max_depth, seed_base, linear, rgb8, segments, true, flat_ctr3);
+}
+static void emu_render_impl(const EmuScene* s, const CameraView* cam, int spp, int max_depth, uint64_t seed_base, float* linear,
+                            uint8_t* rgb8, uint64_t* segments, bool use_flat, uint64_t* flat_ctr3) {
+    FlatScene fs = s->fs;
+    {
+        float scale = s->flat.scale;
+        for (int k = 0; k < 3; k++) scale = fmaxf(scale, fabsf(cam->origin[k]));
+        flat_margins(scale, fs.m0, fs.m1);
+    }
+    FlatCounters fc = {0, 0, 0};
     std::vector<uint32_t> tables((size_t)kXorwowJumps * kXorwowJumpWords);
     xorwow_build_jump_tables(tables.data());
     ShadeParams sp = {max_depth, 3, 0.95f, 0};
@@ -131,8 +180,19 @@ void emu_render(const EmuScene* s, const CameraView* cam, int spp, int max_depth
                 vec3 L = mk3(0, 0, 0);
                 for (;;) {
                     float th; seg++;
-                    uint32_t tri = trace_closest<32, true>(s->view, pv.o, pv.d, 1e-4f, FLT_MAX, th, &g_render_ctr);
-                    uint32_t prim = tri == kMiss ? kMiss : f2u(s->view.tris[(size_t)tri * kTriQuads].w);
+                    uint32_t prim;
+                    if (use_flat) {
+                        flat_closest<true>(fs, pv.o, pv.d, 1e-4f, th, prim, &fc);
+                        if (getenv("EMU_FLAT_DEBUG")) {
+                            float th2; uint32_t tri = trace_closest<32, false>(s->view, pv.o, pv.d, 1e-4f, FLT_MAX, th2, nullptr);
+                            uint32_t prim2 = tri == kMiss ? kMiss : f2u(s->view.tris[(size_t)tri * kTriQuads].w);
+                            if (prim2 != prim || (prim != kMiss && th != th2))
+                                fprintf(stderr, "MISMATCH pix %d depth %d o %.9g %.9g %.9g d %.9g %.9g %.9g flat prim %d t %.9g bvh prim %d t %.9g beta %g %g %g\n", pix, pv.depth, pv.o.x, pv.o.y, pv.o.z, pv.d.x, pv.d.y, pv.d.z, (int)prim, th, (int)prim2, th2, pv.beta.x, pv.beta.y, pv.beta.z);
+                        }
+                    } else {
+                        uint32_t tri = trace_closest<32, true>(s->view, pv.o, pv.d, 1e-4f, FLT_MAX, th, &g_render_ctr);
+                        prim = tri == kMiss ? kMiss : f2u(s->view.tris[(size_t)tri * kTriQuads].w);
+                    }
                     if (!shade_bounce(s->view, sp, pv, prim, th, rng, L)) break;
                 }
                 color = color + L;
@@ -142,6 +202,7 @@ void emu_render(const EmuScene* s, const CameraView* cam, int spp, int max_depth
             if (rgb8) { rgb8[3 * pix] = tonemap_channel(color.x); rgb8[3 * pix + 1] = tonemap_channel(color.y); rgb8[3 * pix + 2] = tonemap_channel(color.z); }
         }
     if (segments) *segments = seg;
+    if (flat_ctr3) { flat_ctr3[0] = fc.rays; flat_ctr3[1] = fc.slow; flat_ctr3[2] = fc.unit_tests; }
 }
 
 // grid-guided / MIS modes (shade.h guided_direction) on the CPU: guide records built by build_guide_record from

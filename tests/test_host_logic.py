@@ -36,6 +36,9 @@ def emu(built):
     L.emu_parse_obj.restype = C.c_int64
     L.emu_parse_obj.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_int64]
     L.emu_xorwow_init.argtypes = [C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]
+    L.emu_flat_units.argtypes = [C.c_void_p, C.c_void_p]
+    L.emu_trace_flat.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.emu_render_flat.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     return L
 
 
@@ -234,6 +237,80 @@ def test_empty_and_tiny_scenes(pkg, emu):
         emu.emu_trace(s, P(rays), 2, C.c_float(1e-4), P(ids), P(ts), None)
         assert list(ids) == want
         emu.emu_scene_free(s)
+
+
+# ---- flat unit list for tiny scenes (flat.h) -------------------------------------------------------
+@pytest.mark.parametrize("name,cq", [("cbox_quads", 0), ("cbox", 0), ("cbox_quads", 1)])
+def test_flat_units_same_hits_as_bvh8(pkg, emu, gold, name, cq):
+    """flat_closest (plane + in-plane rectangle filter, one exact test) against the BVH8 traversal and the reference's
+    linear scan: same primitive and bit-identical distance for random rays; a whole path-traced frame identical to the bit
+    (every path takes the same decisions: equal segment counts), and the every-candidate fallback stays rare."""
+    s = emu.emu_scene_load(os.path.join(SCENES, name + ".obj").encode(), cq, 0, 3)
+    units = np.zeros((20, 16), np.float32)
+    nu = emu.emu_flat_units(s, P(units))
+    assert nu == 17                 # 15 planar quads (or coplanar triangle pairs) + the skewed left wall as two triangles
+    n = units[:nu, 0:3]
+    assert np.allclose(np.linalg.norm(n, axis=1), 1, atol=1e-6)
+    assert np.allclose(np.einsum("ij,ij->i", n, units[:nu, 8:11]), 0, atol=1e-6)        # a1 lies in the plane
+    assert np.allclose(np.einsum("ij,ij->i", n, units[:nu, 4:7]) - units[:nu, 3], 0, atol=1e-5)   # so does the centre
+    if cq == 0:
+        rays = np.ascontiguousarray(gold[name + "_rays"])
+        ids = np.zeros(len(rays), np.int32); ts = np.zeros(len(rays), np.float32); c3 = np.zeros(3, np.uint64)
+        emu.emu_trace_flat(s, P(rays), len(rays), C.c_float(1e-4), C.c_float(0), P(ids), P(ts), P(c3))
+        ref = gold[name + "_rays_lin_ids"].astype(np.int32)
+        diff = ids != ref
+        assert diff.sum() <= 2                      # only exact ties may differ
+        assert np.array_equal(bits(ts[~diff]), bits(gold[name + "_rays_lin_t"][~diff]))
+        assert c3[0] == len(rays)
+    w, h, spp, depth = 96, 54, 6, 16
+    v = cam_view(pkg, w, h)
+    a = np.zeros((h, w, 3), np.float32); b = np.zeros_like(a)
+    sa, sb = C.c_uint64(), C.c_uint64(); c3 = np.zeros(3, np.uint64)
+    emu.emu_render(s, C.byref(v), spp, depth, 2023, P(a), None, C.byref(sa))
+    emu.emu_render_flat(s, C.byref(v), spp, depth, 2023, P(b), None, C.byref(sb), P(c3))
+    assert sa.value == sb.value == c3[0]
+    assert np.array_equal(bits(a), bits(b))
+    assert c3[1] / c3[0] < 2e-3                      # rays that needed the every-candidate path
+    assert c3[2] / c3[0] < 0.7                       # exact unit tests per ray (a third of the camera rays miss everything)
+    emu.emu_scene_free(s)
+
+
+def test_flat_units_reject_large_or_degenerate(pkg, emu):
+    prims = pkg.parse_scene_file(os.path.join(SCENES, "cbox.obj"), subdivision=1)      # 128 triangles
+    s = emu.emu_scene_from_prims(P(prims), len(prims), 3)
+    assert emu.emu_flat_units(s, None) == 0
+    emu.emu_scene_free(s)
+    one = np.zeros(2, pkg.PRIM_DTYPE)
+    one["v"][0, :3] = [[0, 0, 0], [1, 0, 0], [0, 1, 0]]; one["v"][1, :3] = [[0, 0, 0], [1, 0, 0], [2, 0, 0]]   # zero area
+    s = emu.emu_scene_from_prims(P(one), 2, 3)
+    assert emu.emu_flat_units(s, None) == 0
+    emu.emu_scene_free(s)
+    s = emu.emu_scene_from_prims(P(one[:1]), 1, 3)                                       # a single triangle: one unit, null second record
+    assert emu.emu_flat_units(s, None) == 1
+    rays = np.array([[0.2, 0.2, 1, 0, 0, -1], [2, 2, 1, 0, 0, -1], [0.2, 0.2, 1, 1, 0, 0]], np.float32)
+    ids = np.zeros(3, np.int32); ts = np.zeros(3, np.float32)
+    emu.emu_trace_flat(s, P(rays), 3, C.c_float(1e-4), C.c_float(0), P(ids), P(ts), None)
+    assert list(ids) == [0, -1, -1] and ts[0] == 1.0
+    emu.emu_scene_free(s)
+
+
+def test_negative_zero_direction(emu):
+    """A direction component of -0.0f: round 1's Traversal::begin took 1/d negative (copysign) while visit() ordered the slab
+    planes as for a positive component, so such a ray missed everything.  Both intersectors must agree with +0.0f."""
+    s = emu.emu_scene_load(os.path.join(SCENES, "cbox_quads.obj").encode(), 0, 0, 3)
+    base = [2.54588914, 5.31591082, -4.15390921]
+    rays = np.array([base + [-0.0, -0.999709547, -0.0241003428], base + [0.0, -0.999709547, -0.0241003428],
+                     [0, 2.5, 3, -0.0, -0.0, -1], [0, 2.5, 3, 0.0, 0.0, -1], [0, 5.0, -2, 0.3, -0.0, -0.0], [0, 5.0, -2, 0.3, 0.0, 0.0]], np.float32)
+    for fn in ("bvh", "flat"):
+        ids = np.zeros(len(rays), np.int32); ts = np.zeros(len(rays), np.float32)
+        if fn == "bvh":
+            emu.emu_trace(s, P(rays), len(rays), C.c_float(1e-4), P(ids), P(ts), None)
+        else:
+            emu.emu_trace_flat(s, P(rays), len(rays), C.c_float(1e-4), C.c_float(0), P(ids), P(ts), None)
+        assert ids[0] == ids[1] == 3 and ts[0] == ts[1] > 5
+        assert ids[2] == ids[3] >= 0 and ts[2] == ts[3]
+        assert ids[4] == ids[5] >= 0 and ts[4] == ts[5]
+    emu.emu_scene_free(s)
 
 
 # ---- integrator core (shade.h) --------------------------------------------------------------------
