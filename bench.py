@@ -84,6 +84,36 @@ def ref_host_run(scene, w, h, spp, depth, frames, threads=0):
     return json.loads(r.stdout.strip().splitlines()[-1])
 
 
+def ref_cuda_run(scene, w, h, spp, depth, frames=1, orig=False, gpu=0):
+    """The reference's own CUDA kernels on this box's GPU (oracle/_ref/ref_cuda: its unmodified headers compiled for sm_100a;
+    `render_twin` = `render` with max_depth as a parameter, orig=True = `render` exactly as it ships, depth 5).  CUDA-event ms."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_cuda")
+    env = dict(os.environ)
+    env["CUDA_VISIBLE_DEVICES"] = str(gpu)
+    r = subprocess.run([exe, "render", scene, str(w), str(h), str(spp), str(depth), str(frames), "-", "0", "0", "1" if orig else "0"],
+                       capture_output=True, text=True, check=True, env=env, timeout=900)
+    return json.loads(r.stdout.strip().splitlines()[-1])
+
+
+def gpu_baseline(scene_path, w, h, spp, depth, segments_per_frame, segments_depth5=None):
+    """R-GPU baseline of BASELINE.json's metric: the reference's CUDA build on the same B200, same frame, right before the
+    timed region.  The reference has no segment counter; its streams are the product's (compat RNG), so the product's exact
+    count for the same frame converts its ms/frame into the metric."""
+    out = {"unit": METRIC, "impl": "oracle/_ref/ref_cuda (reference headers, nvcc -O3 sm_100a, block 16x16)"}
+    try:
+        ref_cuda_run(scene_path, 256, 256, 4, depth)            # warm-up: context creation, module load
+        j = ref_cuda_run(scene_path, w, h, spp, depth, frames=2)
+        out.update(kernel="render_twin (render with max_depth as a parameter)", ms_per_frame=j["ms_per_frame"], ms_init=j["ms_init"],
+                   value=segments_per_frame / (j["ms_per_frame"] * 1e-3) * 1e-6, segments_per_frame=segments_per_frame,
+                   segments_source="device counter of this build on the same frame (same RNG streams)")
+        o = ref_cuda_run(scene_path, w, h, spp, depth, frames=2, orig=True)
+        out["unmodified_render_depth5"] = {"kernel": "render", "ms_per_frame": o["ms_per_frame"],
+                                           "value": (segments_depth5 / (o["ms_per_frame"] * 1e-3) * 1e-6) if segments_depth5 else None}
+    except Exception as e:       # noqa: BLE001
+        out["error"] = str(e)[:300]
+    return out
+
+
 def segments_per_path_estimate(scene, w, h, depth):
     """Exact segment counts come from the oracle (same streams as the reference): used to convert the
     reference's ms/frame into the metric, since the reference has no segment counter."""
@@ -139,7 +169,8 @@ def run_ours(args, scene_path, w, h, spp, depth):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     rng_mode = pkg.RNG_PHILOX if args.rng == "philox" else pkg.RNG_XORWOW_COMPAT
-    pipeline = {"fused": pkg.PIPELINE_FUSED, "wavefront": pkg.PIPELINE_WAVEFRONT, "loop": pkg.PIPELINE_LOOP, "persist": pkg.PIPELINE_PERSIST, "cta": pkg.PIPELINE_CTA}[args.pipeline]
+    pipeline = {"fused": pkg.PIPELINE_FUSED, "wavefront": pkg.PIPELINE_WAVEFRONT, "loop": pkg.PIPELINE_LOOP, "persist": pkg.PIPELINE_PERSIST, "cta": pkg.PIPELINE_CTA,
+                "flat": pkg.PIPELINE_FLAT, "auto": pkg.PIPELINE_DEFAULT}[args.pipeline]
     shard_mode = pkg.SHARD_NONE if world == 1 else (pkg.SHARD_SAMPLES if rng_mode == pkg.RNG_PHILOX else pkg.SHARD_TILES)
 
     dist = torch = None
@@ -205,6 +236,17 @@ def run_ours(args, scene_path, w, h, spp, depth):
             film.resolve_device()                     # RGB8 stays in HBM (the film's own device buffer)
         return st
 
+    gpu_base = None
+    if rank == 0 and not generated and not args.no_gpu_baseline:
+        # one frame of ours for the exact segment counts (depth of the config, and depth 5 for the unmodified kernel), then the
+        # reference's CUDA kernels on this very GPU; the other ranks wait at the barrier below
+        kw1 = dict(kw); kw1.update(shard_mode=pkg.SHARD_NONE, shard_rank=0, shard_world=1)
+        seg_full = ctx.render(scene, cam, film, **kw1)["segments"]
+        kw5 = dict(kw1); kw5.update(max_depth=5)
+        seg_d5 = ctx.render(scene, cam, film, **kw5)["segments"]
+        ctx.sync()
+        gpu_base = gpu_baseline(scene_path, w, h, spp, depth, seg_full, seg_d5)
+        film.reset()
     for _ in range(args.warmup):
         step(False)
     # ---- timed region A: inputs resident in HBM, device events on the launching stream ------------
@@ -252,14 +294,17 @@ def run_ours(args, scene_path, w, h, spp, depth):
         # algorithmic bytes per segment of the dominant kernel
         loop = pipeline == pkg.PIPELINE_LOOP
         bytes_per_slot_launch = None
-        if pipeline == pkg.PIPELINE_PERSIST:
+        if pipeline in (pkg.PIPELINE_PERSIST, pkg.PIPELINE_FLAT, pkg.PIPELINE_DEFAULT):
             # no path state in memory: per owned pixel and sample chunk the compat kernel moves its id 4 + RNG state 24 + 24 + pixel sum 16 + 16 bytes;
             # per path the counter-RNG kernel moves its pixel id 4 + three float atomics 12
             # (a pixel is handed on between its sample chunks: per chunk pixel id 4 + RNG state 24 + 24 + pixel sum 16 + 16 + progress flag 4 + 4)
             n_chunks = compat_chunk_count(spp, args.chunks, (w * h / world) / (ctx.device_info()["sm_count"] * 768.0))
             per_item = 92.0 * n_chunks * (w * h / world) if rng_mode == pkg.RNG_XORWOW_COMPAT else 16.0 * st_t["paths"]
             bytes_per_seg = per_item / max(st_t["segments"], 1)
-            kname, k_ms = "k_path_persist<rng> (one launch per frame: extend+shade+regenerate, all state in registers)", st_t["shade_ms"]
+            is_flat = pipeline == pkg.PIPELINE_FLAT or (pipeline == pkg.PIPELINE_DEFAULT and scene_stats.get("flat_units", 0) > 0)
+            kname = ("k_path_flat<rng> (one launch per frame: flat unit-list extend + shade + regenerate, all state in registers)" if is_flat else
+                     "k_path_persist<rng> (one launch per frame: BVH8 extend + shade + regenerate, all state in registers)")
+            k_ms = st_t["shade_ms"]
         elif loop:
             # per live slot per launch: queue 4 + read A,B,C,E 64 + D 8 + write A,B,C,E 64 + D 8, compat adds RNG 24+24 and pixel sum 16+16
             bytes_per_slot_launch = 148 + (80 if rng_mode == pkg.RNG_XORWOW_COMPAT else 0)
@@ -284,7 +329,7 @@ def run_ours(args, scene_path, w, h, spp, depth):
         achieved = st_t["segments"] * bytes_per_seg / (k_ms * 1e-3) * 1e-9 if k_ms > 0 else None
         # measured DRAM bytes per launch of the dominant kernel (ncu capture of this very configuration, profiles/traffic.json)
         traffic = traffic_src = issue = None
-        tkey = f"{args.workload}/{args.rng}/{args.pipeline}"
+        tkey = f"{args.workload}/{args.rng}/{'flat' if (pipeline in (pkg.PIPELINE_FLAT, pkg.PIPELINE_DEFAULT) and scene_stats.get('flat_units', 0) > 0) else ('persist' if args.pipeline == 'auto' else args.pipeline)}"
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if world == 1 and args.spp == 0 and os.path.exists(tpath):
             ent = json.load(open(tpath)).get(tkey)
@@ -309,8 +354,13 @@ def run_ours(args, scene_path, w, h, spp, depth):
                          "traversal": traversal, "bytes_per_slot_launch": bytes_per_slot_launch,
                          # not part of the contract: what ncu says about the bound that really limits this kernel (issue slots)
                          "issue": issue},
-            "scene": {k: scene_stats[k] for k in ("n_triangles", "n_nodes", "node_bytes", "triangle_bytes", "build_ms", "builder", "max_depth", "sah_cost")},
+            "scene": {k: scene_stats[k] for k in ("n_triangles", "n_nodes", "node_bytes", "triangle_bytes", "build_ms", "builder", "max_depth", "sah_cost", "flat_units")},
         }
+        if gpu_base is not None:
+            out["gpu_baseline"] = gpu_base
+            if gpu_base.get("value"):
+                out["gpu_baseline"]["speedup_device"] = value / gpu_base["value"] / world
+                out["gpu_baseline"]["note"] = "speedup_device = value / n_gpus / gpu_baseline.value (per-GPU throughput of this build over the reference CUDA build on one B200)"
         if world == 1 and not args.no_cpu_baseline and generated:
             out["cpu_baseline"] = {"value": None, "unit": METRIC, "cores": 0, "kind": "reference",
                                    "sample": "not runnable: the reference keeps 4 364-byte primitives (45.8 GB for this scene) and builds its BVH on one host thread (BASELINE.md)"}
@@ -368,10 +418,12 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rng", default="compat", choices=["compat", "philox"])
-    ap.add_argument("--pipeline", default="persist", choices=["persist", "loop", "fused", "wavefront", "cta"])
+    ap.add_argument("--pipeline", default="auto", choices=["auto", "flat", "persist", "loop", "fused", "wavefront", "cta"],
+                    help="auto = the library default: the flat unit-list kernel for tiny scenes, else the persistent BVH8 kernel")
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override spp (reduced runs are NOT the headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-baseline", action="store_true")
     ap.add_argument("--min-blocks", type=int, default=0, help="experiment: occupancy variant of the path-loop kernels (0 = 3x256 threads/SM, 4 = 4x256, 7 = 7x128)")
     ap.add_argument("--chunks", type=int, default=0, help="experiment: work items per pixel of the persistent kernel, compat RNG (0 = default 6, 1 = none)")
     ap.add_argument("--shade-batch", type=int, default=0, help="experiment: waiting lanes per warp that trigger a shading round (0 = default 12, 1 = at once)")
