@@ -793,7 +793,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
         if (rng_mode == PTX_RNG_XORWOW_COMPAT && rp.n_owned) PTX_CUDA(c, cudaMemsetAsync(c->ws.progress, 0, (size_t)w * h * sizeof(uint32_t), c->stream));
         if (flat) {
             FlatScene fs{};
-            memcpy(fs.u, scene->flat.units.data(), scene->flat.units.size() * sizeof(FlatUnit));
+            for (size_t k = 0; k < scene->flat.units.size(); k++) flat_set_unit(fs, (int)k, scene->flat.units[k]);
             fs.recs = scene->d_flat_recs;
             fs.n_units = (uint32_t)scene->flat.units.size();
             float scale = scene->flat.scale;                               // rays start at the camera or on the scene

@@ -38,13 +38,34 @@ struct FlatUnit {                      // 64 bytes, read as constant-bank operan
     float a2x, a2y, a2z, pad;
 };
 
+// Two units side by side, every constant as a (unit 2j, unit 2j + 1) pair: the device filter handles a pair per step with
+// packed FP32x2 arithmetic (FFMA2 takes the constant pair from a uniform-register pair and the ray component as a
+// broadcast scalar), which halves the issue slots of the dot products.  mc = -c.
+struct FlatPair {                      // 128 bytes
+    float nx[2], ny[2], nz[2], mc[2];
+    float ncx[2], ncy[2], ncz[2], h1[2];     // MINUS the centre of the bounding rectangle
+    float a1x[2], a1y[2], a1z[2], h2[2];
+    float a2x[2], a2y[2], a2z[2], pad[2];
+};
+
 struct FlatScene {
-    FlatUnit u[kFlatUnits];
+    FlatPair p[kFlatUnits / 2];
     const f32x4* recs;                 // kFlatRecQuads float4 per unit: { v0, prim }, { e1 }, { e2 } twice
     uint32_t n_units;
     float m0, m1;                      // margins, see flat_margins()
     uint32_t pad;
 };
+
+// unit k of the list; slots never set stay all-zero: n = 0 -> 1 / 0 = inf -> NaN / inf everywhere, so the loop bound
+// n_units (not the data) decides what is evaluated
+inline void flat_set_unit(FlatScene& fs, int k, const FlatUnit& u) {
+    FlatPair& p = fs.p[k >> 1];
+    const int i = k & 1;
+    p.nx[i] = u.nx; p.ny[i] = u.ny; p.nz[i] = u.nz; p.mc[i] = -u.c;
+    p.ncx[i] = -u.cx; p.ncy[i] = -u.cy; p.ncz[i] = -u.cz; p.h1[i] = u.h1;
+    p.a1x[i] = u.a1x; p.a1y[i] = u.a1y; p.a1z[i] = u.a1z; p.h2[i] = u.h2;
+    p.a2x[i] = u.a2x; p.a2y[i] = u.a2y; p.a2z[i] = u.a2z; p.pad[i] = 0.f;
+}
 
 // Margins for rays whose origins and the scene lie within `scale` of the coordinate origin.
 //   error of t = num / den:  num = c - n.o cancels to ~ 4 ulp of `scale`, den to ~ 3 ulp of 1, |t| <= 2 * scale:
@@ -80,45 +101,114 @@ struct FlatCounters {
     uint32_t rays, slow, unit_tests;
 };
 
+// packed pair helpers: FFMA2 / FMUL2 / FADD2 on the device (sm_100: one issue slot for two IEEE operations), the same two
+// operations one after the other on the host
+struct f2 {
+    float x, y;
+};
+PTX_HD f2 mk2(float a, float b) { f2 r; r.x = a; r.y = b; return r; }
+PTX_HD f2 ld2(const float* p) {
+#if defined(__CUDA_ARCH__)
+    const float2 v = *reinterpret_cast<const float2*>(p);
+    return mk2(v.x, v.y);
+#else
+    return mk2(p[0], p[1]);
+#endif
+}
+PTX_HD f2 fma2(f2 a, f2 b, f2 c) {
+#if defined(__CUDA_ARCH__)
+    const float2 r = __ffma2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y), make_float2(c.x, c.y));
+    return mk2(r.x, r.y);
+#else
+    return mk2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y));
+#endif
+}
+PTX_HD f2 mul2(f2 a, f2 b) {
+#if defined(__CUDA_ARCH__)
+    const float2 r = __fmul2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y));
+    return mk2(r.x, r.y);
+#else
+    return mk2(a.x * b.x, a.y * b.y);
+#endif
+}
+PTX_HD f2 add2(f2 a, f2 b) {
+#if defined(__CUDA_ARCH__)
+    const float2 r = __fadd2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y));
+    return mk2(r.x, r.y);
+#else
+    return mk2(a.x + b.x, a.y + b.y);
+#endif
+}
+
+// min / max that drop a NaN SECOND operand and never produce one from a non-NaN first operand: what FMNMX does on the device.
+// (glibc's fminf returns NaN for a signalling NaN, and (-inf & ~31) | k is one.)
+PTX_HD float min_nn(float a, float b) {
+#if defined(__CUDA_ARCH__)
+    return fminf(a, b);
+#else
+    return b < a ? b : a;
+#endif
+}
+PTX_HD float max_nn(float a, float b) {
+#if defined(__CUDA_ARCH__)
+    return fmaxf(a, b);
+#else
+    return b > a ? b : a;
+#endif
+}
+
+// one unit's share of the selection: key = lower bound t - m with the unit index in its low 5 bits, so ONE min tracks both
+// the smallest bound and whose it is; t2 = second smallest key.  A NaN key (ray parallel to the plane: 0 * inf) drops out
+// of min_nn / max_nn by itself, and such a unit cannot be hit (intersect_tri rejects |det| < 1e-8).
+PTX_HD void flat_select(int k, float t, float nm, float e1, float e2, float hm1, float hm2, float t_min, float& tbest, float& t2) {
+    // negated comparisons: an infinite margin makes the unit a candidate
+    const bool cand = !(fabsf(e1) > hm1) && !(fabsf(e2) > hm2) && !(t - nm < t_min);
+    const float key = u2f((f2u(t + nm) & 0xFFFFFFE0u) | (uint32_t)k);
+    if (cand) {
+        t2 = min_nn(t2, max_nn(tbest, key));
+        tbest = min_nn(tbest, key);
+    }
+}
+
 // Closest hit of (o, d) in [t_min, FLT_MAX).  closest / bestw (primitive id or kMiss) as Traversal leaves them.
 template <bool COUNT>
 PTX_HD void flat_closest(const FlatScene& fs, vec3 o, vec3 d, float t_min, float& closest, uint32_t& bestw, FlatCounters* ctr) {
     const float kInf = u2f(0x7F800000u);
     float tbest = kInf, t2 = kInf;
-    uint32_t kbest = 0, mask = 0;
     const uint32_t n = fs.n_units;
+    const f2 ox = mk2(o.x, o.x), oy = mk2(o.y, o.y), oz = mk2(o.z, o.z);
+    const f2 dx = mk2(d.x, d.x), dy = mk2(d.y, d.y), dz = mk2(d.z, d.z);
+    const float nm1 = -fs.m1, nm0 = -fs.m0;
 #pragma unroll
-    for (int k = 0; k < kFlatUnits; k++) {
-        if ((uint32_t)k < n) {                                        // uniform
-        const FlatUnit& u = fs.u[k];
-        const float den = fmaf(u.nz, d.z, fmaf(u.ny, d.y, u.nx * d.x));
-        const float num = fmaf(-u.nz, o.z, fmaf(-u.ny, o.y, fmaf(-u.nx, o.x, u.c)));
-        const float rden = rcp_ftz(den);
-        const float t = num * rden;
-        const float m = fmaf(fabsf(rden), fs.m1, fs.m0);
-        const float px = fmaf(t, d.x, o.x) - u.cx, py = fmaf(t, d.y, o.y) - u.cy, pz = fmaf(t, d.z, o.z) - u.cz;
-        const float e1 = fabsf(fmaf(u.a1z, pz, fmaf(u.a1y, py, u.a1x * px))) - u.h1;
-        const float e2 = fabsf(fmaf(u.a2z, pz, fmaf(u.a2y, py, u.a2x * px))) - u.h2;
-        // negated comparisons: a NaN (den = 0, num = 0) or an infinite margin (den = 0) makes the unit a candidate
-        const bool cand = !(fmaxf(e1, e2) > m) && !(t + m < t_min);
-        const float tc = cand ? t - m : kInf;
-        if (cand) mask |= 1u << k;
-        t2 = fminf(t2, fmaxf(tc, tbest));                             // second smallest lower bound so far
-        if (tc < tbest) kbest = (uint32_t)k;
-        tbest = fminf(tbest, tc);
+    for (int j = 0; j < kFlatUnits / 2; j++) {
+        if ((uint32_t)(2 * j) < n) {                                  // uniform
+            const FlatPair& u = fs.p[j];
+            const f2 den = fma2(ld2(u.nz), dz, fma2(ld2(u.ny), dy, mul2(ld2(u.nx), dx)));
+            const f2 numn = fma2(ld2(u.nz), oz, fma2(ld2(u.ny), oy, fma2(ld2(u.nx), ox, ld2(u.mc))));     // n.o - c
+            const f2 rn = mk2(rcp_ftz(-den.x), rcp_ftz(-den.y));
+            const f2 t = mul2(numn, rn);
+            const f2 nm = mk2(fmaf(fabsf(rn.x), nm1, nm0), fmaf(fabsf(rn.y), nm1, nm0));                   // -(m0 + m1 / |n.d|)
+            const f2 px = add2(fma2(t, dx, ox), ld2(u.ncx)), py = add2(fma2(t, dy, oy), ld2(u.ncy)), pz = add2(fma2(t, dz, oz), ld2(u.ncz));
+            const f2 e1 = fma2(ld2(u.a1z), pz, fma2(ld2(u.a1y), py, mul2(ld2(u.a1x), px)));
+            const f2 e2 = fma2(ld2(u.a2z), pz, fma2(ld2(u.a2y), py, mul2(ld2(u.a2x), px)));
+            const f2 hm1 = mk2(u.h1[0] - nm.x, u.h1[1] - nm.y), hm2 = mk2(u.h2[0] - nm.x, u.h2[1] - nm.y);
+            flat_select(2 * j, t.x, nm.x, e1.x, e2.x, hm1.x, hm2.x, t_min, tbest, t2);
+            if ((uint32_t)(2 * j + 1) < n) flat_select(2 * j + 1, t.y, nm.y, e1.y, e2.y, hm1.y, hm2.y, t_min, tbest, t2);
         }
     }
     closest = FLT_MAX; bestw = kMiss;
     if (COUNT) ctr->rays++;
-    if (mask) {
+    if (tbest < kInf) {
+        const uint32_t kbest = f2u(tbest) & 31u;
         flat_test_unit(fs.recs, kbest, o, d, t_min, closest, bestw);
         if (COUNT) ctr->unit_tests++;
-        if (!(bestw != kMiss && closest < t2)) {                      // not provably the closest: test the other candidates too
-            if (COUNT && (mask & ~(1u << kbest))) ctr->slow++;
-            mask &= ~(1u << kbest);
-            while (mask) {
-                const uint32_t k = hi_bit(mask);
-                mask &= ~(1u << k);
+        // the keys carry the unit index in their low bits, i.e. they may exceed their bound by < 32 ulp: take 2^-18 off
+        if (!(bestw != kMiss && closest < fmaf(t2, -3.8146973e-06f, t2)) && t2 < kInf) {
+            // not provably the closest (two candidates within their margins: a ray into the edge between two walls; a grazing
+            // plane; a false candidate in front): every other unit gets its exact test.  Rare (< 1e-3 of the rays).
+            if (COUNT) ctr->slow++;
+            for (uint32_t k = 0; k < n; k++) {
+                if (k == kbest) continue;
                 flat_test_unit(fs.recs, k, o, d, t_min, closest, bestw);
                 if (COUNT) ctr->unit_tests++;
             }

@@ -22,22 +22,24 @@ __device__ __forceinline__ void warp_count_add(unsigned long long* ctr, bool pre
 // Pixel hand-off between the sample chunks of one pixel (compat RNG, k_path_persist / k_path_flat): the lane that finished
 // chunk c stores the pixel's RNG state and running sum, then RELEASES progress[pixel] = c + 1; the lane holding chunk c + 1
 // polls the flag and reads the state.
-//   st_progress : st.release.gpu -- orders the state stores before the flag.
-//   ld_progress : ld.acquire.gpu on the flag.  With the acquire the state loads that follow are ordered after the flag
-//                 load by the PTX memory model itself (release/acquire pattern on one location, morally strong), not by a
-//                 control dependency plus the observation that .cg loads bypass L1 (round 1).  An acquire LOAD is not a
-//                 fence: ptxas emits LDG.E.STRONG.GPU + a CCTL-free ordering, the SM's L1 (which holds the BVH) is left
-//                 alone -- the -20 % measured in round 1 was `fence.acq_rel.gpu` (profiles/r2_handoff_acquire.txt has the
-//                 three variants side by side).  The state itself is still read with .cg loads (L2 is the point of
-//                 coherence; an L1 line filled before the hand-off could be stale).
-__device__ __forceinline__ uint32_t ld_progress(const uint32_t* p) {
+//   st_progress    : st.release.gpu -- orders the state stores before the flag.
+//   progress_ready : polls with ld.relaxed.gpu (served by L2, no side effect) and, ONCE the expected value is seen, reads the
+//                    flag again with ld.acquire.gpu.  That acquire load observes the release store (or a later value in the
+//                    flag's modification order -- there is none before this lane itself writes c + 2), so the state loads
+//                    that follow it are ordered after the previous owner's stores by the PTX memory model itself
+//                    (release / acquire on one location), not by a control dependency plus the observation that .cg loads
+//                    bypass L1, as in round 1.  ptxas compiles ld.acquire.gpu to LDG.E.STRONG.GPU + CCTL.IVALL, i.e. it
+//                    invalidates the SM's L1 (seen in the SASS and as a stall site in profiles/r2b_*): paying that on every
+//                    poll cost 6 % on the BVH8 kernel, whose tree lives in L1; once per chunk start it is 6 invalidations
+//                    per pixel and frame.  -DPTX_HANDOFF_RELAXED builds the round-1 protocol for A/B measurements.
+__device__ __forceinline__ bool progress_ready(const uint32_t* p, uint32_t expect) {
     uint32_t v;
-#if defined(PTX_HANDOFF_RELAXED)
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-#else
+    if (v != expect) return false;
+#if !defined(PTX_HANDOFF_RELAXED)
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
 #endif
-    return v;
+    return v == expect;
 }
 __device__ __forceinline__ void st_progress(uint32_t* p, uint32_t v) {
     asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
@@ -479,10 +481,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
         if (RNG == 0 && pending) {
             bool ready = chunk == 0u;
             if (!ready) {
-                ready = ld_progress(ws.progress + pixel) == chunk;            // acquire load of the hand-off flag (served by L2)
+                ready = progress_ready(ws.progress + pixel, chunk);            // relaxed poll, one acquire load on success
             }
             if (ready) {
-                // The flag was read with ld.acquire (ld_progress): the loads below are ordered after it and see what the previous
+                // The flag was read with ld.acquire (progress_ready): the loads below are ordered after it and see what the previous
                 // owner stored before its release.  They go to L2 (.cg) because an L1 line filled earlier could be stale; no
                 // gpu-scope FENCE on purpose: that invalidates the SM's whole L1 (CCTL.IVALL), which holds the BVH (-20 % on C2).
                 uint4 ra; uint2 rb; float4 f;
@@ -614,7 +616,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_flat(WaveState ws, SceneVi
         // ---- compat: start the chunk once its predecessor has been committed (protocol: see k_path_persist)
         if (RNG == 0 && pending) {
             bool ready = chunk == 0u;
-            if (!ready) ready = ld_progress(ws.progress + pixel) == chunk;
+            if (!ready) ready = progress_ready(ws.progress + pixel, chunk);
             if (ready) {
                 uint4 ra; uint2 rb; float4 f;
                 if (chunk == 0u) { ra = film.rngA[pixel]; rb = film.rngB[pixel]; f = film.accum[pixel]; }

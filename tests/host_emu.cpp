@@ -41,7 +41,7 @@ static void finish(EmuScene* s, int max_leaf) {
     s->view.n_mats = (uint32_t)(s->packed.materials.size() / 2);
     memset(&s->fs, 0, sizeof s->fs);
     if (build_flat_units(s->packed.tris.data(), s->packed.tris.size(), s->flat)) {
-        memcpy(s->fs.u, s->flat.units.data(), s->flat.units.size() * sizeof(FlatUnit));
+        for (size_t k = 0; k < s->flat.units.size(); k++) flat_set_unit(s->fs, (int)k, s->flat.units[k]);
         s->fs.recs = s->flat.recs.data();
         s->fs.n_units = (uint32_t)s->flat.units.size();
     }

@@ -70,8 +70,13 @@ def test_full_config_vs_reference_cuda_kernels(pkg, ctx, tmp_path, tag, scene, w
     report(tag, mean_rel_err=err, pixels_differing=differ, pixels=w * h, rgb8_max_diff=int(d8.max()), rgb8_identical=float((d8 == 0).mean()),
            ref_ms=info["ms_per_frame"], ours_ms=st["render_ms"], segments=st["segments"])
     assert err <= TOL_IMAGE, err
-    assert d8.max() <= 1 and (d8 == 0).mean() >= 0.99
-    assert differ <= 0.02 * w * h       # a different pixel = one of its paths took another decision somewhere (1-ulp libm / contraction differences)
+    # Pixels whose linear radiance equals the reference's to 1e-5 relative must be within 1 LSB in RGB8 (device powf both sides).
+    # A pixel that differs more is one where a path took another decision somewhere (a 1-ulp libm / contraction difference moved a
+    # Russian-roulette or hit test): at 64 spp that moves the pixel by whole LSBs, so those are COUNTED and bounded instead.
+    same = (np.abs(lin.astype(np.float64) - rlin) <= 1e-5 * np.maximum(rlin, 1e-3)).all(-1)
+    assert d8[same].max() <= 1 and (d8 == 0).mean() >= 0.99
+    assert (~same).sum() <= 1e-3 * w * h, int((~same).sum())
+    assert differ <= 0.02 * w * h
     # every pipeline that is not the default must give the default's film (bit for bit but for exact hit-distance ties)
     if spp <= 64:
         for pipe in (pkg.PIPELINE_PERSIST, pkg.PIPELINE_FLAT):
