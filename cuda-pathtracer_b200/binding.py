@@ -14,6 +14,7 @@ LIB_PATH = os.environ.get("PTX_LIB") or os.path.join(HERE, "libptx.so")      # P
 
 RNG_XORWOW_COMPAT, RNG_PHILOX = 0, 1
 SHARD_NONE, SHARD_TILES, SHARD_SAMPLES = 0, 1, 2
+NOALLOC_MAX_RAYS = 65536
 PIPELINE_DEFAULT, PIPELINE_FUSED, PIPELINE_LOOP, PIPELINE_PERSIST, PIPELINE_WAVEFRONT, PIPELINE_CTA, PIPELINE_FLAT = 0, 1, 2, 3, 4, 5, 6
 SAMPLING_BSDF, SAMPLING_FORMFACTOR, SAMPLING_RADIOSITY, SAMPLING_MIS, SAMPLING_TOPK = 0, 1, 2, 3, 4
 
@@ -83,7 +84,7 @@ EXPORTS = [
     "ptx_film_create", "ptx_film_reset", "ptx_film_clear", "ptx_film_resolve_rgb8", "ptx_film_read_linear", "ptx_film_write", "ptx_write_png_rgb8",
     "ptx_film_device_buffer", "ptx_film_set_sample_count", "ptx_film_destroy",
     "ptx_shard_pixel_count", "ptx_shard_owned_pixels", "ptx_shard_sample_range",
-    "ptx_render", "ptx_render_stats_get", "ptx_trace_primary_ids", "ptx_trace_rays", "ptx_trace_occluded", "ptx_render_visibility", "ptx_film_rng_state",
+    "ptx_render", "ptx_render_stats_get", "ptx_trace_primary_ids", "ptx_trace_rays", "ptx_trace_rays_noalloc", "ptx_trace_occluded", "ptx_render_visibility", "ptx_film_rng_state",
 ]
 
 _lib = None
@@ -105,6 +106,7 @@ def lib():
         L.ptx_film_set_sample_count.argtypes = [C.c_void_p, C.c_float]
         L.ptx_ctx_flush_l2.argtypes = [C.c_void_p]
         L.ptx_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_float, C.c_void_p, C.c_void_p]
+        L.ptx_trace_rays_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_float, C.c_void_p, C.c_void_p]
         L.ptx_trace_occluded.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.ptx_render_visibility.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.ptx_film_reset.argtypes = [C.c_void_p, C.c_uint64]
@@ -300,6 +302,14 @@ class Context:
         ids = np.empty(len(rays), np.int32)
         ts = np.empty(len(rays), np.float32)
         _check(lib().ptx_trace_rays(self._h, scene._h, _ptr(rays), len(rays), C.c_float(t_min), _ptr(ids), _ptr(ts)), self._h)
+        return ids, ts
+
+    def trace_rays_noalloc(self, scene, rays, t_min=1e-4):
+        """ptx_trace_rays_noalloc: the same query without any device allocation (at most NOALLOC_MAX_RAYS rays per call)."""
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
+        ids = np.empty(len(rays), np.int32)
+        ts = np.empty(len(rays), np.float32)
+        _check(lib().ptx_trace_rays_noalloc(self._h, scene._h, _ptr(rays), len(rays), C.c_float(t_min), _ptr(ids), _ptr(ts)), self._h)
         return ids, ts
 
     def flush_l2(self):

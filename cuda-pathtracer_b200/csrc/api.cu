@@ -958,6 +958,21 @@ int ptx_trace_rays(ptx_ctx* c, const ptx_scene* scene, const float* rays_host, s
     return PTX_OK;
 }
 
+// No counterpart in the reference.  Same result as ptx_trace_rays, but no
+// cudaMalloc / cudaFree (nor any other allocating call) happens here: the device staging is a file-scope array of kernels.cu.
+int ptx_trace_rays_noalloc(ptx_ctx* c, const ptx_scene* scene, const float* rays_host, size_t n, float t_min, int32_t* prim_id_host, float* t_host) {
+    if (!c || !scene || (n && (!rays_host || !prim_id_host || !t_host))) return fail(c, PTX_ERR_INVALID, "ptx_trace_rays_noalloc: bad argument");
+    if (scene->ctx != c) return fail(c, PTX_ERR_INVALID, "ptx_trace_rays_noalloc: the scene belongs to another context");
+    if (n > (size_t)PTX_NOALLOC_MAX_RAYS)
+        return fail(c, PTX_ERR_INVALID, "ptx_trace_rays_noalloc: at most PTX_NOALLOC_MAX_RAYS (65536) rays per call; split the batch or use ptx_trace_rays");
+    if (!scene->view.nodes) return fail(c, PTX_ERR_INVALID, "ptx_trace_rays_noalloc: the scene has no acceleration structure");
+    if (!n) return PTX_OK;
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    cudaError_t e = trace_rays_noalloc(c->stream, c->device, scene->view, rays_host, n, t_min, prim_id_host, t_host);
+    if (e != cudaSuccess) return cuda_fail(c, e, "ptx_trace_rays_noalloc");
+    return PTX_OK;
+}
+
 int ptx_ctx_flush_l2(ptx_ctx* c) {
     if (!c) return fail(nullptr, PTX_ERR_INVALID, "ptx_ctx_flush_l2: ctx is NULL");
     PTX_CUDA(c, cudaSetDevice(c->device));

@@ -1,6 +1,8 @@
 // kernels.cu -- hand-written sm_100a kernels of the wavefront integrator (see kernels.cuh).
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3
 #include "kernels.cuh"
+
+#include <mutex>
 #include "traverse.h"
 #include "flat.h"
 
@@ -1392,6 +1394,63 @@ void launch_primary_ids(cudaStream_t st, const SceneView& scene, const CameraVie
 void launch_trace_rays(cudaStream_t st, const SceneView& scene, const float* rays, size_t n, float t_min, int32_t* prim, float* t) {
     if (!n) return;
     k_trace_rays<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, rays, n, t_min, prim, t);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free closest-hit query (ptx_trace_rays_noalloc; no counterpart in the reference -- added
+// for callers that must not call cudaMalloc: code under CUDA graph capture, tight serving loops).
+// ptx_trace_rays stages rays / ids / distances in device buffers it cudaMallocs per call; this variant runs the same
+// k_trace_rays kernel on a file-scope device array instead.  Every GPU that loads the library holds the array (2 MB) until
+// exit.  All calls share it: calls that overlap on the GPU (two contexts of one device, two host threads) RACE on it.
+// Nothing in it has to start at zero: a call writes rays [0, n) before the kernel reads them and the kernel writes ids / t
+// [0, n) before they are copied out, so the previous call's contents beyond n are never read.
+// g_noalloc_scratch is a HOST-SIDE STAND-IN in host code, not a device address: the address the kernel gets comes from
+// cudaGetSymbolAddress, resolved once per device with that device current.
+// ---------------------------------------------------------------------------------------------
+constexpr size_t kNoAllocBytesPerRay = 6 * sizeof(float) + sizeof(int32_t) + sizeof(float);      // ray + prim id + t
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocMaxRays * kNoAllocBytesPerRay];
+
+namespace {
+constexpr int kNoAllocMaxDevices = 64;
+void* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+std::mutex g_noalloc_mutex;
+}  // namespace
+
+cudaError_t noalloc_scratch_address(int device, void** out) {
+    *out = nullptr;
+    if (device < 0 || device >= kNoAllocMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {
+        int cur = -1;
+        cudaError_t e = cudaGetDevice(&cur);
+        if (e != cudaSuccess) return e;
+        if (cur != device) return cudaErrorInvalidDevice;          // the caller makes the device current first (api.cu does)
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        g_noalloc_ptr[device] = p;
+    }
+    *out = g_noalloc_ptr[device];
+    return cudaSuccess;
+}
+
+cudaError_t trace_rays_noalloc(cudaStream_t st, int device, const SceneView& scene, const float* rays_host, size_t n, float t_min,
+                               int32_t* prim_host, float* t_host) {
+    if (n > kNoAllocMaxRays) return cudaErrorInvalidValue;
+    void* base = nullptr;
+    cudaError_t e = noalloc_scratch_address(device, &base);
+    if (e != cudaSuccess) return e;
+    float* d_rays = reinterpret_cast<float*>(base);                                                   // [kNoAllocMaxRays][6]
+    int32_t* d_ids = reinterpret_cast<int32_t*>(static_cast<unsigned char*>(base) + kNoAllocMaxRays * 6 * sizeof(float));
+    float* d_t = reinterpret_cast<float*>(static_cast<unsigned char*>(base) + kNoAllocMaxRays * 7 * sizeof(float));
+    e = cudaMemcpyAsync(d_rays, rays_host, n * 6 * sizeof(float), cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return e;
+    k_trace_rays<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, d_rays, n, t_min, d_ids, d_t);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(prim_host, d_ids, n * sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(t_host, d_t, n * sizeof(float), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    return e;
 }
 
 void launch_occluded(cudaStream_t st, const SceneView& scene, const float* segs, size_t n, uint8_t* out) {

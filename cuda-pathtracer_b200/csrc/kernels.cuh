@@ -91,6 +91,11 @@ void launch_resolve(cudaStream_t st, const FilmView& film, float inv_spp, uint8_
 void launch_film_scale(cudaStream_t st, const FilmView& film, float inv_spp, float* linear_rgb);
 void launch_primary_ids(cudaStream_t st, const SceneView& scene, const CameraView& cam, int w, int h, int32_t* prim, float* t);
 void launch_trace_rays(cudaStream_t st, const SceneView& scene, const float* rays, size_t n, float t_min, int32_t* prim, float* t);
+// allocation-free variant of the closest-hit query: staging in a file-scope device array of kernels.cu (see there); copies the
+// rays in, runs k_trace_rays, copies ids / distances out, synchronises the stream.  `device` must be the current device.
+constexpr size_t kNoAllocMaxRays = 65536;
+cudaError_t trace_rays_noalloc(cudaStream_t st, int device, const SceneView& scene, const float* rays_host, size_t n, float t_min,
+                               int32_t* prim_host, float* t_host);
 void launch_occluded(cudaStream_t st, const SceneView& scene, const float* segs, size_t n, uint8_t* out);
 void launch_visibility(cudaStream_t st, const SceneView& scene, const FilmView& film, const CameraView& cam, int spp, const float* radiosity,
                        uint8_t* rgb8);

@@ -231,6 +231,15 @@ int ptx_trace_primary_ids(ptx_ctx* ctx, const ptx_scene* scene, const ptx_camera
 /* closest hit for n host rays (6 floats: o, d; d normalised like the Ray ctor, core/ray.h:9-12) */
 int ptx_trace_rays(ptx_ctx* ctx, const ptx_scene* scene, const float* rays_host, size_t n, float t_min,
                    int32_t* prim_id_host, float* t_host);
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs and results as
+ * ptx_trace_rays, but the call allocates nothing: the device staging for rays / ids / distances is a file-scope device array
+ * of the library (2 MB, held by every GPU that loads the library until exit), so n is limited to PTX_NOALLOC_MAX_RAYS per call
+ * (more is rejected with PTX_ERR_INVALID).  All calls share that array: it keeps the last call's contents (never read beyond
+ * the current n), and calls that overlap on the GPU -- two contexts on one device, two host threads -- race on it. */
+#define PTX_NOALLOC_MAX_RAYS 65536
+int ptx_trace_rays_noalloc(ptx_ctx* ctx, const ptx_scene* scene, const float* rays_host, size_t n, float t_min,
+                           int32_t* prim_id_host, float* t_host);
 /* any-hit shadow query: Scene::occluded(from, to) (scene.h:132-190) for n segments of 6 floats (from.xyz, to.xyz);
  * occluded_host[i] = 1 if something lies strictly between the two points (1e-4 off both ends, as the reference) */
 int ptx_trace_occluded(ptx_ctx* ctx, const ptx_scene* scene, const float* segs_host, size_t n, uint8_t* occluded_host);
