@@ -57,6 +57,7 @@ struct ptx_scene {
     SceneView view{};
     ptx_scene_stats stats{};
     float* d_guide = nullptr;                    // grid-guided sampling: kGuideFloats floats per primitive (shade.h)
+    uint32_t* d_quad_bits = nullptr;             // one bit per primitive: Quad (any-hit end-point rule, traverse.h trace_any)
     FlatHost flat;                               // tiny scenes: the planar-unit list of flat.h (empty when the scene does not qualify)
     f32x4* d_flat_recs = nullptr;
 };
@@ -114,17 +115,22 @@ int ptx_ctx_create(int device, ptx_ctx** out) {
     if (device < 0 || device >= n) return fail(nullptr, PTX_ERR_INVALID, "ptx_ctx_create: bad device index");
     ptx_ctx* c = new ptx_ctx();
     c->device = device;
-    PTX_CUDA(c, cudaSetDevice(device));
-    PTX_CUDA(c, cudaGetDeviceProperties(&c->prop, device));
-    PTX_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    PTX_CUDA(c, cudaEventCreate(&c->ev0));
-    PTX_CUDA(c, cudaEventCreate(&c->ev1));
-    PTX_CUDA(c, cudaMallocHost(&c->h_counters, sizeof(unsigned long long) * CTR_COUNT));
-    PTX_CUDA(c, cudaMalloc(&c->ws.counters, sizeof(unsigned long long) * CTR_COUNT));
     std::vector<uint32_t> jump((size_t)kXorwowJumps * kXorwowJumpWords);
     xorwow_build_jump_tables(jump.data());
-    PTX_CUDA(c, cudaMalloc(&c->d_jump, jump.size() * sizeof(uint32_t)));
-    PTX_CUDA(c, cudaMemcpy(c->d_jump, jump.data(), jump.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    cudaError_t ce = cudaSetDevice(device);
+    if (ce == cudaSuccess) ce = cudaGetDeviceProperties(&c->prop, device);
+    if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (ce == cudaSuccess) ce = cudaEventCreate(&c->ev0);
+    if (ce == cudaSuccess) ce = cudaEventCreate(&c->ev1);
+    if (ce == cudaSuccess) ce = cudaMallocHost(&c->h_counters, sizeof(unsigned long long) * CTR_COUNT);
+    if (ce == cudaSuccess) ce = cudaMalloc(&c->ws.counters, sizeof(unsigned long long) * CTR_COUNT);
+    if (ce == cudaSuccess) ce = cudaMalloc(&c->d_jump, jump.size() * sizeof(uint32_t));
+    if (ce == cudaSuccess) ce = cudaMemcpy(c->d_jump, jump.data(), jump.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    if (ce != cudaSuccess) {                     // nothing half-built survives a failed creation
+        int rc = cuda_fail(nullptr, ce, "ptx_ctx_create");
+        ptx_ctx_destroy(c);
+        return rc;
+    }
     *out = c;
     return PTX_OK;
 }
@@ -307,13 +313,19 @@ int build_accel(ptx_scene* s, const ptx_build_opts* bo, const TriIn* d_tris_in =
 }
 
 int finish_scene(ptx_ctx* c, ptx_scene* s, const ptx_build_opts* bo, ptx_scene** out, const TriIn* d_tris_in = nullptr) {
-    PTX_CUDA(c, cudaSetDevice(c->device));
+    // takes ownership of s: on any failure the scene (and whatever device memory it already holds) is destroyed
     size_t np = s->packed.prim_shade.size(), nm = s->packed.materials.size();
-    PTX_CUDA(c, cudaMalloc(&s->d_prim_shade, std::max<size_t>(np, 1) * sizeof(f32x4)));
-    PTX_CUDA(c, cudaMalloc(&s->d_materials, std::max<size_t>(nm, 2) * sizeof(f32x4)));
-    if (np) PTX_CUDA(c, cudaMemcpy(s->d_prim_shade, s->packed.prim_shade.data(), np * sizeof(f32x4), cudaMemcpyHostToDevice));
-    if (nm) PTX_CUDA(c, cudaMemcpy(s->d_materials, s->packed.materials.data(), nm * sizeof(f32x4), cudaMemcpyHostToDevice));
-    s->view.prim_shade = s->d_prim_shade; s->view.materials = s->d_materials;
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_prim_shade, std::max<size_t>(np, 1) * sizeof(f32x4));
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_materials, std::max<size_t>(nm, 2) * sizeof(f32x4));
+    if (e == cudaSuccess && np) e = cudaMemcpy(s->d_prim_shade, s->packed.prim_shade.data(), np * sizeof(f32x4), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && nm) e = cudaMemcpy(s->d_materials, s->packed.materials.data(), nm * sizeof(f32x4), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && !s->packed.quad_bits.empty()) {
+        e = cudaMalloc(&s->d_quad_bits, s->packed.quad_bits.size() * sizeof(uint32_t));
+        if (e == cudaSuccess) e = cudaMemcpy(s->d_quad_bits, s->packed.quad_bits.data(), s->packed.quad_bits.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    }
+    if (e != cudaSuccess) { ptx_scene_destroy(s); return cuda_fail(c, e, "scene upload"); }
+    s->view.prim_shade = s->d_prim_shade; s->view.materials = s->d_materials; s->view.quad_bits = s->d_quad_bits;
     s->view.n_prims = (uint32_t)np; s->view.n_mats = (uint32_t)(nm / 2);
     s->stats.n_primitives = (int64_t)np; s->stats.n_materials = (int64_t)(nm / 2);
     s->stats.shading_bytes = (int64_t)((np + nm) * sizeof(f32x4));
@@ -345,6 +357,7 @@ int scene_from_base_gpu(ptx_ctx* c, const std::vector<ptx_primitive>& base, bool
         if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
         if (e != cudaSuccess) { g.release(); delete s; return cuda_fail(c, e, "scene_from_base_gpu"); }
     }
+    make_quad_bits(s->prims.data(), s->prims.size(), s->packed.quad_bits);
     s->stats.preprocess_ms = g.ms; s->stats.preprocess_on_device = 1;
     int rc = finish_scene(c, s, nullptr, out, g.d_tris);
     g.release();
@@ -442,7 +455,7 @@ void ptx_scene_destroy(ptx_scene* s) {
     cudaSetDevice(s->ctx->device);
     cudaStreamSynchronize(s->ctx->stream);
     free_accel(s);
-    cudaFree(s->d_prim_shade); cudaFree(s->d_materials); cudaFree(s->d_guide);
+    cudaFree(s->d_prim_shade); cudaFree(s->d_materials); cudaFree(s->d_guide); cudaFree(s->d_quad_bits);
     delete s;
 }
 
@@ -799,10 +812,18 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
             float scale = scene->flat.scale;                               // rays start at the camera or on the scene
             for (int k = 0; k < 3; k++) scale = std::max(scale, std::fabs(cam->origin[k]));
             flat_margins(scale, fs.m0, fs.m1);
+            fs.key_mask = kFlatKeyMask;
             int per_sm = opts->reserved[2] & 15;
-            // sequential RNG and fewer than ~3 pixels per resident lane: the frame is bounded by its longest pixel chain, and
-            // fewer warps per SM advance every chain faster (launch_path_persist has the same rule)
-            if (per_sm == 0 && rng_mode == 0 && (unsigned long long)rp.n_owned < 3ull * (unsigned long long)c->prop.multiProcessorCount * 768ull) per_sm = 2;
+            if (per_sm == 0) {
+                // Resident CTAs per SM (256 threads each).  Bulk throughput is best with 4 (64 registers; C2 28.6 against 27.0 G
+                // with 3).  With the sequential RNG a frame cannot end before its longest pixel chain, and a chain advances
+                // faster the fewer warps share its SM: when a rank owns few pixels per resident lane AND the chains are long
+                // (spp >= 512: a tile-sharded 1080p frame on 8 GPUs) 2 CTAs finish sooner; short chains (C1: 64 spp, 2.3
+                // pixels per lane) are throughput-bound again and want 3 (23.5 against 19.7 G with 2, 20.5 with 4).
+                const double px_per_lane = (double)rp.n_owned / ((double)c->prop.multiProcessorCount * 768.0);
+                if (rng_mode == 0 && px_per_lane < 3.0) per_sm = rp.spp >= 512 ? 2 : 3;
+                else per_sm = px_per_lane >= 8.0 ? 4 : 3;
+            }
             launch_path_flat(c->stream, rng_mode, c->ws, scene->view, fs, fv, cv, rp, c->prop.multiProcessorCount, per_sm);
         } else if (cta_wave) launch_path_cta(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->reserved[2]);
         else launch_path_persist(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->reserved[2]);
@@ -924,6 +945,7 @@ int ptx_render_stats_get(const ptx_ctx* c, ptx_render_stats* out) {
 int ptx_trace_primary_ids(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, int width, int height, int32_t* prim_id_host,
                           float* t_host) {
     if (!c || !scene || !cam || width <= 0 || height <= 0 || !prim_id_host || !t_host) return fail(c, PTX_ERR_INVALID, "ptx_trace_primary_ids: bad argument");
+    if (!scene->view.nodes) return fail(c, PTX_ERR_INVALID, "ptx_trace_primary_ids: the scene has no acceleration structure (a rebuild failed)");
     PTX_CUDA(c, cudaSetDevice(c->device));
     size_t n = (size_t)width * height;
     int32_t* d_ids = nullptr; float* d_t = nullptr;
@@ -942,6 +964,7 @@ int ptx_trace_primary_ids(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* 
 
 int ptx_trace_rays(ptx_ctx* c, const ptx_scene* scene, const float* rays_host, size_t n, float t_min, int32_t* prim_id_host, float* t_host) {
     if (!c || !scene || (n && (!rays_host || !prim_id_host || !t_host))) return fail(c, PTX_ERR_INVALID, "ptx_trace_rays: bad argument");
+    if (!scene->view.nodes) return fail(c, PTX_ERR_INVALID, "ptx_trace_rays: the scene has no acceleration structure (a rebuild failed)");
     if (!n) return PTX_OK;
     PTX_CUDA(c, cudaSetDevice(c->device));
     float* d_rays = nullptr; int32_t* d_ids = nullptr; float* d_t = nullptr;
@@ -985,6 +1008,7 @@ int ptx_ctx_flush_l2(ptx_ctx* c) {
 
 int ptx_trace_occluded(ptx_ctx* c, const ptx_scene* scene, const float* segs_host, size_t n, uint8_t* occluded_host) {
     if (!c || !scene || (n && (!segs_host || !occluded_host))) return fail(c, PTX_ERR_INVALID, "ptx_trace_occluded: bad argument");
+    if (!scene->view.nodes) return fail(c, PTX_ERR_INVALID, "ptx_trace_occluded: the scene has no acceleration structure (a rebuild failed)");
     if (!n) return PTX_OK;
     PTX_CUDA(c, cudaSetDevice(c->device));
     float* d_segs = nullptr; uint8_t* d_out = nullptr;
@@ -1003,6 +1027,7 @@ int ptx_render_visibility(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* 
                           uint8_t* rgb8_host) {
     if (!c || !scene || !cam || !film || !rgb8_host || spp <= 0) return fail(c, PTX_ERR_INVALID, "ptx_render_visibility: bad argument");
     if (scene->ctx != c || film->ctx != c) return fail(c, PTX_ERR_INVALID, "ptx_render_visibility: scene/film belong to another context");
+    if (!scene->view.nodes) return fail(c, PTX_ERR_INVALID, "ptx_render_visibility: the scene has no acceleration structure (a rebuild failed)");
     PTX_CUDA(c, cudaSetDevice(c->device));
     const size_t npix = (size_t)film->w * film->h, nprim = scene->view.n_prims;
     float* d_rad = nullptr; uint8_t* d_img = nullptr;

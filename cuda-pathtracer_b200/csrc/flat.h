@@ -53,7 +53,7 @@ struct FlatScene {
     const f32x4* recs;                 // kFlatRecQuads float4 per unit: { v0, prim }, { e1 }, { e2 } twice
     uint32_t n_units;
     float m0, m1;                      // margins, see flat_margins()
-    uint32_t pad;
+    uint32_t key_mask;                 // 0xFFFFFFE0: clears the 5 key bits that carry the unit index (a register operand of LOP3)
 };
 
 // unit k of the list; slots never set stay all-zero: n = 0 -> 1 / 0 = inf -> NaN / inf everywhere, so the loop bound
@@ -75,6 +75,7 @@ inline void flat_set_unit(FlatScene& fs, int k, const FlatUnit& u) {
 //   storage rounding of the unit constants (host double -> float) and of the in-plane projections:         < 1e-6 * scale
 // m0 = 1e-5 * scale and m1 = 1e-5 * scale leave a factor > 2 on top of their sum.
 inline void flat_margins(float scale, float& m0, float& m1) { m0 = 1e-5f * scale; m1 = 1e-5f * scale; }
+constexpr uint32_t kFlatKeyMask = 0xFFFFFFE0u;
 
 // 1 / x for the filter: one MUFU.RCP, denormals flushed (a denormal n.d becomes 0 -> 1 / 0 = inf -> infinite margin -> candidate).
 // rcp.approx WITHOUT .ftz costs two range tests, two selects and two scalings around the MUFU.
@@ -158,12 +159,20 @@ PTX_HD float max_nn(float a, float b) {
 }
 
 // one unit's share of the selection: key = lower bound t - m with the unit index in its low 5 bits, so ONE min tracks both
-// the smallest bound and whose it is; t2 = second smallest key.  A NaN key (ray parallel to the plane: 0 * inf) drops out
-// of min_nn / max_nn by itself, and such a unit cannot be hit (intersect_tri rejects |det| < 1e-8).
-PTX_HD void flat_select(int k, float t, float nm, float e1, float e2, float hm1, float hm2, float t_min, float& tbest, float& t2) {
-    // negated comparisons: an infinite margin makes the unit a candidate
-    const bool cand = !(fabsf(e1) > hm1) && !(fabsf(e2) > hm2) && !(t - nm < t_min);
-    const float key = u2f((f2u(t + nm) & 0xFFFFFFE0u) | (uint32_t)k);
+// the smallest bound and whose it is; t2 = second smallest key.
+PTX_HD void flat_select(int k, float tpm, float tmm, float e1, float e2, float hm1, float hm2, float t_min, uint32_t key_mask, float& tbest,
+                        float& t2) {
+    // tpm = t + m, tmm = t - m.  A NaN (n.d = 0 after flushing: t = 0 * inf, or the all-zero unit that pads an odd list) makes
+    // the unit a NON-candidate: it cannot be hit, intersect_tri rejects |det| = 2 area |n.d| < 1e-8.  A grazing but finite
+    // 1 / |n.d| just gives a large finite margin.
+    const bool cand = (fabsf(e1) <= hm1) && (fabsf(e2) <= hm2) && (tpm >= t_min);
+#if defined(__CUDA_ARCH__)
+    uint32_t kb;      // (bits & mask) | k as ONE LOP3: the mask sits in a register (it comes from the parameter block), k is the immediate
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(kb) : "r"(f2u(tmm)), "r"(key_mask), "r"((uint32_t)k));
+    const float key = u2f(kb);
+#else
+    const float key = u2f((f2u(tmm) & key_mask) | (uint32_t)k);
+#endif
     if (cand) {
         t2 = min_nn(t2, max_nn(tbest, key));
         tbest = min_nn(tbest, key);
@@ -178,22 +187,24 @@ PTX_HD void flat_closest(const FlatScene& fs, vec3 o, vec3 d, float t_min, float
     const uint32_t n = fs.n_units;
     const f2 ox = mk2(o.x, o.x), oy = mk2(o.y, o.y), oz = mk2(o.z, o.z);
     const f2 dx = mk2(d.x, d.x), dy = mk2(d.y, d.y), dz = mk2(d.z, d.z);
-    const float nm1 = -fs.m1, nm0 = -fs.m0;
+    const uint32_t key_mask = fs.key_mask;                            // 0xFFFFFFE0
+    const f2 m1 = mk2(fs.m1, fs.m1), m0 = mk2(fs.m0, fs.m0), minus1 = mk2(-1.0f, -1.0f);
 #pragma unroll
     for (int j = 0; j < kFlatUnits / 2; j++) {
-        if ((uint32_t)(2 * j) < n) {                                  // uniform
+        if ((uint32_t)(2 * j) < n) {                                  // uniform; an odd list ends with an all-zero unit (NaN key: dropped)
             const FlatPair& u = fs.p[j];
             const f2 den = fma2(ld2(u.nz), dz, fma2(ld2(u.ny), dy, mul2(ld2(u.nx), dx)));
             const f2 numn = fma2(ld2(u.nz), oz, fma2(ld2(u.ny), oy, fma2(ld2(u.nx), ox, ld2(u.mc))));     // n.o - c
             const f2 rn = mk2(rcp_ftz(-den.x), rcp_ftz(-den.y));
             const f2 t = mul2(numn, rn);
-            const f2 nm = mk2(fmaf(fabsf(rn.x), nm1, nm0), fmaf(fabsf(rn.y), nm1, nm0));                   // -(m0 + m1 / |n.d|)
+            const f2 m = fma2(mk2(fabsf(rn.x), fabsf(rn.y)), m1, m0);                                      // m0 + m1 / |n.d|
             const f2 px = add2(fma2(t, dx, ox), ld2(u.ncx)), py = add2(fma2(t, dy, oy), ld2(u.ncy)), pz = add2(fma2(t, dz, oz), ld2(u.ncz));
             const f2 e1 = fma2(ld2(u.a1z), pz, fma2(ld2(u.a1y), py, mul2(ld2(u.a1x), px)));
             const f2 e2 = fma2(ld2(u.a2z), pz, fma2(ld2(u.a2y), py, mul2(ld2(u.a2x), px)));
-            const f2 hm1 = mk2(u.h1[0] - nm.x, u.h1[1] - nm.y), hm2 = mk2(u.h2[0] - nm.x, u.h2[1] - nm.y);
-            flat_select(2 * j, t.x, nm.x, e1.x, e2.x, hm1.x, hm2.x, t_min, tbest, t2);
-            if ((uint32_t)(2 * j + 1) < n) flat_select(2 * j + 1, t.y, nm.y, e1.y, e2.y, hm1.y, hm2.y, t_min, tbest, t2);
+            const f2 hm1 = add2(ld2(u.h1), m), hm2 = add2(ld2(u.h2), m);
+            const f2 tpm = add2(t, m), tmm = fma2(m, minus1, t);
+            flat_select(2 * j, tpm.x, tmm.x, e1.x, e2.x, hm1.x, hm2.x, t_min, key_mask, tbest, t2);
+            flat_select(2 * j + 1, tpm.y, tmm.y, e1.y, e2.y, hm1.y, hm2.y, t_min, key_mask, tbest, t2);
         }
     }
     closest = FLT_MAX; bestw = kMiss;

@@ -48,6 +48,8 @@ struct SceneView {
     // grid-guided sampling (shade.h): kGuideFloats floats per reference primitive, or nullptr; Scene::mis_bsdf_fraction
     const float* guide = nullptr;
     float mis_bsdf_fraction = 0.5f;
+    // one bit per reference primitive: 1 = Quad (its halves reject t == t_max in the any-hit query, trace_any); nullptr = no quads
+    const uint32_t* quad_bits = nullptr;
 };
 
 // Camera in the reference's Sensor terms (rendering/sensor.h:92-95): what get_ray needs.

@@ -152,6 +152,8 @@ struct Lexer {
 struct Param {
     std::string type, name;
     std::vector<float> nums;
+    std::vector<long long> ints;       // "integer" parameters, parsed as integers: float32 is exact only up to 2^24, and a mesh with
+                                       // more than 16.7 M vertices would otherwise get its indices silently rounded
     std::vector<std::string> strs;
 };
 
@@ -188,6 +190,7 @@ struct Parser {
         return false;
     }
     bool open(const std::string& path) {
+        if (lexers.size() >= 32) return fail("Include nested deeper than 32 levels (a file that includes itself?): " + path);
         std::unique_ptr<Lexer> lx(new Lexer());
         if (!lx->load(path)) return fail("cannot open " + path);
         lexers.push_back(std::move(lx));
@@ -216,7 +219,12 @@ struct Parser {
             size_t ns = t.text.find_first_not_of(" \t", sp);
             p.name = ns == std::string::npos ? "" : t.text.substr(ns);
             Token v = next();
-            auto take = [&](const Token& x) { if (x.kind == Token::Number) p.nums.push_back(to_float(x.text)); else p.strs.push_back(x.text); };
+            const bool integer = p.type == "integer";
+            auto take = [&](const Token& x) {
+                if (x.kind != Token::Number) p.strs.push_back(x.text);
+                else if (integer) p.ints.push_back(strtoll(x.text.c_str(), nullptr, 10));
+                else p.nums.push_back(to_float(x.text));
+            };
             if (v.kind == Token::LBracket) {
                 for (;;) {
                     Token x = next();
@@ -298,12 +306,14 @@ struct Parser {
             for (size_t i = 0; i < m.N.size(); i++) m.N[i] = xfm_normal(gs.ctm, mk3(N->nums[3 * i], N->nums[3 * i + 1], N->nums[3 * i + 2]));
         }
         if (I) {
-            size_t nt = I->nums.size() / 3;
+            // "integer indices" arrive in I->ints; a file that declares them as "float indices" still works up to 2^24
+            const bool as_int = I->type == "integer";
+            size_t nt = (as_int ? I->ints.size() : I->nums.size()) / 3;
             m.idx.resize(nt * 3);
             for (size_t i = 0; i < nt * 3; i++) {
-                int v = (int)I->nums[i];
-                if (v < 0 || (size_t)v >= nv) return fail("trianglemesh index out of range");
-                m.idx[i] = v;
+                long long v = as_int ? I->ints[i] : (long long)I->nums[i];
+                if (v < 0 || (unsigned long long)v >= nv) return fail("trianglemesh index out of range");
+                m.idx[i] = (int)v;
             }
         }
         current_object().meshes.push_back(std::move(m));

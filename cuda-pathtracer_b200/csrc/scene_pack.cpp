@@ -16,8 +16,19 @@ struct MatKey {
 };
 }  // namespace
 
+void make_quad_bits(const ptx_primitive* prims, size_t n, std::vector<uint32_t>& out) {
+    out.clear();
+    bool any = false;
+    for (size_t i = 0; i < n && !any; i++) any = prims[i].type == 1;
+    if (!any) return;
+    out.assign((n + 31) / 32, 0u);
+    for (size_t i = 0; i < n; i++)
+        if (prims[i].type == 1) out[i >> 5] |= 1u << (i & 31);
+}
+
 void pack_primitives(const ptx_primitive* prims, size_t n, PackedScene& out) {
     out.tris.clear(); out.prim_shade.clear(); out.materials.clear();
+    make_quad_bits(prims, n, out.quad_bits);
     out.tris.reserve(n); out.prim_shade.reserve(n);
     std::map<MatKey, uint32_t> table;
     for (size_t i = 0; i < n; i++) {
@@ -45,7 +56,7 @@ void pack_primitives(const ptx_primitive* prims, size_t n, PackedScene& out) {
 
 void pack_triangles(const float* v, const float* normals, const uint32_t* mat_id, const ptx_material* mats, size_t n_tri,
                     size_t n_mat, PackedScene& out) {
-    out.tris.resize(n_tri); out.prim_shade.resize(n_tri); out.materials.clear();
+    out.tris.resize(n_tri); out.prim_shade.resize(n_tri); out.materials.clear(); out.quad_bits.clear();
     for (size_t m = 0; m < n_mat; m++) {
         out.materials.push_back(f32x4{mats[m].bsdf[0], mats[m].bsdf[1], mats[m].bsdf[2], u2f((uint32_t)mats[m].type)});
         out.materials.push_back(f32x4{mats[m].Le[0], mats[m].Le[1], mats[m].Le[2], 0.f});
@@ -60,7 +71,7 @@ void pack_triangles(const float* v, const float* normals, const uint32_t* mat_id
         t.prim_id = (uint32_t)i;
         vec3 nn = normals ? ld3(normals + 3 * i) : unit(cross(ld3(t.v1) - ld3(t.v0), ld3(t.v2) - ld3(t.v0)));
         uint32_t mid = mat_id ? mat_id[i] : 0u;
-        if (n_mat && mid >= n_mat) mid = 0;
+        if (mid >= (n_mat ? n_mat : (size_t)1)) mid = 0;      // n_mat == 0: only the default material exists
         out.prim_shade[i] = f32x4{nn.x, nn.y, nn.z, u2f(mid)};
     }
 }

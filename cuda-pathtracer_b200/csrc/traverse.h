@@ -305,18 +305,34 @@ PTX_HD uint32_t trace_closest(const SceneView& s, vec3 o, vec3 d, float t_min, f
     return tr.best;
 }
 
-// Any hit along (o, d) in [t_min, t_max): the traversal stops at the first accepted triangle (Scene::occluded_bvh,
-// scene.h:152-190).  The answer does not depend on the visiting order.  (Reference detail not reproduced: its
-// Triangle::intersect accepts t == t_max, triangle.h:84, its Quad halves do not; here every record uses t < t_max.)
+// Any hit along (o, d) in [t_min, t_max]: the traversal stops at the first accepted record (Scene::occluded_bvh, scene.h:152-190).
+// The answer does not depend on the visiting order.  End-point rule of the reference: Triangle::intersect accepts
+// t_min <= t <= t_max (triangle.h:83), the two halves of a Quad only t < t_max (quad.h:76, 106: `t < closest_t` with
+// closest_t = t_max).  So the records are tested against the next float above t_max, and a hit at exactly t_max counts
+// unless its primitive is a quad (s.quad_bits: one bit per reference primitive, read only in that rare case).
 template <int STACK>
 PTX_HD bool trace_any(const SceneView& s, vec3 o, vec3 d, float t_min, float t_max) {
+    if (!(t_max >= t_min) || !(t_max > 0.0f)) return false;
+    const float bound = u2f(f2u(t_max) + 1u);          // t < bound  <=>  t <= t_max   (t_max > 0, finite)
     Traversal tr;
     TravStack<STACK> stk;
-    tr.begin(d, t_max);
+    tr.begin(d, bound);
     for (;;) {
-        bool done = tr.template step<false, STACK>(s, stk, o, d, t_min, nullptr);
-        if (tr.best != kMiss) return true;
-        if (done) return false;
+        uint32_t tg_x, tg_y;
+        tr.template visit<false>(s, stk, o, d, t_min, tg_x, tg_y, nullptr);
+        while (tg_y != 0) {
+            uint32_t bit = hi_bit(tg_y);
+            tg_y &= ~(1u << bit);
+            const f32x4* tp = s.tris + (size_t)(tg_x + bit) * kTriQuads;
+            f32x4 a = ldq(tp + 0), b = ldq(tp + 1), c = ldq(tp + 2);
+            float t = bound;
+            if (intersect_tri(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), o, d, t_min, t)) {
+                if (t < t_max) return true;
+                const uint32_t prim = f2u(a.w);
+                if (!(s.quad_bits != nullptr && ((s.quad_bits[prim >> 5] >> (prim & 31u)) & 1u))) return true;
+            }
+        }
+        if (tr.next_group(stk)) return false;
     }
 }
 

@@ -39,6 +39,7 @@ static void finish(EmuScene* s, int max_leaf) {
     s->view.n_tris = (uint32_t)s->bvh.tri_src.size();
     s->view.n_prims = (uint32_t)s->packed.prim_shade.size();
     s->view.n_mats = (uint32_t)(s->packed.materials.size() / 2);
+    s->view.quad_bits = s->packed.quad_bits.empty() ? nullptr : s->packed.quad_bits.data();
     memset(&s->fs, 0, sizeof s->fs);
     if (build_flat_units(s->packed.tris.data(), s->packed.tris.size(), s->flat)) {
         for (size_t k = 0; k < s->flat.units.size(); k++) flat_set_unit(s->fs, (int)k, s->flat.units[k]);
@@ -109,6 +110,7 @@ int emu_flat_units(const EmuScene* s, float* units_out /* 16 floats per unit, ma
 void emu_trace_flat(const EmuScene* s, const float* rays, int64_t n, float t_min, float scale, int32_t* prim, float* t, uint64_t* ctr3) {
     FlatScene fs = s->fs;
     flat_margins(scale > 0.f ? scale : s->flat.scale, fs.m0, fs.m1);
+    fs.key_mask = kFlatKeyMask;
     FlatCounters c = {0, 0, 0};
     for (int64_t i = 0; i < n; i++) {
         vec3 o = ld3(rays + 6 * i), d = unit(ld3(rays + 6 * i + 3));
@@ -118,6 +120,19 @@ void emu_trace_flat(const EmuScene* s, const float* rays, int64_t n, float t_min
         t[i] = w == kMiss ? -1.0f : th;
     }
     if (ctr3) { ctr3[0] = c.rays; ctr3[1] = c.slow; ctr3[2] = c.unit_tests; }
+}
+
+// Scene::occluded(from, to) through trace_any (the arithmetic of k_occluded, kernels.cu)
+void emu_occluded(const EmuScene* s, const float* segs, int64_t n, uint8_t* out) {
+    for (int64_t i = 0; i < n; i++) {
+        vec3 from = ld3(segs + 6 * i);
+        vec3 dir = ld3(segs + 6 * i + 3) - from;
+        float dist = length(dir);
+        dir = div_scalar(dir, dist);
+        vec3 o = from + 1e-4f * dir;
+        vec3 d = unit(dir);
+        out[i] = trace_any<32>(s->view, o, d, 1e-4f, dist - 1e-4f) ? 1 : 0;
+    }
 }
 
 void emu_jump_tables(uint32_t* out) { xorwow_build_jump_tables(out); }
@@ -158,6 +173,7 @@ static void emu_render_impl(const EmuScene* s, const CameraView* cam, int spp, i
         float scale = s->flat.scale;
         for (int k = 0; k < 3; k++) scale = fmaxf(scale, fabsf(cam->origin[k]));
         flat_margins(scale, fs.m0, fs.m1);
+        fs.key_mask = kFlatKeyMask;
     }
     FlatCounters fc = {0, 0, 0};
     std::vector<uint32_t> tables((size_t)kXorwowJumps * kXorwowJumpWords);

@@ -36,6 +36,7 @@ def emu(built):
     L.emu_parse_obj.restype = C.c_int64
     L.emu_parse_obj.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_int64]
     L.emu_xorwow_init.argtypes = [C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]
+    L.emu_occluded.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
     L.emu_flat_units.argtypes = [C.c_void_p, C.c_void_p]
     L.emu_trace_flat.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
     L.emu_render_flat.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -313,6 +314,28 @@ def test_negative_zero_direction(emu):
     emu.emu_scene_free(s)
 
 
+# ---- any-hit end-point rule (traverse.h trace_any) -------------------------------------------------
+@pytest.mark.parametrize("name,cq", [("cbox", 0), ("cbox_quads", 0), ("cbox_quads", 1)])
+def test_occluded_endpoint_rule_matches_reference(pkg, emu, oracle, name, cq):
+    """Segments ending within a few ulps of a surface (tests/golden/f4_boundary.npz, answers from the reference's own
+    Scene::occluded): a triangle accepts t == t_max, the halves of a quad do not (triangle.h:83, quad.h:76).  The oracle
+    restatement and the product's trace_any (compiled for the host) must both reproduce every answer."""
+    g = np.load(os.path.join(GOLDEN, "f4_boundary.npz"))
+    segs = np.ascontiguousarray(g["segs"]); want = g[f"{name}_cq{cq}_occ"]
+    assert np.array_equal(want, g[f"{name}_cq{cq}_occ_lin"])
+    assert (g["cbox_quads_cq0_occ"] != g["cbox_quads_cq1_occ"]).sum() > 100          # the vectors do contain t == t_max cases
+    path = os.path.join(SCENES, name + ".obj")
+    osc = oracle.load_obj(path, convert_quads=bool(cq))
+    sub = slice(0, len(segs), 5)
+    assert np.array_equal(oracle.occluded(osc, segs[sub], mode=0), want[sub])
+    oracle.free(osc)
+    s = emu.emu_scene_load(path.encode(), cq, 0, 3)
+    out = np.zeros(len(segs), np.uint8)
+    emu.emu_occluded(s, P(segs), len(segs), P(out))
+    assert np.array_equal(out, want), int((out != want).sum())
+    emu.emu_scene_free(s)
+
+
 # ---- integrator core (shade.h) --------------------------------------------------------------------
 @pytest.mark.parametrize("tag,w,h,spp,depth", [("cbox_cq0", 48, 48, 8, 8), ("cbox_quads_cq0", 64, 36, 4, 16), ("cbox_quads_cq1", 32, 32, 16, 5)])
 def test_integrator_core_bit_exact_vs_reference(pkg, emu, gold, tag, w, h, spp, depth):
@@ -358,6 +381,31 @@ def test_pbrt_loader_extension_and_errors(pkg, tmp_path):
         pkg.parse_scene_file(str(bad))
     with pytest.raises(pkg.PtxError):
         pkg.parse_scene_file(str(tmp_path / "missing.pbrt"))
+
+
+def test_pbrt_indices_above_2_pow_24(pkg, tmp_path):
+    """"integer indices" are parsed as integers: float32 is exact only up to 2^24, so a mesh with more than 16.7 M vertices
+    used to get its indices silently rounded (2^24 + 1 -> 2^24) and rendered the wrong geometry.  Also: Include cycles fail."""
+    nv = 2 ** 24 + 4
+    f = tmp_path / "big.pbrt"
+    with open(f, "w") as fh:
+        fh.write('WorldBegin\nShape "trianglemesh" "point P" [\n')
+        chunk = "0 0 0 " * 65536 + "\n"
+        for _ in range((nv - 4) // 65536):
+            fh.write(chunk)
+        fh.write("0 0 0 " * ((nv - 4) % 65536))
+        fh.write("1 1 5  2 1 5  2 2 5  1 2 5 ]\n")
+        fh.write(f'"integer indices" [ {nv - 4} {nv - 3} {nv - 2}  {nv - 4} {nv - 2} {nv - 1} ]\nWorldEnd\n')
+    prims = pkg.parse_scene_file(str(f))
+    assert len(prims) == 2
+    assert prims["v"][0, :3].tolist() == [[1, 1, 5], [2, 1, 5], [2, 2, 5]]
+    assert prims["v"][1, :3].tolist() == [[1, 1, 5], [2, 2, 5], [1, 2, 5]]
+    os.remove(f)
+    loop = tmp_path / "loop.pbrt"
+    loop.write_text('WorldBegin\nInclude "loop.pbrt"\nWorldEnd\n')
+    with pytest.raises(pkg.PtxError) as e:
+        pkg.parse_scene_file(str(loop))
+    assert "Include nested deeper" in str(e.value)
 
 
 def test_pbrt_triangle_cap_proxy(pkg):
