@@ -149,217 +149,289 @@ def run_reference(args, scene_path, w, h, spp, depth):
     emit(({
         "impl": "reference", "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload_desc, "sample": sample, "segments_per_path": seg_per_path},
+        "config": {"workload": args.workload_desc, "sample": sample, "segments_per_path": seg_per_path,
+                   "segments_per_path_source": "C oracle on a 1/8-scale frame at 4 spp (same streams as the reference), not counted on the timed frame"},
         "cpu_baseline": {"value": value, "unit": METRIC, "cores": threads, "kind": "reference", "sample": sample, "host_cores": cores},
         "e2e": {"value": value, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
 
-class DeviceArray:
-    """__cuda_array_interface__ view of a raw device pointer, so torch can wrap the film accumulator."""
+def build_scene(pkg, ctx, workload, rank, max_leaf=0):
+    """Scene + camera of a workload, replicated on this rank's GPU (one-time, outside every timed region)."""
+    scene_name, w, h, _, _ = WORKLOADS[workload]
+    cam = None
+    if scene_name.startswith("generated:"):
+        from cuda_pathtracer_b200 import scenegen
+        base = pkg.parse_scene_file(os.path.join(ROOT, "scenes", "cbox_quads.obj"))
+        if scene_name.endswith("c5"):
+            pbrt = os.path.join("/tmp", f"c5_rank{rank}.pbrt")
+            scenegen.write_c5_pbrt(pbrt)
+            scene = ctx.load_scene(pbrt, mirror_from_mtl=True)
+            side = 17; room = 4.0 * side                      # camera of the generated file (scenegen.write_c5_pbrt)
+            cam = pkg.look_at_camera((room / 2, room / 2, room * 1.9), (room / 2, room / 2, 0.0), (0.0, 1.0, 0.0), 40.0, w, h)
+        elif scene_name.endswith("c4"):
+            scene = ctx.scene_from_primitives(scenegen.c4_prims(base), builder=0, max_leaf=max_leaf)
+        else:
+            level = int(scene_name.rsplit("level", 1)[1])
+            tris, mat, mats = scenegen.c3_scene(base, level)
+            scene = ctx.scene_from_triangles(tris, mat, mats, builder=0, max_leaf=max_leaf)
+            del tris, mat
+    else:
+        scene = ctx.load_scene(os.path.join(ROOT, "scenes", scene_name))
+        if max_leaf:
+            scene.rebuild(builder=0, max_leaf=max_leaf)
+    return scene, (cam or pkg.default_camera(w, h))
 
-    def __init__(self, ptr, nfloats):
-        self.__cuda_array_interface__ = {"shape": (nfloats,), "typestr": "<f4", "data": (ptr, False), "version": 3, "strides": None}
+
+class Run:
+    """One workload on this rank: frames through the C ABI, sharded over `world` ranks, film combined by the LIBRARY
+    (ptx_film_combine: NCCL on the context's stream); torch.distributed only carries barriers and the metric reductions."""
+
+    def __init__(self, pkg, ctx, comm, dist, torch, rank, world, workload, spp, depth, rng, pipeline, args):
+        import numpy as np
+        self.np, self.pkg, self.ctx, self.comm, self.dist, self.torch, self.rank, self.world = np, pkg, ctx, comm, dist, torch, rank, world
+        self.workload, self.spp, self.depth = workload, spp, depth
+        _, self.w, self.h, _, _ = WORKLOADS[workload]
+        self.rng_mode = pkg.RNG_PHILOX if rng == "philox" else pkg.RNG_XORWOW_COMPAT
+        self.shard_mode = pkg.SHARD_NONE if world == 1 else (pkg.SHARD_SAMPLES if self.rng_mode == pkg.RNG_PHILOX else pkg.SHARD_TILES)
+        self.scene, self.cam = build_scene(pkg, ctx, workload, rank, args.max_leaf)
+        self.default_cam = not WORKLOADS[workload][0].endswith("c5")
+        self.film = ctx.create_film(self.w, self.h)
+        self.rgb_host = np.empty((self.h, self.w, 3), np.uint8)
+        self.kw = dict(spp=spp, max_depth=depth, rng_mode=self.rng_mode, pipeline=pipeline, shard_mode=self.shard_mode, shard_rank=rank, shard_world=world,
+                       loop_min_blocks=args.min_blocks, chunks=args.chunks, shade_batch=args.shade_batch)
+
+    def barrier(self):
+        self.ctx.sync()
+        if self.world > 1:
+            self.dist.barrier()
+            self.torch.cuda.synchronize()
+
+    def step(self, host_output, stage_timing=False):
+        """One frame.  host_output=False: the RGB8 result stays in HBM. True: it is copied to the host (renderFrame, application.h:211-212).
+        Nothing synchronises the host between render and combine (PTX_RENDER_ASYNC); the resolve at the end of the frame does."""
+        self.ctx.flush_l2()                           # 256 MB memset on the render stream: nothing of the last frame stays in L2
+        multi = self.world > 1
+        st = self.ctx.render(self.scene, self.cam, self.film, stage_timing=stage_timing, async_=multi and not stage_timing, **self.kw)
+        if multi:
+            self.film.combine(self.comm, self.shard_mode)
+        if host_output:
+            self.film.rgb8(out=self.rgb_host)
+        else:
+            self.film.resolve_device()
+        return st if st is not None else self.ctx.render_stats()
+
+    def measure(self, steps, warmup, e2e=True):
+        pkg = self.pkg
+        for _ in range(warmup):
+            self.step(False)
+        # ---- timed region A: inputs resident in HBM, device events on the launching stream
+        self.barrier()
+        self.ctx.timer_start()
+        seg = launches = 0
+        for _ in range(steps):
+            st = self.step(False)
+            seg += st["segments"]; launches += st["kernel_launches"] + 1 + (3 if self.shard_mode == pkg.SHARD_TILES else (1 if self.world > 1 else 0))
+        ms_dev = self.ctx.timer_stop()
+        self.barrier()
+        # ---- timed region B: end to end through the C ABI with host buffers
+        seg_e2e, ms_e2e = 0, 0.0
+        if e2e:
+            self.barrier()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                if self.default_cam:
+                    self.cam = pkg.default_camera(self.w, self.h)    # host camera update + by-value upload, like renderFrame (application.h:161-164)
+                st = self.step(True)
+                seg_e2e += st["segments"]
+            self.ctx.sync()
+            ms_e2e = (time.perf_counter() - t0) * 1e3
+            self.barrier()
+        out = dict(seg=seg, seg_e2e=seg_e2e, ms_dev=ms_dev, ms_e2e=ms_e2e, launches=launches)
+        if self.world > 1:
+            t = self.torch.tensor([float(seg), float(seg_e2e)], dtype=self.torch.float64, device="cuda")
+            self.dist.all_reduce(t)
+            m = self.torch.tensor([ms_dev, ms_e2e], dtype=self.torch.float64, device="cuda")
+            self.dist.all_reduce(m, op=self.dist.ReduceOp.MAX)
+            out.update(seg=t[0].item(), seg_e2e=t[1].item(), ms_dev=m[0].item(), ms_e2e=m[1].item())
+        out["value"] = out["seg"] / (out["ms_dev"] * 1e-3) * 1e-6
+        out["e2e_value"] = out["seg_e2e"] / (out["ms_e2e"] * 1e-3) * 1e-6 if e2e else None
+        out["ms_per_step"] = out["ms_dev"] / steps
+        return out
+
+    def check_against_unsharded(self):
+        """Multi-rank check, outside every timed region: every rank compares the combined film it holds with the same frame
+        rendered unsharded on its own GPU -- bit for bit with tiles + compat RNG, to 1e-5 with sample ranges + counter RNG."""
+        np, pkg = self.np, self.pkg
+        self.film.reset()
+        self.step(False)
+        combined = self.film.linear()
+        kw = dict(self.kw); kw.update(shard_mode=pkg.SHARD_NONE, shard_rank=0, shard_world=1)
+        self.film.reset()
+        self.ctx.render(self.scene, self.cam, self.film, **kw)
+        whole = self.film.linear()
+        self.film.reset()
+        differing = int((combined != whole).any(-1).sum())
+        rel = float(np.max(np.abs(combined.astype(np.float64) - whole) / np.maximum(np.abs(whole), 1e-3)))
+        ok = differing == 0 if self.shard_mode == pkg.SHARD_TILES else rel <= 1e-5
+        res = {"mode": {1: "tiles: bit-exact", 2: "sample ranges: <= 1e-5 relative"}[self.shard_mode], "pixels_differing": differing,
+               "max_rel_diff": rel, "ok": bool(ok), "rank": self.rank}
+        if self.world > 1:
+            flags = self.torch.tensor([0.0 if ok else 1.0], dtype=self.torch.float64, device="cuda")
+            self.dist.all_reduce(flags)
+            res["ranks_failing"] = int(flags[0].item())
+            res["ok"] = res["ranks_failing"] == 0
+        return res
+
+    def close(self):
+        self.film.close(); self.scene.close()
 
 
-def run_ours(args, scene_path, w, h, spp, depth):
+def roofline_of(run, m, st_t, args, clocks, sm_count):
+    """roofline object of the dominant kernel of `run` (k_path_flat / k_path_persist: one launch per frame = the whole render).
+    Large scenes (BVH8 + records > L2): HBM bound on node + triangle fetches, algorithmic bytes from the instrumented extend kernel.
+    Cache-resident scenes: HBM is not the bound (the kernel moves < 1 byte per segment); the binding resource is instruction
+    ISSUE: achieved = segments/s x warp-instructions per segment (from the committed ncu capture of this kernel, profiles/traffic.json),
+    peak = SMs x 4 schedulers x the SM clock sampled during this run.  The HBM figures stay as a side note."""
+    pkg, ctx = run.pkg, run.ctx
+    peak, peak_src = read_peaks()
+    scene_stats = run.scene.stats()
+    k_ms = st_t["shade_ms"]
+    is_flat = scene_stats.get("flat_units", 0) > 0 and args.pipeline in ("auto", "flat")
+    kname = ("k_path_flat<rng> (one launch per frame: flat unit-list extend + shade + regenerate, all state in registers)" if is_flat else
+             "k_path_persist<rng> (one launch per frame: BVH8 extend + shade + regenerate, all state in registers)")
+    n_px = run.w * run.h / run.world
+    n_chunks = compat_chunk_count(run.spp, args.chunks, n_px / (sm_count * 768.0))
+    # per owned pixel and sample chunk: pixel id 4 + RNG state 24 + 24 + pixel sum 16 + 16 + progress flag 4 + 4; counter RNG: pixel id 4 + three float atomics 12 per path
+    per_item = 92.0 * n_chunks * n_px if run.rng_mode == pkg.RNG_XORWOW_COMPAT else 16.0 * st_t["paths"]
+    bytes_per_seg = per_item / max(st_t["segments"], 1)
+    seg_per_s = st_t["segments"] / (k_ms * 1e-3) if k_ms > 0 else 0.0
+    tkey = f"{run.workload}/{'philox' if run.rng_mode == pkg.RNG_PHILOX else 'compat'}/{'flat' if is_flat else 'persist'}"
+    ent = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        ent = json.load(open(tpath)).get(tkey)
+    common = {"kernel": kname, "kernel_ms_per_step": k_ms, "kernel_share_of_step": k_ms / m["ms_per_step"] if m["ms_per_step"] else None,
+              "traffic": ent["bytes"] if ent and run.world == 1 and args.spp == 0 else None, "traffic_source": ent["source"] if ent else None}
+    if scene_stats["node_bytes"] + scene_stats["triangle_bytes"] > 126e6:
+        kwc = dict(run.kw); kwc.update(spp=2, pipeline=pkg.PIPELINE_WAVEFRONT, shard_mode=pkg.SHARD_NONE, shard_rank=0, shard_world=1)
+        st_c = ctx.render(run.scene, run.cam, run.film, count_work=True, **kwc)
+        n_node, n_tri = st_c["node_visits"] / max(st_c["segments"], 1), st_c["tri_tests"] / max(st_c["segments"], 1)
+        bps = n_node * 80 + n_tri * 48
+        achieved = seg_per_s * bps * 1e-9
+        return dict(common, bound="hbm", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak, peak_source=peak_src, bytes_per_segment=bps,
+                    traversal={"nodes_per_segment": n_node, "tris_per_segment": n_tri, "node_bytes": 80, "tri_bytes": 48})
+    hbm = {"achieved": seg_per_s * bytes_per_seg * 1e-9, "peak": peak, "unit": "GB/s", "frac": seg_per_s * bytes_per_seg * 1e-9 / peak, "peak_source": peak_src,
+           "bytes_per_segment": bytes_per_seg, "note": "algorithmic HBM bytes of a kernel that keeps all path state in registers: not the bound"}
+    issue = (ent or {}).get("issue")
+    if issue and clocks.get("sm_mhz"):
+        wips = issue["warp_instructions_per_segment"]
+        peak_issue = sm_count * 4 * clocks["sm_mhz"] * 1e6 * 1e-9            # G warp-instructions / s
+        ach = seg_per_s * wips * 1e-9
+        return dict(common, bound="issue", achieved=ach, peak=peak_issue, unit="G warp-instr/s", frac=ach / peak_issue,
+                    peak_source=f"{sm_count} SMs x 4 schedulers x {clocks['sm_mhz']:.0f} MHz (nvidia-smi, median during the timed region)",
+                    warp_instructions_per_segment=wips, lane_efficiency=issue.get("lane_efficiency"), issue_source=issue.get("source"), hbm=hbm)
+    return dict(common, bound="hbm", **hbm)
+
+
+def run_ours(args, w, h, spp, depth):
     import __graft_entry__ as ge
     pkg = ge.load_package()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    rng_mode = pkg.RNG_PHILOX if args.rng == "philox" else pkg.RNG_XORWOW_COMPAT
     pipeline = {"fused": pkg.PIPELINE_FUSED, "wavefront": pkg.PIPELINE_WAVEFRONT, "loop": pkg.PIPELINE_LOOP, "persist": pkg.PIPELINE_PERSIST, "cta": pkg.PIPELINE_CTA,
                 "flat": pkg.PIPELINE_FLAT, "auto": pkg.PIPELINE_DEFAULT}[args.pipeline]
-    shard_mode = pkg.SHARD_NONE if world == 1 else (pkg.SHARD_SAMPLES if rng_mode == pkg.RNG_PHILOX else pkg.SHARD_TILES)
-
-    dist = torch = None
+    dist = torch = comm = None
+    ctx = pkg.Context(local_rank)
     if world > 1:
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # the library's own communicator: rank 0 makes the id, torch.distributed only ships its 128 bytes
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid.copy_(torch.tensor(list(pkg.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, 0)
+        comm = ctx.create_comm(bytes(uid.cpu().tolist()), rank, world)
+    sm_count = ctx.device_info()["sm_count"]
+    generated = WORKLOADS[args.workload][0].startswith("generated:")
+    scene_path = os.path.join(ROOT, "scenes", WORKLOADS[args.workload][0])
 
-    ctx = pkg.Context(local_rank)
-    generated = os.path.basename(scene_path).startswith("generated:")
-    if generated:                                   # scene replicated on every GPU (one-time, outside the timed region)
-        from cuda_pathtracer_b200 import scenegen
-        base = pkg.parse_scene_file(os.path.join(ROOT, "scenes", "cbox_quads.obj"))
-        if scene_path.endswith("c5"):
-            pbrt = os.path.join("/tmp", f"c5_rank{rank}.pbrt")
-            scenegen.write_c5_pbrt(pbrt)
-            scene = ctx.load_scene(pbrt, mirror_from_mtl=True)
-            side = 17; room = 4.0 * side                      # camera of the generated file (scenegen.write_c5_pbrt)
-            c5_cam = ((room / 2, room / 2, room * 1.9), (room / 2, room / 2, 0.0), (0.0, 1.0, 0.0), 40.0)
-        elif scene_path.endswith("c4"):
-            scene = ctx.scene_from_primitives(scenegen.c4_prims(base), builder=0, max_leaf=args.max_leaf)
-        else:
-            level = int(scene_path.rsplit("level", 1)[1])
-            tris, mat, mats = scenegen.c3_scene(base, level)
-            scene = ctx.scene_from_triangles(tris, mat, mats, builder=0, max_leaf=args.max_leaf)
-            del tris, mat
-    else:
-        scene = ctx.load_scene(scene_path)
-        if args.max_leaf:
-            scene.rebuild(builder=0, max_leaf=args.max_leaf)
-    scene_stats = scene.stats()
-    cam = pkg.look_at_camera(*c5_cam, w, h) if generated and scene_path.endswith("c5") else pkg.default_camera(w, h)
-    film = ctx.create_film(w, h)
-    film_ptr, film_bytes = film.device_buffer()
-    film_tensor = None
-    if world > 1:
-        film_tensor = torch.as_tensor(DeviceArray(film_ptr, film_bytes // 4), device=torch.device("cuda", local_rank))
-        lib_stream = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", local_rank))
-    import numpy as np
-    rgb_host = np.empty((h, w, 3), np.uint8)
-
-    def barrier():
-        ctx.sync()
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    kw = dict(spp=spp, max_depth=depth, rng_mode=rng_mode, pipeline=pipeline, shard_mode=shard_mode, shard_rank=rank, shard_world=world,
-              loop_min_blocks=args.min_blocks, chunks=args.chunks, shade_batch=args.shade_batch)
-
-    def step(host_output, stage_timing=False):
-        """One frame.  host_output=False: result stays in HBM (device resolve). True: RGB8 image copied to the host."""
-        ctx.flush_l2()                                # 256 MB memset on the render stream (~0.05 ms): nothing of the last frame stays in L2
-        st = ctx.render(scene, cam, film, stage_timing=stage_timing, **kw)
-        if world > 1:
-            with torch.cuda.stream(lib_stream):
-                dist.all_reduce(film_tensor)          # NCCL film combine over NVLink (sum of disjoint tiles / sample ranges)
-            film.set_sample_count(spp)
-        if host_output:
-            film.rgb8(out=rgb_host)                   # resolve + D2H of w*h*3 bytes, like renderFrame (application.h:211-212)
-        else:
-            film.resolve_device()                     # RGB8 stays in HBM (the film's own device buffer)
-        return st
-
+    run = Run(pkg, ctx, comm, dist, torch, rank, world, args.workload, spp, depth, args.rng, pipeline, args)
+    scene_stats = run.scene.stats()
     gpu_base = None
     if rank == 0 and not generated and not args.no_gpu_baseline:
         # one frame of ours for the exact segment counts (depth of the config, and depth 5 for the unmodified kernel), then the
-        # reference's CUDA kernels on this very GPU; the other ranks wait at the barrier below
-        kw1 = dict(kw); kw1.update(shard_mode=pkg.SHARD_NONE, shard_rank=0, shard_world=1)
-        seg_full = ctx.render(scene, cam, film, **kw1)["segments"]
+        # reference's CUDA kernels on this very GPU; the other ranks wait at the first barrier of measure()
+        kw1 = dict(run.kw); kw1.update(shard_mode=pkg.SHARD_NONE, shard_rank=0, shard_world=1)
+        seg_full = ctx.render(run.scene, run.cam, run.film, **kw1)["segments"]
         kw5 = dict(kw1); kw5.update(max_depth=5)
-        seg_d5 = ctx.render(scene, cam, film, **kw5)["segments"]
+        seg_d5 = ctx.render(run.scene, run.cam, run.film, **kw5)["segments"]
         ctx.sync()
         gpu_base = gpu_baseline(scene_path, w, h, spp, depth, seg_full, seg_d5)
-        film.reset()
-    for _ in range(args.warmup):
-        step(False)
-    # ---- timed region A: inputs resident in HBM, device events on the launching stream ------------
+        run.film.reset()
     sampler = ClockSampler(local_rank)
     sampler.start()
-    barrier()
-    ctx.timer_start()
-    seg = launches = 0
-    for _ in range(args.steps):
-        st = step(False)
-        seg += st["segments"]; launches += st["kernel_launches"] + 1
-    ms_dev = ctx.timer_stop()
-    barrier()
-    # ---- timed region B: end to end through the C ABI with host buffers ---------------------------
-    barrier()
-    t0 = time.perf_counter()
-    seg_e2e = 0
-    for _ in range(args.steps):
-        if not (generated and scene_path.endswith("c5")):
-            cam = pkg.default_camera(w, h)            # host camera update + by-value upload, like renderFrame (application.h:161-164)
-        st = step(True)
-        seg_e2e += st["segments"]
-    ctx.sync()
-    ms_e2e = (time.perf_counter() - t0) * 1e3
-    barrier()
+    m = run.measure(args.steps, args.warmup)
     sampler.stop_flag = True
     sampler.join(timeout=2)
-    # ---- dominant-kernel timing (separate, per-launch events; not part of the timed regions) ------
-    st_t = step(False, stage_timing=True)
+    clocks = sampler.summary()
+    st_t = run.step(False, stage_timing=True)          # dominant-kernel time of one more frame (per-launch events; outside the timed regions)
+    check = run.check_against_unsharded() if world > 1 else None
+    roof = roofline_of(run, m, st_t, args, clocks, sm_count) if pipeline in (pkg.PIPELINE_PERSIST, pkg.PIPELINE_FLAT, pkg.PIPELINE_DEFAULT) else None
+    run.close()
 
-    seg_all, seg_e2e_all, ms_dev_max, ms_e2e_max = seg, seg_e2e, ms_dev, ms_e2e
-    if world > 1:
-        t = torch.tensor([float(seg), float(seg_e2e)], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t)
-        seg_all, seg_e2e_all = t[0].item(), t[1].item()
-        m = torch.tensor([ms_dev, ms_e2e], dtype=torch.float64, device="cuda")
-        dist.all_reduce(m, op=dist.ReduceOp.MAX)
-        ms_dev_max, ms_e2e_max = m[0].item(), m[1].item()
+    # ---- secondary records (outside the headline timing): the other configurations the targets are quoted on ----
+    extra = {}
+    if not args.no_extra and args.workload == "c2" and args.spp == 0:
+        def secondary(workload, rng, spp_x, steps, note):
+            _, ww, hh, spp_full, dd = WORKLOADS[workload]
+            r = Run(pkg, ctx, comm, dist, torch, rank, world, workload, spp_x or spp_full, dd, rng, pkg.PIPELINE_DEFAULT, args)
+            mm = r.measure(steps, 1, e2e=False)
+            rec = {"workload": f"{workload}: {WORKLOADS[workload][0]} {ww}x{hh}, {spp_x or spp_full} spp, depth {dd}", "rng": rng, "value": mm["value"], "unit": METRIC,
+                   "ms_per_step": mm["ms_per_step"], "steps": steps, "warmup": 1, "n_gpus": world, "note": note,
+                   "sharding": {0: "none", 1: "tiles", 2: "sample ranges"}[r.shard_mode]}
+            if world > 1:
+                rec["multi_rank_check"] = r.check_against_unsharded()
+            sst = r.scene.stats()
+            if sst["node_bytes"] + sst["triangle_bytes"] > 126e6:
+                stt = r.step(False, stage_timing=True)
+                rec["roofline"] = roofline_of(r, mm, stt, args, clocks, sm_count)
+                rec["scene"] = {k: sst[k] for k in ("n_triangles", "n_nodes", "build_ms", "sah_cost")}
+            r.close()
+            return rec
+        extra["philox"] = secondary("c2", "philox", 0, 3, "counter RNG; sharded by sample range when n_gpus > 1")
+        extra["c4"] = secondary("c4", "compat", 1024, 3, "the 4K mirror / emissive Cornell scene of the >= 7x scaling target, at 1024 of its 4096 spp")
+        if world == 1:
+            extra["c3"] = secondary("c3", "compat", 0, 3, "10.5 M triangles: the traversal-roofline target (>= 0.60)")
 
     if rank == 0:
-        peak, peak_src = read_peaks()
-        value = seg_all / (ms_dev_max * 1e-3) * 1e-6
-        e2e_value = seg_e2e_all / (ms_e2e_max * 1e-3) * 1e-6
-        fused = pipeline == pkg.PIPELINE_FUSED
-        # algorithmic bytes per segment of the dominant kernel (DESIGN.md section 4)
-        loop = pipeline == pkg.PIPELINE_LOOP
-        bytes_per_slot_launch = None
-        if pipeline in (pkg.PIPELINE_PERSIST, pkg.PIPELINE_FLAT, pkg.PIPELINE_DEFAULT):
-            # no path state in memory: per owned pixel and sample chunk the compat kernel moves its id 4 + RNG state 24 + 24 + pixel sum 16 + 16 bytes;
-            # per path the counter-RNG kernel moves its pixel id 4 + three float atomics 12
-            # (a pixel is handed on between its sample chunks: per chunk pixel id 4 + RNG state 24 + 24 + pixel sum 16 + 16 + progress flag 4 + 4)
-            n_chunks = compat_chunk_count(spp, args.chunks, (w * h / world) / (ctx.device_info()["sm_count"] * 768.0))
-            per_item = 92.0 * n_chunks * (w * h / world) if rng_mode == pkg.RNG_XORWOW_COMPAT else 16.0 * st_t["paths"]
-            bytes_per_seg = per_item / max(st_t["segments"], 1)
-            is_flat = pipeline == pkg.PIPELINE_FLAT or (pipeline == pkg.PIPELINE_DEFAULT and scene_stats.get("flat_units", 0) > 0)
-            kname = ("k_path_flat<rng> (one launch per frame: flat unit-list extend + shade + regenerate, all state in registers)" if is_flat else
-                     "k_path_persist<rng> (one launch per frame: BVH8 extend + shade + regenerate, all state in registers)")
-            k_ms = st_t["shade_ms"]
-        elif loop:
-            # per live slot per launch: queue 4 + read A,B,C,E 64 + D 8 + write A,B,C,E 64 + D 8, compat adds RNG 24+24 and pixel sum 16+16
-            bytes_per_slot_launch = 148 + (80 if rng_mode == pkg.RNG_XORWOW_COMPAT else 0)
-            bytes_per_seg = bytes_per_slot_launch * st_t["slot_launches"] / max(st_t["segments"], 1)
-            kname, k_ms = "k_path_loop<rng> (extend+shade+regenerate, state in registers)", st_t["shade_ms"]
-        elif fused:
-            bytes_per_seg = 4 + 48 + 8 + 48 + (48 if rng_mode == pkg.RNG_XORWOW_COMPAT else 0)
-            kname, k_ms = "k_shade<rng,FUSED> (bounce: extend+shade)", st_t["shade_ms"]
-        else:
-            bytes_per_seg = 4 + 48 + 8 + 40 + (48 if rng_mode == pkg.RNG_XORWOW_COMPAT else 0)
-            kname, k_ms = "k_shade<rng>", st_t["shade_ms"]
-        traversal = None
-        if scene_stats["node_bytes"] + scene_stats["triangle_bytes"] > 126e6:
-            # scene larger than L2: the bound is node + triangle fetch traffic (SURVEY.md 8(d)); N_node, N_tri per segment
-            # measured by the instrumented extend kernel on a 2-spp frame outside the timed region
-            # (the whole frame, unsharded: a 2-spp frame split into sample ranges leaves most ranks without a sample)
-            kwc = dict(kw); kwc.update(spp=2, pipeline=pkg.PIPELINE_WAVEFRONT, shard_mode=pkg.SHARD_NONE, shard_rank=0, shard_world=1)
-            st_c = ctx.render(scene, cam, film, count_work=True, **kwc)
-            n_node, n_tri = st_c["node_visits"] / max(st_c["segments"], 1), st_c["tri_tests"] / max(st_c["segments"], 1)
-            bytes_per_seg = n_node * 80 + n_tri * 48
-            traversal = {"nodes_per_segment": n_node, "tris_per_segment": n_tri, "node_bytes": 80, "tri_bytes": 48}
-        achieved = st_t["segments"] * bytes_per_seg / (k_ms * 1e-3) * 1e-9 if k_ms > 0 else None
-        # measured DRAM bytes per launch of the dominant kernel (ncu capture of this very configuration, profiles/traffic.json)
-        traffic = traffic_src = issue = None
-        tkey = f"{args.workload}/{args.rng}/{'flat' if (pipeline in (pkg.PIPELINE_FLAT, pkg.PIPELINE_DEFAULT) and scene_stats.get('flat_units', 0) > 0) else ('persist' if args.pipeline == 'auto' else args.pipeline)}"
-        tpath = os.path.join(ROOT, "profiles", "traffic.json")
-        if world == 1 and args.spp == 0 and os.path.exists(tpath):
-            ent = json.load(open(tpath)).get(tkey)
-            if ent:
-                traffic, traffic_src = ent["bytes"], ent["source"]
-                issue = ent.get("issue")
         out = {
-            "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_dev_max / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "metric": METRIC, "value": m["value"], "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": m["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload_desc, "rng": args.rng, "pipeline": args.pipeline,
-                       "sharding": {0: "none", 1: "tiles", 2: "sample ranges"}[shard_mode],
+                       "sharding": {0: "none", 1: "tiles", 2: "sample ranges"}[run.shard_mode],
+                       "film_combine": None if world == 1 else ("ptx_film_combine (library): pack owned tiles + ncclAllGather + unpack" if run.shard_mode == pkg.SHARD_TILES else "ptx_film_combine (library): in-place ncclAllReduce"),
                        "l2": "flushed before every step: 256 MB memset on the render stream, inside the timed region (film + RNG state are %.0f MB)" % (w * h * 40 / 1e6 / world),
-                       "segments_per_step": seg_all / args.steps},
-            "clocks": sampler.summary(),
-            "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": ctypes.sizeof(pkg.Camera), "d2h_bytes_per_step": w * h * 3,
-                    "ms_per_step": ms_e2e_max / args.steps},
-            "gpu_launches": launches,
-            "roofline": {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
-                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "bytes_per_segment": bytes_per_seg,
-                         "kernel_ms_per_step": k_ms, "kernel_share_of_step": k_ms / st_t["render_ms"] if st_t["render_ms"] else None,
-                         "traversal": traversal, "bytes_per_slot_launch": bytes_per_slot_launch,
-                         # not part of the contract: what ncu says about the bound that really limits this kernel (issue slots)
-                         "issue": issue},
+                       "segments_per_step": m["seg"] / args.steps},
+            "clocks": clocks,
+            "e2e": {"value": m["e2e_value"], "unit": METRIC, "h2d_bytes_per_step": ctypes.sizeof(pkg.Camera), "d2h_bytes_per_step": w * h * 3,
+                    "ms_per_step": m["ms_e2e"] / args.steps},
+            "gpu_launches": m["launches"],
+            "roofline": roof,
             "scene": {k: scene_stats[k] for k in ("n_triangles", "n_nodes", "node_bytes", "triangle_bytes", "build_ms", "builder", "max_depth", "sah_cost", "flat_units")},
         }
+        if check is not None:
+            out["multi_rank_check"] = check
+        if extra:
+            out["extra"] = extra
         if gpu_base is not None:
             out["gpu_baseline"] = gpu_base
             if gpu_base.get("value"):
-                out["gpu_baseline"]["speedup_device"] = value / gpu_base["value"] / world
+                out["gpu_baseline"]["speedup_device"] = m["value"] / gpu_base["value"] / world
                 out["gpu_baseline"]["note"] = "speedup_device = value / n_gpus / gpu_baseline.value (per-GPU throughput of this build over the reference CUDA build on one B200)"
         if world == 1 and not args.no_cpu_baseline and generated:
             out["cpu_baseline"] = {"value": None, "unit": METRIC, "cores": 0, "kind": "reference",
@@ -370,14 +442,18 @@ def run_ours(args, scene_path, w, h, spp, depth):
                 spp_ratio = segments_per_path_estimate(scene_path, w, h, depth)
                 j = ref_host_run(scene_path, w, h, cb_spp, depth, 1)
                 out["cpu_baseline"] = {"value": w * h * cb_spp * spp_ratio / (j["ms_per_frame"] * 1e-3) * 1e-6, "unit": METRIC, "cores": j["threads"],
-                                       "kind": "reference", "sample": f"{w}x{h}, {cb_spp} of {spp} spp, depth {depth}, oracle/_ref/ref_host (reference headers, host build, OpenMP rows)"}
+                                       "kind": "reference", "sample": f"{w}x{h}, {cb_spp} of {spp} spp, depth {depth}, oracle/_ref/ref_host (reference headers, host build, OpenMP rows)",
+                                       "segments_per_path_source": "C oracle on a 1/8-scale frame at 4 spp (same streams), not counted on the timed frame"}
             except Exception as e:       # noqa: BLE001
                 out["cpu_baseline"] = {"value": None, "error": str(e)[:200]}
         emit(out)
-    film.close(); scene.close(); ctx.close()
+    if comm is not None:
+        comm.close()
+    ctx.close()
     if world > 1:
         dist.destroy_process_group()
-
+    if check is not None and not check["ok"]:
+        raise SystemExit("multi-rank film check failed: " + json.dumps(check))
 
 _REAL_STDOUT = None
 
@@ -424,6 +500,7 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override spp (reduced runs are NOT the headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary records (extra.philox / extra.c4 / extra.c3) of the default C2 run")
     ap.add_argument("--min-blocks", type=int, default=0, help="experiment: occupancy variant of the path-loop kernels (0 = 3x256 threads/SM, 4 = 4x256, 7 = 7x128)")
     ap.add_argument("--chunks", type=int, default=0, help="experiment: work items per pixel of the persistent kernel, compat RNG (0 = default 6, 1 = none)")
     ap.add_argument("--shade-batch", type=int, default=0, help="experiment: waiting lanes per warp that trigger a shading round (0 = default 12, 1 = at once)")
@@ -441,7 +518,7 @@ def main():
     if args.impl == "reference":
         run_reference(args, scene_path, w, h, spp, depth)
     else:
-        run_ours(args, scene_path, w, h, spp, depth)
+        run_ours(args, w, h, spp, depth)
 
 
 if __name__ == "__main__":

@@ -15,6 +15,7 @@ LIB_PATH = os.environ.get("PTX_LIB") or os.path.join(HERE, "libptx.so")      # P
 RNG_XORWOW_COMPAT, RNG_PHILOX = 0, 1
 SHARD_NONE, SHARD_TILES, SHARD_SAMPLES = 0, 1, 2
 NOALLOC_MAX_RAYS = 65536
+RENDER_STAGE_TIMING, RENDER_COUNT_WORK, RENDER_ASYNC = 1, 2, 4
 PIPELINE_DEFAULT, PIPELINE_FUSED, PIPELINE_LOOP, PIPELINE_PERSIST, PIPELINE_WAVEFRONT, PIPELINE_CTA, PIPELINE_FLAT = 0, 1, 2, 3, 4, 5, 6
 SAMPLING_BSDF, SAMPLING_FORMFACTOR, SAMPLING_RADIOSITY, SAMPLING_MIS, SAMPLING_TOPK = 0, 1, 2, 3, 4
 
@@ -65,7 +66,8 @@ class Camera(C.Structure):
 class RenderOpts(C.Structure):
     _fields_ = [("spp", C.c_int32), ("max_depth", C.c_int32), ("rng_mode", C.c_int32), ("sampling_mode", C.c_int32),
                 ("accumulate", C.c_int32), ("shard_mode", C.c_int32), ("shard_rank", C.c_int32), ("shard_world", C.c_int32),
-                ("rr_start_depth", C.c_int32), ("rr_cap", C.c_float), ("pipeline", C.c_int32), ("reserved", C.c_int32 * 5)]
+                ("rr_start_depth", C.c_int32), ("rr_cap", C.c_float), ("pipeline", C.c_int32),
+                ("flags", C.c_int32), ("loop_iters", C.c_int32), ("ctas_per_sm", C.c_int32), ("chunks", C.c_int32), ("shade_batch", C.c_int32)]
 
 
 class RenderStats(C.Structure):
@@ -84,7 +86,8 @@ EXPORTS = [
     "ptx_film_create", "ptx_film_reset", "ptx_film_clear", "ptx_film_resolve_rgb8", "ptx_film_read_linear", "ptx_film_write", "ptx_write_png_rgb8",
     "ptx_film_device_buffer", "ptx_film_set_sample_count", "ptx_film_destroy",
     "ptx_shard_pixel_count", "ptx_shard_owned_pixels", "ptx_shard_sample_range",
-    "ptx_render", "ptx_render_stats_get", "ptx_trace_primary_ids", "ptx_trace_rays", "ptx_trace_rays_noalloc", "ptx_trace_occluded", "ptx_render_visibility", "ptx_film_rng_state",
+    "ptx_render", "ptx_render_stats_get", "ptx_comm_unique_id", "ptx_comm_create", "ptx_comm_destroy", "ptx_film_combine",
+    "ptx_trace_primary_ids", "ptx_trace_rays", "ptx_trace_rays_noalloc", "ptx_trace_occluded", "ptx_render_visibility", "ptx_film_rng_state",
 ]
 
 _lib = None
@@ -106,6 +109,11 @@ def lib():
         L.ptx_film_set_sample_count.argtypes = [C.c_void_p, C.c_float]
         L.ptx_ctx_flush_l2.argtypes = [C.c_void_p]
         L.ptx_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_float, C.c_void_p, C.c_void_p]
+        L.ptx_comm_unique_id.argtypes = [C.c_void_p, C.c_size_t]
+        L.ptx_comm_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.ptx_comm_destroy.argtypes = [C.c_void_p]
+        L.ptx_comm_destroy.restype = None
+        L.ptx_film_combine.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
         L.ptx_trace_rays_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_float, C.c_void_p, C.c_void_p]
         L.ptx_trace_occluded.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.ptx_render_visibility.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
@@ -273,18 +281,18 @@ class Context:
 
     # -- rendering ----------------------------------------------------------------------------
     def render(self, scene, camera, film, spp, max_depth=5, rng_mode=RNG_XORWOW_COMPAT, accumulate=False, shard_mode=SHARD_NONE,
-               shard_rank=0, shard_world=1, pipeline=PIPELINE_DEFAULT, stage_timing=False, count_work=False, sampling_mode=0, loop_iters=0, loop_min_blocks=0, chunks=0, shade_batch=0):
+               shard_rank=0, shard_world=1, pipeline=PIPELINE_DEFAULT, stage_timing=False, count_work=False, sampling_mode=0, loop_iters=0, loop_min_blocks=0, chunks=0, shade_batch=0, async_=False):
         o = RenderOpts()
         o.spp, o.max_depth, o.rng_mode, o.sampling_mode = int(spp), int(max_depth), int(rng_mode), int(sampling_mode)
         o.accumulate, o.shard_mode, o.shard_rank, o.shard_world = int(accumulate), int(shard_mode), int(shard_rank), int(shard_world)
         o.pipeline = int(pipeline)
-        o.reserved[0] = (1 if stage_timing else 0) | (2 if count_work else 0)
-        o.reserved[1] = int(loop_iters)
-        o.reserved[2] = int(loop_min_blocks)
-        o.reserved[3] = int(chunks)
-        o.reserved[4] = int(shade_batch)
+        o.flags = (RENDER_STAGE_TIMING if stage_timing else 0) | (RENDER_COUNT_WORK if count_work else 0) | (RENDER_ASYNC if async_ else 0)
+        o.loop_iters = int(loop_iters)
+        o.ctas_per_sm = int(loop_min_blocks)
+        o.chunks = int(chunks)
+        o.shade_batch = int(shade_batch)
         _check(lib().ptx_render(self._h, scene._h, C.byref(camera), film._h, C.byref(o)), self._h)
-        return self.render_stats()
+        return None if async_ else self.render_stats()       # async: statistics on the next render_stats() / sync()
 
     def render_stats(self):
         st = RenderStats()
@@ -303,6 +311,13 @@ class Context:
         ts = np.empty(len(rays), np.float32)
         _check(lib().ptx_trace_rays(self._h, scene._h, _ptr(rays), len(rays), C.c_float(t_min), _ptr(ids), _ptr(ts)), self._h)
         return ids, ts
+
+    def create_comm(self, unique_id, rank, world):
+        """Collective: every rank passes the 128-byte id rank 0 got from comm_unique_id()."""
+        buf = (C.c_uint8 * 128).from_buffer_copy(bytes(unique_id))
+        h = C.c_void_p()
+        _check(lib().ptx_comm_create(self._h, buf, int(rank), int(world), C.byref(h)), self._h)
+        return Comm(self, h)
 
     def trace_rays_noalloc(self, scene, rays, t_min=1e-4):
         """ptx_trace_rays_noalloc: the same query without any device allocation (at most NOALLOC_MAX_RAYS rays per call)."""
@@ -328,6 +343,22 @@ class Context:
         img = np.empty((film.height, film.width, 3), np.uint8)
         _check(lib().ptx_render_visibility(self._h, scene._h, C.byref(camera), film._h, int(spp), None if rad is None else _ptr(rad), _ptr(img)), self._h)
         return img
+
+
+def comm_unique_id():
+    buf = (C.c_uint8 * 128)()
+    _check(lib().ptx_comm_unique_id(buf, 128))
+    return bytes(buf)
+
+
+class Comm:
+    def __init__(self, ctx, handle):
+        self.ctx, self._h = ctx, handle
+
+    def close(self):
+        if self._h:
+            lib().ptx_comm_destroy(self._h)
+            self._h = C.c_void_p()
 
 
 class Scene:
@@ -407,6 +438,10 @@ class Film:
         p, n = C.c_void_p(), C.c_size_t()
         _check(lib().ptx_film_device_buffer(self._h, C.byref(p), C.byref(n)), self.ctx._h)
         return p.value, n.value
+
+    def combine(self, comm, shard_mode):
+        """ptx_film_combine: NCCL exchange of the ranks' films on the context's stream (no host synchronisation)."""
+        _check(lib().ptx_film_combine(self._h, comm._h, int(shard_mode)), self.ctx._h)
 
     def set_sample_count(self, spp_total):
         _check(lib().ptx_film_set_sample_count(self._h, float(spp_total)))

@@ -5,6 +5,8 @@
 // entry point that produces pixels or hits launches CUDA kernels and fails with PTX_ERR_NO_DEVICE /
 // PTX_ERR_CUDA when that is impossible.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>          // types only: the functions are resolved with dlopen (a single-GPU host needs no NCCL)
 
 #include <algorithm>
 #include <cmath>
@@ -47,6 +49,7 @@ struct ptx_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, tev0 = nullptr, tev1 = nullptr;
     std::vector<cudaEvent_t> stage_events;
     ptx_render_stats stats{};
+    bool stats_pending = false;                 // PTX_RENDER_ASYNC: the counters of the last render are still on their way
 };
 
 struct ptx_scene {
@@ -67,6 +70,7 @@ struct ptx_film {
     int w = 0, h = 0;
     float4* d_accum = nullptr; uint4* d_rngA = nullptr; uint2* d_rngB = nullptr; uint8_t* d_rgb8 = nullptr; float* d_linear = nullptr;
     float total_spp = 0.f;
+    float frame_spp = 0.f;                       // samples per pixel asked for over ALL ranks since the last clear (sample-range combine)
     uint32_t sample_base = 0;                    // global index of the next frame's first sample (progressive mode)
     unsigned long long seed_base = 2023ull;      // integrator.h:279
     FilmView view() const { FilmView f; f.accum = d_accum; f.rngA = d_rngA; f.rngB = d_rngB; f.width = w; f.height = h; return f; }
@@ -122,7 +126,7 @@ int ptx_ctx_create(int device, ptx_ctx** out) {
     if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (ce == cudaSuccess) ce = cudaEventCreate(&c->ev0);
     if (ce == cudaSuccess) ce = cudaEventCreate(&c->ev1);
-    if (ce == cudaSuccess) ce = cudaMallocHost(&c->h_counters, sizeof(unsigned long long) * CTR_COUNT);
+    if (ce == cudaSuccess) ce = cudaMallocHost(&c->h_counters, sizeof(unsigned long long) * CTR_COUNT * 2);
     if (ce == cudaSuccess) ce = cudaMalloc(&c->ws.counters, sizeof(unsigned long long) * CTR_COUNT);
     if (ce == cudaSuccess) ce = cudaMalloc(&c->d_jump, jump.size() * sizeof(uint32_t));
     if (ce == cudaSuccess) ce = cudaMemcpy(c->d_jump, jump.data(), jump.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
@@ -151,11 +155,24 @@ void ptx_ctx_destroy(ptx_ctx* c) {
     delete c;
 }
 
+// PTX_RENDER_ASYNC: wait for the last render and complete its statistics from the counters it copied back
+static int finalize_pending(ptx_ctx* c) {
+    if (!c->stats_pending) return PTX_OK;
+    c->stats_pending = false;
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+    const unsigned long long* hc = c->h_counters;
+    cudaEventElapsedTime(&c->stats.render_ms, c->ev0, c->ev1);
+    c->stats.shade_ms = c->stats.render_ms;
+    c->stats.segments = hc[CTR_SEGMENTS]; c->stats.paths = hc[CTR_PATHS];
+    return PTX_OK;
+}
+
 int ptx_sync(ptx_ctx* c) {
     if (!c) return fail(nullptr, PTX_ERR_INVALID, "ptx_sync: ctx is NULL");
     PTX_CUDA(c, cudaSetDevice(c->device));
     PTX_CUDA(c, cudaStreamSynchronize(c->stream));
-    return PTX_OK;
+    return finalize_pending(c);
 }
 
 int ptx_timer_start(ptx_ctx* c) {
@@ -530,7 +547,7 @@ int ptx_film_clear(ptx_film* f) {
     ptx_ctx* c = f->ctx;
     PTX_CUDA(c, cudaSetDevice(c->device));
     PTX_CUDA(c, cudaMemsetAsync(f->d_accum, 0, (size_t)f->w * f->h * sizeof(float4), c->stream));
-    f->total_spp = 0.f; f->sample_base = 0;
+    f->total_spp = 0.f; f->frame_spp = 0.f; f->sample_base = 0;
     return PTX_OK;
 }
 
@@ -707,6 +724,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     if (shard_mode == PTX_SHARD_SAMPLES && rng_mode != PTX_RNG_PHILOX)
         return fail(c, PTX_ERR_INVALID, "sample-range sharding needs the counter-based RNG (the XORWOW stream is sequential per pixel)");
     PTX_CUDA(c, cudaSetDevice(c->device));
+    { int frc = finalize_pending(c); if (frc != PTX_OK) return frc; }
 
     const int w = film->w, h = film->h;
     RenderParams rp{};
@@ -747,13 +765,13 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     // bounded by a 1/32 pixel.  U = 2 (1/2, 1/4, ... : 6 items per pixel) costs the fewest hand-offs and is right when every
     // lane gets many pixels; with few pixels per lane (a tile-sharded 1080p frame on 8 GPUs: 2.3) a pixel whose first half
     // starts late cannot finish its remaining half inside the frame, and more, smaller parts keep all chains moving in
-    // step.  reserved[3] overrides: n > 0 = n halving chunks, n < 0 = U = -n.
+    // step.  opts->chunks overrides: n > 0 = n halving chunks, n < 0 = U = -n.
     {
         const uint32_t spp = (uint32_t)std::max(rp.spp, 0);
         const uint32_t floor_sz = std::max(1u, spp / 32u);
         int U = 2;
-        if (opts->reserved[3] < 0) U = -opts->reserved[3];
-        else if (opts->reserved[3] == 0) {
+        if (opts->chunks < 0) U = -opts->chunks;
+        else if (opts->chunks == 0) {
             const double per_lane = (double)rp.n_owned / ((double)c->prop.multiProcessorCount * 768.0);
             // C2 on one rank of 1 / 2 / 4 / 8: 18 / 9 / 4.6 / 2.3 pixels per lane (tools/shard_probe.py).  Parts shorter than 64
             // samples cost more in hand-offs than they gain (C1, 64 spp: 13.8 -> 12.2 G with eight parts)
@@ -762,10 +780,10 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
         U = (int)std::min<uint32_t>((uint32_t)std::max(U, 1), std::max(1u, std::min(spp, 32u)));
         int n = 0;
         rp.chunk_start[0] = 0;
-        if (opts->reserved[3] > 0) {
+        if (opts->chunks > 0) {
             int log2spp = 0;
             while ((spp >> (log2spp + 1)) > 0) log2spp++;
-            const int want = std::min(opts->reserved[3], log2spp + 1);
+            const int want = std::min(opts->chunks, log2spp + 1);
             for (n = 1; n < want; n++) rp.chunk_start[n] = spp - (spp >> n);
         } else if (spp > 0) {
             for (n = 1; n < U; n++) rp.chunk_start[n] = (uint32_t)((unsigned long long)spp * (unsigned)n / (unsigned)U);
@@ -775,7 +793,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
         rp.n_chunks = std::max(n, 1);
         for (int i = rp.n_chunks; i <= kMaxChunks; i++) rp.chunk_start[i] = spp;
     }
-    rp.shade_batch = opts->reserved[4] > 0 ? opts->reserved[4] : 12;      // lanes of a warp that must be waiting before it shades
+    rp.shade_batch = opts->shade_batch > 0 ? opts->shade_batch : 12;      // lanes of a warp that must be waiting before it shades
     int key[5] = {w, h, shard_mode, rank, world};
     if (memcmp(key, c->slot_key, sizeof key) != 0) {
         launch_slot_pixels(c->stream, c->ws.slot_pixel, w, h, shard_mode, rank, world, rp.n_owned);
@@ -788,17 +806,18 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     const bool fused = pipeline == 1;
     const bool path_loop = pipeline == 2;
     // bounces per path-loop launch: a compat-mode slot lives for >= spp segments, so long launches waste
-    // little on lanes that die early; reserved[1] overrides (tuning / tests)
-    int loop_iters = opts->reserved[1] > 0 ? opts->reserved[1] : 2 * std::min(std::max(rp.spp, 16), 256);
-    const bool count_work = (opts->reserved[0] & 2) != 0;
-    const bool stage_timing = (opts->reserved[0] & 1) != 0;
+    // little on lanes that die early; opts->loop_iters overrides (tuning / tests)
+    int loop_iters = opts->loop_iters > 0 ? opts->loop_iters : 2 * std::min(std::max(rp.spp, 16), 256);
+    const bool count_work = (opts->flags & 2) != 0;
+    const bool stage_timing = (opts->flags & 1) != 0;
 
     unsigned long long live0 = (rp.spp > 0) ? std::min<unsigned long long>(rp.n_slots, rng_mode == PTX_RNG_PHILOX ? rp.total_paths : rp.n_slots) : 0ull;
-    unsigned long long* hc = c->h_counters;
+    unsigned long long* hc = c->h_counters + CTR_COUNT;   // upload half of the pinned block (the first half is the read-back buffer)
     for (int i = 0; i < CTR_COUNT; i++) hc[i] = 0;
     hc[CTR_LIVE] = live0; hc[CTR_QLEN] = rp.n_slots; hc[CTR_NEXT_PATH] = persist ? 0ull : rp.n_slots;
     PTX_CUDA(c, cudaMemcpyAsync(c->ws.counters, hc, sizeof(unsigned long long) * CTR_COUNT, cudaMemcpyHostToDevice, c->stream));
-    PTX_CUDA(c, cudaStreamSynchronize(c->stream));      // hc is reused as the read-back buffer below
+    hc = c->h_counters;                                   // read-back half from here on
+    const bool async = persist && (opts->flags & PTX_RENDER_ASYNC) != 0;
 
     ptx_render_stats st{};
     PTX_CUDA(c, cudaEventRecord(c->ev0, c->stream));
@@ -813,7 +832,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
             for (int k = 0; k < 3; k++) scale = std::max(scale, std::fabs(cam->origin[k]));
             flat_margins(scale, fs.m0, fs.m1);
             fs.key_mask = kFlatKeyMask;
-            int per_sm = opts->reserved[2] & 15;
+            int per_sm = opts->ctas_per_sm & 15;
             if (per_sm == 0) {
                 // Resident CTAs per SM (256 threads each).  Bulk throughput is best with 4 (64 registers; C2 28.6 against 27.0 G
                 // with 3).  With the sequential RNG a frame cannot end before its longest pixel chain, and a chain advances
@@ -825,8 +844,8 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
                 else per_sm = px_per_lane >= 8.0 ? 4 : 3;
             }
             launch_path_flat(c->stream, rng_mode, c->ws, scene->view, fs, fv, cv, rp, c->prop.multiProcessorCount, per_sm);
-        } else if (cta_wave) launch_path_cta(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->reserved[2]);
-        else launch_path_persist(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->reserved[2]);
+        } else if (cta_wave) launch_path_cta(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->ctas_per_sm);
+        else launch_path_persist(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->ctas_per_sm);
         PTX_CUDA(c, cudaGetLastError());
         st.kernel_launches++;
         live0 = 0;
@@ -851,7 +870,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
         if (path_loop) {
             iters = loop_iters;
             if (stage_timing) cudaEventRecord(c->stage_events[1], c->stream);
-            launch_path_loop(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, q, qbound, iters, opts->reserved[2]);
+            launch_path_loop(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, q, qbound, iters, opts->ctas_per_sm);
             if (stage_timing) cudaEventRecord(c->stage_events[2], c->stream);
             st.kernel_launches++; st.iterations += (uint64_t)iters;
         }
@@ -892,6 +911,16 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     }
     PTX_CUDA(c, cudaEventRecord(c->ev1, c->stream));
     PTX_CUDA(c, cudaMemcpyAsync(hc, c->ws.counters, sizeof(unsigned long long) * CTR_COUNT, cudaMemcpyDeviceToHost, c->stream));
+    if (shard_mode == PTX_SHARD_SAMPLES) film->total_spp += (float)spp_local;   // partial: ptx_film_combine (or the caller) sets the total
+    else film->total_spp += (float)opts->spp;
+    film->frame_spp += (float)opts->spp;
+    film->sample_base += (uint32_t)opts->spp;
+    if (async) {                                          // completed by finalize_pending()
+        PTX_CUDA(c, cudaGetLastError());
+        c->stats = st;
+        c->stats_pending = true;
+        return PTX_OK;
+    }
     PTX_CUDA(c, cudaStreamSynchronize(c->stream));
     PTX_CUDA(c, cudaGetLastError());
     cudaEventElapsedTime(&st.render_ms, c->ev0, c->ev1);
@@ -900,9 +929,6 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     st.other_ms = st.render_ms - st.extend_ms - st.shade_ms;
     st.node_visits = hc[CTR_NODE_VISITS]; st.tri_tests = hc[CTR_TRI_TESTS]; st.slot_launches = hc[CTR_SLOT_LAUNCHES];
     c->stats = st;
-    if (shard_mode == PTX_SHARD_SAMPLES) film->total_spp += (float)spp_local;   // partial: caller reduces and sets the total
-    else film->total_spp += (float)opts->spp;
-    film->sample_base += (uint32_t)opts->spp;
     return PTX_OK;
 }
 
@@ -935,6 +961,7 @@ int ptx_shard_sample_range(int spp, int shard_mode, int rank, int world, int32_t
 
 int ptx_render_stats_get(const ptx_ctx* c, ptx_render_stats* out) {
     if (!c || !out) return fail(nullptr, PTX_ERR_INVALID, "ptx_render_stats_get: NULL argument");
+    { int frc = finalize_pending(const_cast<ptx_ctx*>(c)); if (frc != PTX_OK) return frc; }
     *out = c->stats;
     return PTX_OK;
 }
@@ -1041,6 +1068,141 @@ int ptx_render_visibility(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* 
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     cudaFree(d_rad); cudaFree(d_img);
     if (e != cudaSuccess) return cuda_fail(c, e, "ptx_render_visibility");
+    return PTX_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// multi-GPU film combine: one process per GPU, the scene replicated, every rank renders its share
+// (ptx_render_opts.shard_*) and the films are combined over NCCL / NVLink INSIDE the library, on the context's stream.
+// The reference has no multi-GPU path: nothing to cite.
+// ---------------------------------------------------------------------------------------------
+}  // extern "C"
+
+namespace {
+struct NcclApi {
+    void* handle = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    std::string error;
+};
+NcclApi* nccl_api() {
+    static NcclApi api;
+    static bool tried = false;
+    if (tried) return &api;
+    tried = true;
+    // a process that already carries NCCL (e.g. PyTorch's bundled copy) gets that very copy: same soname
+    const char* names[] = {getenv("PTX_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+    for (const char* n : names) {
+        if (!n || !*n) continue;
+        api.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (api.handle) break;
+    }
+    if (!api.handle) { api.error = std::string("NCCL not found (set PTX_NCCL_LIB): ") + (dlerror() ? dlerror() : ""); return &api; }
+    bool ok = true;
+    auto sym = [&](const char* name) { void* p = dlsym(api.handle, name); if (!p) { ok = false; api.error = std::string("NCCL symbol missing: ") + name; } return p; };
+    api.GetUniqueId = (decltype(api.GetUniqueId))sym("ncclGetUniqueId");
+    api.CommInitRank = (decltype(api.CommInitRank))sym("ncclCommInitRank");
+    api.CommDestroy = (decltype(api.CommDestroy))sym("ncclCommDestroy");
+    api.AllGather = (decltype(api.AllGather))sym("ncclAllGather");
+    api.AllReduce = (decltype(api.AllReduce))sym("ncclAllReduce");
+    api.GetErrorString = (decltype(api.GetErrorString))sym("ncclGetErrorString");
+    if (!ok) { dlclose(api.handle); api.handle = nullptr; }
+    return &api;
+}
+}  // namespace
+
+struct ptx_comm {
+    ptx_ctx* ctx = nullptr;
+    ncclComm_t comm = nullptr;
+    int rank = 0, world = 1;
+    float4* d_gather = nullptr; size_t gather_capacity = 0;      // tiles: world x (pixels owned by rank 0) float4
+};
+
+extern "C" {
+
+int ptx_comm_unique_id(uint8_t* id_out, size_t bytes) {
+    if (!id_out || bytes < PTX_COMM_ID_BYTES) return fail(nullptr, PTX_ERR_INVALID, "ptx_comm_unique_id: the id needs PTX_COMM_ID_BYTES (128) bytes");
+    static_assert(sizeof(ncclUniqueId) == PTX_COMM_ID_BYTES, "ncclUniqueId is 128 bytes");
+    NcclApi* n = nccl_api();
+    if (!n->handle) return fail(nullptr, PTX_ERR_UNSUPPORTED, n->error);
+    ncclUniqueId id;
+    ncclResult_t r = n->GetUniqueId(&id);
+    if (r != ncclSuccess) return fail(nullptr, PTX_ERR_CUDA, std::string("ncclGetUniqueId: ") + n->GetErrorString(r));
+    memcpy(id_out, &id, sizeof id);
+    return PTX_OK;
+}
+
+int ptx_comm_create(ptx_ctx* c, const uint8_t* id, int rank, int world, ptx_comm** out) {
+    if (!c || !id || !out || world <= 0 || rank < 0 || rank >= world) return fail(c, PTX_ERR_INVALID, "ptx_comm_create: bad argument");
+    *out = nullptr;
+    NcclApi* n = nccl_api();
+    if (!n->handle) return fail(c, PTX_ERR_UNSUPPORTED, n->error);
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    ncclUniqueId uid;
+    memcpy(&uid, id, sizeof uid);
+    ptx_comm* m = new ptx_comm();
+    m->ctx = c; m->rank = rank; m->world = world;
+    ncclResult_t r = n->CommInitRank(&m->comm, world, uid, rank);
+    if (r != ncclSuccess) { delete m; return fail(c, PTX_ERR_CUDA, std::string("ncclCommInitRank: ") + n->GetErrorString(r)); }
+    *out = m;
+    return PTX_OK;
+}
+
+void ptx_comm_destroy(ptx_comm* m) {
+    if (!m) return;
+    cudaSetDevice(m->ctx->device);
+    cudaStreamSynchronize(m->ctx->stream);
+    if (m->comm) nccl_api()->CommDestroy(m->comm);
+    cudaFree(m->d_gather);
+    delete m;
+}
+
+int ptx_film_combine(ptx_film* f, ptx_comm* m, int shard_mode) {
+    if (!f || !m) return fail(nullptr, PTX_ERR_INVALID, "ptx_film_combine: NULL argument");
+    ptx_ctx* c = f->ctx;
+    if (m->ctx != c) return fail(c, PTX_ERR_INVALID, "ptx_film_combine: film and communicator belong to different contexts");
+    if (shard_mode != PTX_SHARD_TILES && shard_mode != PTX_SHARD_SAMPLES) return fail(c, PTX_ERR_INVALID, "ptx_film_combine: shard_mode must be PTX_SHARD_TILES or PTX_SHARD_SAMPLES");
+    NcclApi* n = nccl_api();
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    const int w = f->w, h = f->h;
+    FilmView fv = f->view();
+    ncclResult_t r = ncclSuccess;
+    if (shard_mode == PTX_SHARD_TILES) {
+        // every rank sends only what it owns (1 / G of the film, no zeros); rank 0 owns the most pixels, its count pads the slices
+        const uint32_t per_rank = owned_pixel_count(w, h, 1, 0, m->world);
+        const uint32_t mine = owned_pixel_count(w, h, 1, m->rank, m->world);
+        const size_t need = (size_t)per_rank * m->world;
+        if (need > m->gather_capacity) {
+            PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+            cudaFree(m->d_gather); m->d_gather = nullptr; m->gather_capacity = 0;
+            PTX_CUDA(c, cudaMalloc(&m->d_gather, need * sizeof(float4)));
+            m->gather_capacity = need;
+        }
+        int rc = ensure_pixmap(c, mine, 0u);
+        if (rc != PTX_OK) return rc;
+        int key[5] = {w, h, PTX_SHARD_TILES, m->rank, m->world};
+        if (memcmp(key, c->slot_key, sizeof key) != 0) {
+            launch_slot_pixels(c->stream, c->ws.slot_pixel, w, h, PTX_SHARD_TILES, m->rank, m->world, mine);
+            memcpy(c->slot_key, key, sizeof key);
+        }
+        float4* my_slice = m->d_gather + (size_t)m->rank * per_rank;
+        launch_film_pack_owned(c->stream, fv, c->ws.slot_pixel, mine, my_slice);
+        PTX_CUDA(c, cudaGetLastError());
+        r = n->AllGather(my_slice, m->d_gather, (size_t)per_rank * 4, ncclFloat32, m->comm, c->stream);     // in place
+        if (r != ncclSuccess) return fail(c, PTX_ERR_CUDA, std::string("ncclAllGather: ") + n->GetErrorString(r));
+        launch_film_unpack_all(c->stream, fv, m->d_gather, per_rank, m->world);
+        PTX_CUDA(c, cudaGetLastError());
+    } else {
+        // sample ranges: every rank holds partial sums of every pixel
+        r = n->AllReduce(f->d_accum, f->d_accum, (size_t)w * h * 4, ncclFloat32, ncclSum, m->comm, c->stream);
+        if (r != ncclSuccess) return fail(c, PTX_ERR_CUDA, std::string("ncclAllReduce: ") + n->GetErrorString(r));
+        f->total_spp = f->frame_spp;          // what the ranks were asked for together (ptx_render keeps count)
+    }
     return PTX_OK;
 }
 

@@ -1147,6 +1147,25 @@ __global__ void __launch_bounds__(kBlock) k_film_scale(FilmView film, float inv_
 }
 
 // ---------------------------------------------------------------------------------------------
+// film combine, tile sharding (ptx_film_combine): every rank packs the running sums of the pixels it owns into its slice
+// of the gather buffer, one ncclAllGather moves 1 / G of the film per rank, and every rank unpacks all slices into its film.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) k_film_pack_owned(FilmView film, const uint32_t* __restrict__ slot_pixel, uint32_t n_owned, float4* dst) {
+    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+    if (i < n_owned) dst[i] = film.accum[slot_pixel[i]];
+}
+// inverse of k_slot_pixels for every rank at once: pixel -> (owner, local slot)
+__global__ void __launch_bounds__(kBlock) k_film_unpack_all(FilmView film, const float4* __restrict__ gathered, uint32_t per_rank, int world) {
+    uint32_t p = blockIdx.x * kBlock + threadIdx.x;
+    uint32_t npix = (uint32_t)film.width * (uint32_t)film.height;
+    if (p >= npix) return;
+    const uint32_t band_px = (uint32_t)kBandRows * (uint32_t)film.width;
+    const uint32_t band = p / band_px, within = p - band * band_px;
+    const uint32_t owner = band % (uint32_t)world, local_band = band / (uint32_t)world;
+    film.accum[p] = gathered[(size_t)owner * per_rank + (size_t)local_band * band_px + within];
+}
+
+// ---------------------------------------------------------------------------------------------
 // queries for parity tests
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock) k_primary_ids(SceneView scene, CameraView cam, int w, int h, int32_t* prim, float* tout) {
@@ -1380,6 +1399,15 @@ void launch_resolve(cudaStream_t st, const FilmView& film, float inv_spp, uint8_
     size_t npix = (size_t)film.width * film.height;
     if (!npix) return;
     k_resolve<<<blocks_for(npix, kBlock), kBlock, 0, st>>>(film, inv_spp, rgb8, flip_y);
+}
+void launch_film_pack_owned(cudaStream_t st, const FilmView& film, const uint32_t* slot_pixel, uint32_t n_owned, float4* dst) {
+    if (!n_owned) return;
+    k_film_pack_owned<<<blocks_for(n_owned, kBlock), kBlock, 0, st>>>(film, slot_pixel, n_owned, dst);
+}
+void launch_film_unpack_all(cudaStream_t st, const FilmView& film, const float4* gathered, uint32_t per_rank, int world) {
+    size_t npix = (size_t)film.width * film.height;
+    if (!npix) return;
+    k_film_unpack_all<<<blocks_for(npix, kBlock), kBlock, 0, st>>>(film, gathered, per_rank, world);
 }
 void launch_film_scale(cudaStream_t st, const FilmView& film, float inv_spp, float* linear_rgb) {
     size_t npix = (size_t)film.width * film.height;

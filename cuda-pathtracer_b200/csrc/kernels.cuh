@@ -88,6 +88,9 @@ void launch_build_guide(cudaStream_t st, const float* rgb, size_t n_prims, float
 // compacts queue[q] -> queue[q^1]; scratch holds per-block counts (>= ceil(qlen_bound/1024)+1 words)
 void launch_compact(cudaStream_t st, const WaveState& ws, int q, uint32_t qlen_bound, uint32_t* scratch);
 void launch_resolve(cudaStream_t st, const FilmView& film, float inv_spp, uint8_t* rgb8, int flip_y);
+// tile-sharded film combine: pack the owned pixels' sums (slot order) / unpack all ranks' slices (per_rank float4 each) into the film
+void launch_film_pack_owned(cudaStream_t st, const FilmView& film, const uint32_t* slot_pixel, uint32_t n_owned, float4* dst);
+void launch_film_unpack_all(cudaStream_t st, const FilmView& film, const float4* gathered, uint32_t per_rank, int world);
 void launch_film_scale(cudaStream_t st, const FilmView& film, float inv_spp, float* linear_rgb);
 void launch_primary_ids(cudaStream_t st, const SceneView& scene, const CameraView& cam, int w, int h, int32_t* prim, float* t);
 void launch_trace_rays(cudaStream_t st, const SceneView& scene, const float* rays, size_t n, float t_min, int32_t* prim, float* t);

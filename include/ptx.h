@@ -185,22 +185,33 @@ typedef struct {
     int32_t shard_rank, shard_world;
     int32_t rr_start_depth;   /* 0 => 3  (depth > 2, integrator.h:207) */
     float rr_cap;             /* 0 => 0.95 */
-    int32_t pipeline;         /* 0 = default (= 3).  3 = persistent path loop: one launch per frame; lanes pull pixels / paths from
-                                     a counter, no path state in memory; with the compat RNG a pixel's samples are split into
-                                     work items handed from lane to lane through the film, so the frame's tail is one small
-                                     chunk, not one pixel (default: 1/2, 1/4, ... 1/32, 1/32 of spp, or eight equal parts with
-                                     the last one halved down to 1/32 when a rank owns few pixels per resident lane and spp >= 512;
-                                     reserved[3] = n > 0: n halving chunks, n < 0: -n equal parts).
-                                 Cross-checks (bit-identical images): 4 = wavefront (raygen / extend / shade / compact kernels),
-                                 1 = fused bounce kernel (one launch per bounce), 2 = path loop with a slot queue (state in
-                                 registers for reserved[1] bounces per launch), 5 = CTA wavefront (paths in shared memory, four
-                                 dense phases per iteration: node visits, triangle tasks, shading, regeneration; identical
-                                 except at exact hit-distance ties; measured slower than 3, kept as an experiment).
-                                 reserved[2] = 1 / 2 / 4 / 7 select other residency builds of 2 and 3 (CTAs per SM); + 16 / + 32 force
-                                 the persistent kernel's triangle loop to two records / one record per round (default: two when the
-                                 scene has more than 1024 triangles; identical images either way) */
-    int32_t reserved[5];
+    int32_t pipeline;         /* 0 = default: 6 when the scene is tiny enough to carry a flat unit list (ptx_scene_stats.flat_units > 0,
+                                     BSDF sampling), else 3.
+                                 3 = persistent path loop over the BVH8: one launch per frame; lanes pull pixels / paths from a counter,
+                                     no path state in memory; with the compat RNG a pixel's samples are split into work items
+                                     handed from lane to lane through the film (see `chunks`).
+                                 6 = the same loop with the tree replaced by one straight-line pass over <= 20 planar units
+                                     (csrc/flat.h); identical hits.
+                                 Cross-checks kept for the parity tests (bit-identical images): 4 = wavefront (raygen / extend / shade /
+                                 compact kernels), 1 = fused bounce kernel, 2 = path loop with a slot queue, 5 = CTA wavefront
+                                 (experiment, slower; identical except at exact hit-distance ties). */
+    int32_t flags;            /* PTX_RENDER_* bits below */
+    int32_t loop_iters;       /* pipeline 2 only: bounces per launch (0 = default) */
+    int32_t ctas_per_sm;      /* pipelines 2 / 3 / 6: resident 256-thread CTAs per SM, 1..4 (0 = chosen from pixels per lane and spp);
+                                 pipeline 3 also: 7 = 7 x 128 threads, + 16 / + 32 force two / one triangle records per loop round */
+    int32_t chunks;           /* compat RNG, pipelines 3 / 5 / 6: work items per pixel.  0 = default (1/2, 1/4, ... 1/32, 1/32 of spp, or
+                                 eight equal parts with the last one halved down to 1/32 when a rank owns few pixels per resident lane
+                                 and spp >= 512); n > 0: n halving chunks; n < 0: -n equal parts.  Images do not depend on it. */
+    int32_t shade_batch;      /* pipeline 3: waiting lanes per warp that trigger a shading round (0 = default 12) */
 } ptx_render_opts;
+
+enum {
+    PTX_RENDER_STAGE_TIMING = 1,   /* fill ptx_render_stats.extend_ms / shade_ms (pipelines 1, 2, 4) */
+    PTX_RENDER_COUNT_WORK = 2,     /* pipeline 4: instrumented extend kernel, fills node_visits / tri_tests */
+    PTX_RENDER_ASYNC = 4           /* pipelines 3 / 6: ptx_render returns without waiting for the GPU (nothing between the render
+                                      and a following ptx_film_combine / resolve synchronises the host); the statistics are
+                                      completed by the next ptx_render_stats_get, ptx_sync or ptx_render on this context */
+};
 
 typedef struct {
     uint64_t segments;        /* Scene::intersect-equivalent calls (path segments) of the last render */
@@ -209,8 +220,8 @@ typedef struct {
     uint64_t kernel_launches; /* kernels launched by the last ptx_render */
     uint64_t compactions;
     float render_ms;          /* CUDA-event time of the last ptx_render on the ctx stream */
-    float extend_ms, shade_ms, other_ms;   /* filled when opts.reserved[0] & 1 (per-stage timing) */
-    uint64_t node_visits, tri_tests;       /* filled when opts.reserved[0] & 2 (instrumented extend) */
+    float extend_ms, shade_ms, other_ms;   /* filled with PTX_RENDER_STAGE_TIMING */
+    uint64_t node_visits, tri_tests;       /* filled with PTX_RENDER_COUNT_WORK */
     uint64_t slot_launches;                /* path loop: sum over launches of the live slots that entered the kernel */
 } ptx_render_stats;
 
@@ -223,6 +234,23 @@ int ptx_shard_sample_range(int spp, int shard_mode, int rank, int world, int32_t
 int ptx_render(ptx_ctx* ctx, const ptx_scene* scene, const ptx_camera* cam, ptx_film* film,
                const ptx_render_opts* opts);
 int ptx_render_stats_get(const ptx_ctx* ctx, ptx_render_stats* out);
+
+/* ---- multi-GPU film combine (no counterpart in the reference, which is single-GPU: SURVEY.md 2.3) -------------------
+ * One process (or thread) per GPU, each with its own ptx_ctx, the scene replicated; every rank renders its share of the frame
+ * (ptx_render_opts.shard_mode / shard_rank / shard_world) and ptx_film_combine exchanges the films over NCCL (NVLink / NVSwitch)
+ * on the context's stream.  Afterwards EVERY rank's film holds the whole frame (resolve / read / write as usual).
+ *   PTX_SHARD_TILES   (compat RNG): a rank packs the pixels it owns, ONE ncclAllGather moves 1/G of the film per rank, a
+ *                     kernel unpacks all slices; the result equals the single-GPU film bit for bit.
+ *   PTX_SHARD_SAMPLES (counter RNG): in-place ncclAllReduce(sum) of the running sums; the sample count becomes the total.
+ * No host synchronisation happens in ptx_film_combine; with PTX_RENDER_ASYNC none happens between render and combine either.
+ * NCCL is loaded at run time (dlopen of $PTX_NCCL_LIB, libnccl.so.2): rank 0 calls ptx_comm_unique_id, ships the 128 bytes to
+ * the other ranks by any means (MPI, a file, torch.distributed ...), then every rank calls ptx_comm_create -- collectively. */
+typedef struct ptx_comm ptx_comm;
+#define PTX_COMM_ID_BYTES 128
+int ptx_comm_unique_id(uint8_t* id_out, size_t bytes);
+int ptx_comm_create(ptx_ctx* ctx, const uint8_t* id, int rank, int world, ptx_comm** out);
+void ptx_comm_destroy(ptx_comm* comm);
+int ptx_film_combine(ptx_film* film, ptx_comm* comm, int shard_mode);
 
 /* ---- queries used by parity tests (spec: pick_primitive_kernel, ui/callbacks.h:22-48) --------- */
 /* pixel-centre primary rays, u=(x+0.5)/w, v=(y+0.5)/h; prim_id in the reference's numbering, -1 = miss */
