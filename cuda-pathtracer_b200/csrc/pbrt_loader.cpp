@@ -18,14 +18,18 @@
 //   * AreaLightSource "diffuse" "rgb L" -> Le;
 //   * the 2 000 000-triangle cap that swaps the scene for a 12-triangle bounding-box proxy (pbrt_loader.h:205-272) is
 //     reproduced only when ptx_load_opts.triangle_cap asks for it (0 = no cap).
-// Not supported (reported as errors rather than silently dropped): plymesh shapes, "blackbody L", spectrum files.
+// `Shape "plymesh"` reads ascii / binary PLY files like the reference's parser does through rply (load_ply below).
+// Not supported (reported as errors rather than silently dropped): "blackbody L", spectrum files.
 // Non-triangle shapes (sphere, ...) are skipped like the reference does (pbrt_loader.h:288-292).
+#include <algorithm>
+#include <cctype>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
+#include <sstream>
 #include <string>
 #include <vector>
 
@@ -157,6 +161,156 @@ struct Param {
     std::vector<std::string> strs;
 };
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// PLY reader for `Shape "plymesh"`: what the reference's parser extracts through rply (ext/pbrtparser/pbrtParser/impl/semantic/
+// Geometry.cpp:25-66 callbacks, :78-207 ply::parse): vertex x / y / z (required), nx / ny / nz (all three or none), the
+// face list `vertex_indices` | `vertex_index`; every value goes through a double and is cast to float / int; a face whose
+// list length is not 3 is an error ("only triangles are supported"); a file without vertices or faces is an error.
+// Formats: ascii, binary_little_endian, binary_big_endian; every scalar type; other elements and properties are skipped.
+// ---------------------------------------------------------------------------------------------------------------
+struct PlyProp {
+    std::string name;
+    int type = 0, count_type = -1;      // count_type >= 0: list property
+};
+struct PlyElem {
+    std::string name;
+    long long count = 0;
+    std::vector<PlyProp> props;
+};
+int ply_type(const std::string& t) {
+    static const char* names[][2] = {{"char", "int8"}, {"uchar", "uint8"}, {"short", "int16"}, {"ushort", "uint16"},
+                                     {"int", "int32"}, {"uint", "uint32"}, {"float", "float32"}, {"double", "float64"}};
+    for (int i = 0; i < 8; i++) if (t == names[i][0] || t == names[i][1]) return i;
+    return -1;
+}
+const int kPlySize[8] = {1, 1, 2, 2, 4, 4, 4, 8};
+
+struct PlyReader {
+    const unsigned char* p; const unsigned char* end;
+    int format = 0;                      // 0 ascii, 1 little endian, 2 big endian
+    bool ok = true;
+    double scalar(int type) {
+        if (format == 0) {
+            while (p < end && isspace(*p)) p++;
+            if (p >= end) { ok = false; return 0.0; }
+            char* e = nullptr;
+            double v = strtod(reinterpret_cast<const char*>(p), &e);      // the buffer is NUL-terminated by load_ply
+            if (e == reinterpret_cast<const char*>(p)) { ok = false; return 0.0; }
+            p = reinterpret_cast<const unsigned char*>(e);
+            return v;
+        }
+        const int n = kPlySize[type];
+        if (end - p < n) { ok = false; return 0.0; }
+        unsigned char b[8];
+        for (int i = 0; i < n; i++) b[i] = format == 1 ? p[i] : p[n - 1 - i];      // to little endian (the host's order)
+        p += n;
+        switch (type) {
+            case 0: { int8_t v; memcpy(&v, b, 1); return v; }
+            case 1: { uint8_t v; memcpy(&v, b, 1); return v; }
+            case 2: { int16_t v; memcpy(&v, b, 2); return v; }
+            case 3: { uint16_t v; memcpy(&v, b, 2); return v; }
+            case 4: { int32_t v; memcpy(&v, b, 4); return v; }
+            case 5: { uint32_t v; memcpy(&v, b, 4); return v; }
+            case 6: { float v; memcpy(&v, b, 4); return v; }
+            default: { double v; memcpy(&v, b, 8); return v; }
+        }
+    }
+};
+
+bool load_ply(const std::string& path, std::vector<vec3>& P, std::vector<vec3>& N, std::vector<int>& idx, std::string& err) {
+    std::vector<unsigned char> buf;
+    {
+        FILE* f = fopen(path.c_str(), "rb");
+        if (!f) { err = "Couldn't open PLY file " + path; return false; }
+        fseek(f, 0, SEEK_END); long sz = ftell(f); fseek(f, 0, SEEK_SET);
+        buf.resize((size_t)std::max(sz, 0l) + 1);
+        size_t got = sz > 0 ? fread(buf.data(), 1, (size_t)sz, f) : 0;
+        fclose(f);
+        buf.resize(got + 1); buf[got] = 0;
+    }
+    const unsigned char* p = buf.data(); const unsigned char* end = buf.data() + buf.size() - 1;
+    auto line = [&](std::string& out) {
+        if (p >= end) return false;
+        const unsigned char* e = p;
+        while (e < end && *e != '\n') e++;
+        out.assign(reinterpret_cast<const char*>(p), e - p);
+        if (!out.empty() && out.back() == '\r') out.pop_back();
+        p = e < end ? e + 1 : end;
+        return true;
+    };
+    std::string ln;
+    if (!line(ln) || ln != "ply") { err = "Unable to read the header of PLY file " + path; return false; }
+    std::vector<PlyElem> elems;
+    int format = -1;
+    bool header_done = false;
+    while (line(ln)) {
+        std::istringstream is(ln);
+        std::string kw; is >> kw;
+        if (kw == "end_header") { header_done = true; break; }
+        if (kw == "format") {
+            std::string f; is >> f;
+            format = f == "ascii" ? 0 : (f == "binary_little_endian" ? 1 : (f == "binary_big_endian" ? 2 : -1));
+        } else if (kw == "element") {
+            PlyElem e; is >> e.name >> e.count;
+            elems.push_back(e);
+        } else if (kw == "property" && !elems.empty()) {
+            PlyProp pr; std::string t; is >> t;
+            if (t == "list") { std::string ct, it; is >> ct >> it >> pr.name; pr.count_type = ply_type(ct); pr.type = ply_type(it); if (pr.count_type < 0) pr.type = -1; }
+            else { pr.type = ply_type(t); is >> pr.name; }
+            if (pr.type < 0) { err = "Unable to read the header of PLY file " + path; return false; }
+            elems.back().props.push_back(pr);
+        }
+    }
+    if (!header_done || format < 0) { err = "Unable to read the header of PLY file " + path; return false; }
+    long long vertex_count = 0, face_count = 0;
+    bool has_pos[3] = {false, false, false}, has_nor[3] = {false, false, false}, has_indices = false;
+    for (const PlyElem& e : elems) {
+        if (e.name == "vertex") {
+            vertex_count = e.count;
+            for (const PlyProp& pr : e.props) {
+                if (pr.name == "x") has_pos[0] = true; else if (pr.name == "y") has_pos[1] = true; else if (pr.name == "z") has_pos[2] = true;
+                else if (pr.name == "nx") has_nor[0] = true; else if (pr.name == "ny") has_nor[1] = true; else if (pr.name == "nz") has_nor[2] = true;
+            }
+            if (!(has_pos[0] && has_pos[1] && has_pos[2])) { err = path + ": Vertex coordinate property not found!"; return false; }
+        } else if (e.name == "face") {
+            face_count = e.count;
+            for (const PlyProp& pr : e.props) if (pr.name == "vertex_index" || pr.name == "vertex_indices") has_indices = true;
+        }
+    }
+    if (vertex_count <= 0 || face_count <= 0) { err = path + ": PLY file is invalid! No face/vertex elements found!"; return false; }
+    const bool has_normals = has_nor[0] && has_nor[1] && has_nor[2];
+    P.assign((size_t)vertex_count, mk3(0.f, 0.f, 0.f));
+    N.assign(has_normals ? (size_t)vertex_count : 0, mk3(0.f, 0.f, 0.f));
+    idx.assign(has_indices ? (size_t)face_count * 3 : 0, 0);
+    PlyReader rd; rd.p = p; rd.end = end; rd.format = format;
+    for (const PlyElem& e : elems) {
+        const bool is_vertex = e.name == "vertex", is_face = e.name == "face";
+        for (long long i = 0; i < e.count; i++)
+            for (const PlyProp& pr : e.props) {
+                if (pr.count_type < 0) {
+                    const double v = rd.scalar(pr.type);
+                    if (is_vertex) {
+                        const float fv = (float)v;
+                        if (pr.name == "x") P[(size_t)i].x = fv; else if (pr.name == "y") P[(size_t)i].y = fv; else if (pr.name == "z") P[(size_t)i].z = fv;
+                        else if (has_normals && pr.name == "nx") N[(size_t)i].x = fv; else if (has_normals && pr.name == "ny") N[(size_t)i].y = fv;
+                        else if (has_normals && pr.name == "nz") N[(size_t)i].z = fv;
+                    }
+                } else {
+                    const long long len = (long long)rd.scalar(pr.count_type);
+                    const bool mine = is_face && (pr.name == "vertex_index" || pr.name == "vertex_indices");
+                    if (mine && len != 3) { err = "Found face with vertex count different from 3, only triangles are supported"; return false; }
+                    if (len < 0 || !rd.ok) { err = path + ": unable to read the contents of PLY file"; return false; }
+                    for (long long k = 0; k < len; k++) {
+                        const double v = rd.scalar(pr.type);
+                        if (mine) idx[(size_t)i * 3 + (size_t)k] = (int)v;
+                    }
+                }
+                if (!rd.ok) { err = path + ": unable to read the contents of PLY file"; return false; }
+            }
+    }
+    return true;
+}
 }  // namespace
 
 namespace {
@@ -291,7 +445,20 @@ struct Parser {
         if (ty.kind != Token::String) return fail("Shape: type string expected");
         std::vector<Param> ps;
         if (!read_params(ps)) return false;
-        if (ty.text == "plymesh") return fail("plymesh shapes are not supported");
+        if (ty.text == "plymesh") {                                     // emitPlyMesh, Geometry.cpp:220-236
+            const Param* F = find(ps, "filename");
+            if (!F || F->strs.empty()) return fail("plymesh without a 'filename'");
+            Mesh m;
+            m.mat = gs.material;
+            if (gs.area_L.size() >= 3) memcpy(m.Le, gs.area_L.data(), 12);
+            std::string perr;
+            if (!load_ply(root_dir + "/" + F->strs[0], m.P, m.N, m.idx, perr)) return fail(perr);      // makeGlobalFileName: basePath + name
+            for (vec3& v : m.P) v = xfm_point(gs.ctm, v);
+            for (vec3& v : m.N) v = xfm_normal(gs.ctm, v);
+            for (int v : m.idx) if (v < 0 || (size_t)v >= m.P.size()) return fail("plymesh index out of range");
+            current_object().meshes.push_back(std::move(m));
+            return true;
+        }
         if (ty.text != "trianglemesh") return true;                     // skipped, like the reference's non-triangle shapes
         const Param* P = find(ps, "P"); const Param* I = find(ps, "indices"); const Param* N = find(ps, "N");
         if (!P || P->nums.size() % 3) return fail("trianglemesh without a valid 'P'");

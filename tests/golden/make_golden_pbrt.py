@@ -7,7 +7,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 exe = os.path.join(ROOT, "oracle", "_ref", "ref_pbrt")
 out = {}
 with tempfile.TemporaryDirectory() as td:
-    for name in ("basic", "materials", "transforms"):
+    for name in ("basic", "materials", "transforms", "plymesh"):
         subprocess.run([exe, "dump", os.path.join(ROOT, "tests", "pbrt", name + ".pbrt"), os.path.join(td, name)], check=True, capture_output=True)
         r = np.fromfile(os.path.join(td, name + ".prims.bin"), np.float32).reshape(-1, 22)
         out[name + "_v"] = r[:, 1:10].copy(); out[name + "_normal"] = r[:, 13:16].copy()

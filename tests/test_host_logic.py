@@ -350,7 +350,7 @@ def test_integrator_core_bit_exact_vs_reference(pkg, emu, gold, tag, w, h, spp, 
     emu.emu_scene_free(s)
 
 
-@pytest.mark.parametrize("name", ["basic", "materials", "transforms"])
+@pytest.mark.parametrize("name", ["basic", "materials", "transforms", "plymesh"])
 def test_pbrt_loader_matches_reference_loadPBRT(pkg, name):
     """tests/golden/pbrt_vectors.npz holds what the reference's loadPBRT (utils/pbrt_loader.h:178-422 + its vendored
     pbrtParser) returns for tests/pbrt/*.pbrt (tests/golden/make_golden_pbrt.py).  Order, vertices, normals, albedo and
@@ -370,9 +370,16 @@ def test_pbrt_loader_extension_and_errors(pkg, tmp_path):
     pr = pkg.parse_scene_file(os.path.join(ROOT, "tests", "pbrt", "materials.pbrt"), mirror_from_mtl=True)
     assert list(np.nonzero(pr["material_type"] == 1)[0]) == [4, 5]            # the two `Material "mirror"` triangles
     bad = tmp_path / "bad.pbrt"
-    bad.write_text('WorldBegin\nShape "plymesh" "string filename" "x.ply"\nWorldEnd\n')
+    bad.write_text('WorldBegin\nShape "plymesh" "string filename" "x.ply"\nWorldEnd\n')       # missing file
     with pytest.raises(pkg.PtxError):
         pkg.parse_scene_file(str(bad))
+    # a PLY file with a quad face: the reference's parser throws "only triangles are supported" and loadPBRT fails
+    quad = os.path.join(ROOT, "tests", "pbrt", "quad_ascii.ply")
+    bad.write_text(f'WorldBegin\nShape "plymesh" "string filename" "../../../../../../../../{quad}"\n'
+                   'Shape "trianglemesh" "point P" [0 0 0 1 0 0 0 1 0] "integer indices" [0 1 2]\nWorldEnd\n')
+    with pytest.raises(pkg.PtxError) as e:
+        pkg.parse_scene_file(str(bad))
+    assert "only triangles are supported" in str(e.value)
     bad.write_text('WorldBegin\nFrobnicate 1 2 3\nWorldEnd\n')
     with pytest.raises(pkg.PtxError):
         pkg.parse_scene_file(str(bad))
