@@ -272,10 +272,12 @@ class Run:
         whole = self.film.linear()
         self.film.reset()
         differing = int((combined != whole).any(-1).sum())
-        rel = float(np.max(np.abs(combined.astype(np.float64) - whole) / np.maximum(np.abs(whole), 1e-3)))
-        ok = differing == 0 if self.shard_mode == pkg.SHARD_TILES else rel <= 1e-5
-        res = {"mode": {1: "tiles: bit-exact", 2: "sample ranges: <= 1e-5 relative"}[self.shard_mode], "pixels_differing": differing,
-               "max_rel_diff": rel, "ok": bool(ok), "rank": self.rank}
+        relerr = np.abs(combined.astype(np.float64) - whole) / np.maximum(np.abs(whole), 1e-3)
+        rel, mean_rel = float(relerr.max()), float(relerr.mean())
+        # sample ranges: the same samples, added with float atomics in another order (and in two partial sums): mean <= 1e-6, worst pixel <= 1e-4
+        ok = differing == 0 if self.shard_mode == pkg.SHARD_TILES else (mean_rel <= 1e-6 and rel <= 1e-4)
+        res = {"mode": {1: "tiles: bit-exact", 2: "sample ranges: mean <= 1e-6, max <= 1e-4 relative (float atomics in another order)"}[self.shard_mode],
+               "pixels_differing": differing, "max_rel_diff": rel, "mean_rel_diff": mean_rel, "ok": bool(ok), "rank": self.rank}
         if self.world > 1:
             flags = self.torch.tensor([0.0 if ok else 1.0], dtype=self.torch.float64, device="cuda")
             self.dist.all_reduce(flags)

@@ -753,6 +753,9 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     if (opts->pipeline == 6 && (!has_flat || guided))
         return fail(c, PTX_ERR_UNSUPPORTED, "pipeline 6 (flat unit list) needs a scene of at most 20 planar units and BSDF sampling");
     const int pipeline = opts->pipeline == 0 ? ((has_flat && !guided) ? 6 : 3) : opts->pipeline;
+#if !defined(PTX_EXPERIMENTAL)
+    if (pipeline == 5) return fail(c, PTX_ERR_UNSUPPORTED, "pipeline 5 (CTA wavefront) is an experiment: build the library with -DPTX_EXPERIMENTAL");
+#endif
     const bool cta_wave = pipeline == 5;                               // CTA wavefront: same items and hand-off as the persistent kernel
     const bool flat = pipeline == 6;
     const bool persist = pipeline == 3 || cta_wave || flat;
@@ -844,7 +847,10 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
                 else per_sm = px_per_lane >= 8.0 ? 4 : 3;
             }
             launch_path_flat(c->stream, rng_mode, c->ws, scene->view, fs, fv, cv, rp, c->prop.multiProcessorCount, per_sm);
-        } else if (cta_wave) launch_path_cta(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->ctas_per_sm);
+        }
+#if defined(PTX_EXPERIMENTAL)
+        else if (cta_wave) launch_path_cta(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->ctas_per_sm);
+#endif
         else launch_path_persist(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, c->prop.multiProcessorCount, opts->ctas_per_sm);
         PTX_CUDA(c, cudaGetLastError());
         st.kernel_launches++;

@@ -684,6 +684,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_flat(WaveState ws, SceneVi
     }
 }
 
+#if defined(PTX_EXPERIMENTAL)   // measured slower than k_path_persist on every scene: not part of the product build
 // ---------------------------------------------------------------------------------------------
 // CTA wavefront (pipeline 5): ONE launch per frame like k_path_persist, but a path is no longer tied to a
 // lane.  A CTA keeps P = BLOCK * PPT paths in SHARED memory (SoA, 4-byte columns) and runs them through four
@@ -1038,6 +1039,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_cta(WaveState ws, SceneVie
     }
 }
 
+#endif  // PTX_EXPERIMENTAL
+
 // ---------------------------------------------------------------------------------------------
 // compact: stable removal of dead slots from the queue.  count -> scan -> scatter -> commit.
 // Each block owns 1024 consecutive queue entries; order is preserved so state accesses stay coalesced.
@@ -1359,6 +1362,7 @@ void launch_path_flat(cudaStream_t st, int rng_mode, const WaveState& ws, const 
         else k_path_flat<1, kBlock, 3><<<g, kBlock, 0, st>>>(ws, scene, fs, film, cam, rp);
     }
 }
+#if defined(PTX_EXPERIMENTAL)
 template <int RNG, int BLOCK, int PPT, int MINB>
 static void launch_cta_variant(cudaStream_t st, const WaveState& ws, const SceneView& scene, const FilmView& film, const CameraView& cam,
                                const RenderParams& rp, int sm_count, unsigned long long items) {
@@ -1383,6 +1387,7 @@ void launch_path_cta(cudaStream_t st, int rng_mode, const WaveState& ws, const S
     else PTX_CTA_LAUNCH(128, 1, 8);
 #undef PTX_CTA_LAUNCH
 }
+#endif  // PTX_EXPERIMENTAL
 void launch_build_guide(cudaStream_t st, const float* rgb, size_t n_prims, float* out) {
     if (!n_prims) return;
     k_build_guide<<<blocks_for(n_prims, kBlock), kBlock, 0, st>>>(rgb, n_prims, out);

@@ -81,8 +81,10 @@ void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, con
 void launch_path_flat(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FlatScene& fs, const FilmView& film,
                       const CameraView& cam, const RenderParams& rp, int sm_count, int per_sm);
 // CTA wavefront (pipeline 5): one launch per frame, paths in shared memory, four dense phases per iteration (kernels.cu)
+#if defined(PTX_EXPERIMENTAL)
 void launch_path_cta(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FilmView& film, const CameraView& cam,
                      const RenderParams& rp, int sm_count, int variant);
+#endif
 // guide records (kGuideFloats floats per primitive, shade.h) from n_prims x 256 x 3 device floats of radiosity
 void launch_build_guide(cudaStream_t st, const float* rgb, size_t n_prims, float* out);
 // compacts queue[q] -> queue[q^1]; scratch holds per-block counts (>= ceil(qlen_bound/1024)+1 words)

@@ -193,8 +193,8 @@ typedef struct {
                                  6 = the same loop with the tree replaced by one straight-line pass over <= 20 planar units
                                      (csrc/flat.h); identical hits.
                                  Cross-checks kept for the parity tests (bit-identical images): 4 = wavefront (raygen / extend / shade /
-                                 compact kernels), 1 = fused bounce kernel, 2 = path loop with a slot queue, 5 = CTA wavefront
-                                 (experiment, slower; identical except at exact hit-distance ties). */
+                                 compact kernels), 1 = fused bounce kernel, 2 = path loop with a slot queue.  5 = CTA wavefront: an experiment
+                                 that measured slower, compiled only with -DPTX_EXPERIMENTAL (PTX_ERR_UNSUPPORTED otherwise). */
     int32_t flags;            /* PTX_RENDER_* bits below */
     int32_t loop_iters;       /* pipeline 2 only: bounces per launch (0 = default) */
     int32_t ctas_per_sm;      /* pipelines 2 / 3 / 6: resident 256-thread CTAs per SM, 1..4 (0 = chosen from pixels per lane and spp);

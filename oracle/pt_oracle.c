@@ -239,7 +239,7 @@ pto_scene* pto_scene_new(const pto_prim* prims, int n) {
     if (n > 0) build_rec(s, 0, n);
     return s;
 }
-void pto_scene_free(pto_scene* s) { if (!s) return; free(s->prims); free(s->nodes); free(s->idx); free(s->guide); free(s); }
+void pto_scene_free(pto_scene* s) { if (!s) return; free(s->prims); free(s->nodes); free(s->idx); free(s->guide); free(s->mirror); free(s); }
 int pto_scene_num_prims(const pto_scene* s) { return s->n_prims; }
 int pto_scene_num_nodes(const pto_scene* s) { return s->n_nodes; }
 const pto_prim* pto_scene_prims(const pto_scene* s) { return s->prims; }
@@ -767,10 +767,18 @@ static v3 integrate_mode(const pto_scene* s, ray_t r, int max_depth, pto_xorwow*
                 weight = fminf(fmaxf(weight, 0.0f), 10.0f);
             }
             beta = V(beta.e[0] * weight, beta.e[1] * weight, beta.e[2] * weight);   /* operator*=(T), vector.h */
-        } else next = sample_cosine_hemisphere(ns, rng);
+        } else if (s->mirror && s->mirror[id]) next = vsub(r.d, vscale(2.0f * vdot(r.d, ns), ns));   /* extension: mirror, no draws */
+        else next = sample_cosine_hemisphere(ns, rng);
         r = make_ray(vadd(h.p, vscale(1e-4f, ns)), next);
     }
     return L;
+}
+
+void pto_scene_set_mirrors(pto_scene* s, const unsigned char* flags) {
+    free(s->mirror); s->mirror = NULL;
+    if (!flags || s->n_prims <= 0) return;
+    s->mirror = (unsigned char*)malloc((size_t)s->n_prims);
+    memcpy(s->mirror, flags, (size_t)s->n_prims);
 }
 
 void pto_render_init(int w, int h, pto_xorwow* rng, int threads) {

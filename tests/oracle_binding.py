@@ -68,7 +68,12 @@ class Oracle:
         for k in ("type", "v", "bsdf", "Le"):
             a[k] = prims[k]
         a["n"] = prims["normal"] if "normal" in prims.dtype.names else prims["n"]
-        return C.c_void_p(self.L.pto_scene_new(_p(a), len(a)))
+        s = C.c_void_p(self.L.pto_scene_new(_p(a), len(a)))
+        if "material_type" in prims.dtype.names and (prims["material_type"] == 1).any():      # extension: mirrors (no reference counterpart)
+            flags = np.ascontiguousarray(prims["material_type"] == 1, np.uint8)
+            self.L.pto_scene_set_mirrors.argtypes = [C.c_void_p, C.c_void_p]
+            self.L.pto_scene_set_mirrors(s, _p(flags))
+        return s
 
     def free(self, s):
         self.L.pto_scene_free(s)

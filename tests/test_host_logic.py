@@ -314,6 +314,23 @@ def test_negative_zero_direction(emu):
     emu.emu_scene_free(s)
 
 
+def test_mirror_extension_core_vs_oracle(pkg, emu, oracle):
+    """Mirrors are an extension (the reference integrator is Lambertian-only): the oracle restates the product's own rule, and the
+    shading core compiled for the host must agree with it bit for bit on C4's geometry (tall box mirror, short box emissive)."""
+    from cuda_pathtracer_b200 import scenegen
+    prims = scenegen.c4_prims(pkg.parse_scene_file(os.path.join(SCENES, "cbox_quads.obj")))
+    w, h, spp, depth = 64, 36, 4, 8
+    osc = oracle.scene_from_prims(prims)
+    olin, _, ostats = oracle.render(osc, w, h, spp, depth)
+    s = emu.emu_scene_from_prims(P(prims), len(prims), 3)
+    v = cam_view(pkg, w, h)
+    lin = np.zeros((h, w, 3), np.float32); seg = C.c_uint64()
+    emu.emu_render(s, C.byref(v), spp, depth, 2023, P(lin), None, C.byref(seg))
+    assert seg.value == ostats[0]
+    assert np.array_equal(bits(lin), bits(olin))
+    emu.emu_scene_free(s); oracle.free(osc)
+
+
 # ---- any-hit end-point rule (traverse.h trace_any) -------------------------------------------------
 @pytest.mark.parametrize("name,cq", [("cbox", 0), ("cbox_quads", 0), ("cbox_quads", 1)])
 def test_occluded_endpoint_rule_matches_reference(pkg, emu, oracle, name, cq):

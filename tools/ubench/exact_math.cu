@@ -60,6 +60,26 @@ __global__ void k_sincos(unsigned long long* c) {
     atomicAdd(c + 0, in); atomicAdd(c + 1, bad);
 }
 
+// EVERY divisor 1 ... 65535 (ptx_film_create accepts any image dimension up to 65535): all 2^23 mantissas of the numerator at three
+// exponents (2^-33: the smallest jitter, 2^0, and 2^15: the largest coordinate range).  The sequence of div_exact_pos is scale-invariant
+// in the numerator (r depends on b only; a r, a - b q and q + r e are IEEE operations on scaled operands, nothing under- or overflows
+// for 2^-40 <= a <= 65536), so a mantissa that divides exactly at one exponent does at every exponent of the domain; the three
+// exponents and the exhaustive all-exponent pass over 35 dimensions below check that claim as well.
+__global__ void k_div_all(unsigned long long* c) {
+    const float b = (float)(blockIdx.y + 1);
+    unsigned long long bad = 0;
+    const uint32_t chunk = (1u << 23) / gridDim.x;
+    for (uint32_t m = blockIdx.x * chunk + threadIdx.x; m < (blockIdx.x + 1) * chunk; m += blockDim.x) {
+        const float a0 = __uint_as_float((94u << 23) | m), a1 = __uint_as_float((127u << 23) | m), a2 = __uint_as_float((142u << 23) | m);
+        bad += !same(div_exact_pos(a0, b), __fdiv_rn(a0, b));
+        bad += !same(div_exact_pos(a1, b), __fdiv_rn(a1, b));
+        bad += !same(div_exact_pos(a2, b), __fdiv_rn(a2, b));
+    }
+    bad = __reduce_add_sync(0xFFFFFFFFu, (unsigned)bad);
+    if ((threadIdx.x & 31) == 0 && bad) atomicAdd(c + 1, bad);
+    if (threadIdx.x == 0 && blockIdx.x == 0) atomicAdd(c + 0, 3ull << 23);
+}
+
 int main() {
     unsigned long long* d; cudaMalloc(&d, 64);
     unsigned long long h[4];
@@ -81,6 +101,10 @@ int main() {
     printf("%-28s in-domain %llu mismatches %llu | out-of-domain %llu mismatches %llu (a: every float in [2^-40, 65536] / below; b: %zu image dimensions)\n",
            "div_exact_pos vs __fdiv_rn", tot, bad, otot, obad, sizeof dims / sizeof dims[0]);
     fails += bad;
+    cudaMemset(d, 0, 64); k_div_all<<<dim3(32, 65535), 256>>>(d); cudaDeviceSynchronize();
+    cudaMemcpy(h, d, 32, cudaMemcpyDeviceToHost);
+    printf("%-28s checks %llu mismatches %llu (EVERY divisor 1 ... 65535 x every numerator mantissa x exponents 2^-33, 2^0, 2^15)\n", "div_exact_pos, all divisors", h[0], h[1]);
+    fails += h[1];
     cudaMemset(d, 0, 64); k_sincos<<<148 * 8, 256>>>(d); cudaDeviceSynchronize();
     cudaMemcpy(h, d, 32, cudaMemcpyDeviceToHost);
     printf("%-28s in-domain %llu mismatches %llu | (every float in [0, 8], both outputs)\n", "sincos_small vs sincosf", h[0], h[1]);
