@@ -29,9 +29,9 @@ WORKLOADS = {
     "c4": ("generated:c4", 3840, 2160, 4096, 8),        # mirror tall box + emissive short box (scenegen.c4_prims)
     # generated on the box (cuda-pathtracer_b200/scenegen.py): two displaced icospheres, 10 485 772 triangles, Cornell enclosure
     "c3": ("generated:c3_level9", 1920, 1080, 256, 8),
-    # generated on the box as a .pbrt file (scenegen.write_c5_pbrt) and loaded through ptx_scene_load: 4883 instances of a
-    # 20 480-triangle mesh = 100 003 978 triangles, 64 emissive quads.  ~35 s per frame on one GPU: not a default.
-    "c5": ("generated:c5", 3840, 2160, 1024, 8),
+    # generated on the box as a .pbrt file (scenegen.write_c5_pbrt) and loaded through ptx_scene_load with keep_instances:
+    # 305 instances of a 327 680-triangle mesh = 99 942 538 triangles, 64 emissive quads.  Not a default.
+    "c5": ("generated:c5", 3840, 2160, 1024, 8),        # 305 instances x 327 680 triangles = 99.9 M, 64 emissive quads; kept TWO-LEVEL
 }
 METRIC = "Mpaths*bounces/s"
 
@@ -165,9 +165,9 @@ def build_scene(pkg, ctx, workload, rank, max_leaf=0):
         base = pkg.parse_scene_file(os.path.join(ROOT, "scenes", "cbox_quads.obj"))
         if scene_name.endswith("c5"):
             pbrt = os.path.join("/tmp", f"c5_rank{rank}.pbrt")
-            scenegen.write_c5_pbrt(pbrt)
-            scene = ctx.load_scene(pbrt, mirror_from_mtl=True)
-            side = 17; room = 4.0 * side                      # camera of the generated file (scenegen.write_c5_pbrt)
+            scenegen.write_c5_pbrt(pbrt, instances=305, level=7)
+            scene = ctx.load_scene(pbrt, mirror_from_mtl=True, keep_instances=True)
+            side = 7; room = 4.0 * side                       # camera of the generated file (scenegen.write_c5_pbrt)
             cam = pkg.look_at_camera((room / 2, room / 2, room * 1.9), (room / 2, room / 2, 0.0), (0.0, 1.0, 0.0), 40.0, w, h)
         elif scene_name.endswith("c4"):
             scene = ctx.scene_from_primitives(scenegen.c4_prims(base), builder=0, max_leaf=max_leaf)

@@ -41,7 +41,7 @@ class Material(C.Structure):
 
 class LoadOpts(C.Structure):
     _fields_ = [("convert_quads", C.c_int32), ("subdivision", C.c_int32), ("triangle_cap", C.c_int64),
-                ("mirror_from_mtl", C.c_int32), ("host_preprocess", C.c_int32)]
+                ("mirror_from_mtl", C.c_int32), ("host_preprocess", C.c_int32), ("keep_instances", C.c_int32), ("reserved", C.c_int32)]
 
 
 class BuildOpts(C.Structure):
@@ -53,6 +53,7 @@ class SceneStats(C.Structure):
                 ("node_bytes", C.c_int64), ("triangle_bytes", C.c_int64), ("shading_bytes", C.c_int64),
                 ("bounds_min", C.c_float * 3), ("bounds_max", C.c_float * 3), ("sah_cost", C.c_float), ("build_ms", C.c_float),
                 ("builder", C.c_int32), ("max_depth", C.c_int32), ("preprocess_ms", C.c_float), ("preprocess_on_device", C.c_int32),
+                ("n_instances", C.c_int32), ("reserved2", C.c_int32), ("stored_triangles", C.c_int64),
                 ("flat_units", C.c_int32), ("reserved", C.c_int32)]
 
 
@@ -247,8 +248,8 @@ class Context:
         return {"sm_count": sm.value, "cc": (ma.value, mi.value), "total_mem": mem.value}
 
     # -- scenes -------------------------------------------------------------------------------
-    def load_scene(self, path, convert_quads=False, subdivision=0, mirror_from_mtl=False, host_preprocess=False):
-        opts = LoadOpts(int(convert_quads), int(subdivision), 0, int(mirror_from_mtl), int(host_preprocess))
+    def load_scene(self, path, convert_quads=False, subdivision=0, mirror_from_mtl=False, host_preprocess=False, keep_instances=False):
+        opts = LoadOpts(int(convert_quads), int(subdivision), 0, int(mirror_from_mtl), int(host_preprocess), int(keep_instances), 0)
         h = C.c_void_p()
         _check(lib().ptx_scene_load(self._h, os.fspath(path).encode(), C.byref(opts), C.byref(h)), self._h)
         return Scene(self, h)

@@ -60,6 +60,7 @@ struct ptx_scene {
     SceneView view{};
     ptx_scene_stats stats{};
     float* d_guide = nullptr;                    // grid-guided sampling: kGuideFloats floats per primitive (shade.h)
+    InstanceRec* d_inst = nullptr;               // two-level scenes (traverse_inst.h)
     uint32_t* d_quad_bits = nullptr;             // one bit per primitive: Quad (any-hit end-point rule, traverse.h trace_any)
     FlatHost flat;                               // tiny scenes: the planar-unit list of flat.h (empty when the scene does not qualify)
     f32x4* d_flat_recs = nullptr;
@@ -381,6 +382,125 @@ int scene_from_base_gpu(ptx_ctx* c, const std::vector<ptx_primitive>& base, bool
     return rc;
 }
 
+// 3 x 4 affine inverse in double precision (columns vx, vy, vz, translation)
+bool invert_affine(const float* m, float* inv) {
+    const double a = m[0], b = m[3], c = m[6], d = m[1], e = m[4], f = m[7], g = m[2], h = m[5], i = m[8];
+    const double det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
+    if (!(std::fabs(det) > 1e-30)) return false;
+    const double r[9] = {(e * i - f * h) / det, (c * h - b * i) / det, (b * f - c * e) / det,
+                         (f * g - d * i) / det, (a * i - c * g) / det, (c * d - a * f) / det,
+                         (d * h - e * g) / det, (b * g - a * h) / det, (a * e - b * d) / det};      // row-major inverse of the linear part
+    // store as columns: inv[0..2] = first column = (r[0], r[3], r[6]) ...
+    for (int col = 0; col < 3; col++) for (int row = 0; row < 3; row++) inv[3 * col + row] = (float)r[3 * row + col];
+    for (int row = 0; row < 3; row++) inv[9 + row] = (float)(-(r[3 * row + 0] * m[9] + r[3 * row + 1] * m[10] + r[3 * row + 2] * m[11]));
+    return true;
+}
+
+// Two-level scene: one BLAS per object (the world's own shapes are object 0 under the identity), a TLAS over the instances' world
+// boxes, all in ONE node array and ONE triangle array (TLAS first).  Every tree comes from the device builder; the TLAS is built
+// from one placeholder triangle per instance whose bounding box is the instance's box and whose prim id is the instance index.
+int scene_from_instanced(ptx_ctx* c, InstancedScene& is, ptx_scene** out) {
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    ptx_scene* s = new ptx_scene();
+    s->ctx = c;
+    auto bail = [&](int rc) { ptx_scene_destroy(s); return rc; };
+    // objects: 0 = world shapes (may be empty), then the instanced objects; one global material table / shading array
+    std::vector<size_t> obj_first;           // first object-primitive of every object in the concatenated list
+    std::vector<ptx_primitive> all;
+    const bool has_world = !is.world.empty();
+    if (has_world) { obj_first.push_back(0); all.insert(all.end(), is.world.begin(), is.world.end()); }
+    for (auto& o : is.objects) { obj_first.push_back(all.size()); all.insert(all.end(), o.begin(), o.end()); o.clear(); o.shrink_to_fit(); }
+    obj_first.push_back(all.size());
+    const size_t n_obj = obj_first.size() - 1;
+    pack_primitives(all.data(), all.size(), s->packed);
+    all.clear(); all.shrink_to_fit();
+    if (s->packed.tris.size() > 0x7FFFFFF0ull) return bail(fail(c, PTX_ERR_INVALID, "scene too large"));
+    cudaError_t e = cudaMalloc(&s->d_prim_shade, std::max<size_t>(s->packed.prim_shade.size(), 1) * sizeof(f32x4));
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_materials, std::max<size_t>(s->packed.materials.size(), 2) * sizeof(f32x4));
+    if (e == cudaSuccess) e = cudaMemcpy(s->d_prim_shade, s->packed.prim_shade.data(), s->packed.prim_shade.size() * sizeof(f32x4), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(s->d_materials, s->packed.materials.data(), s->packed.materials.size() * sizeof(f32x4), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return bail(cuda_fail(c, e, "instanced scene upload"));
+    PTX_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    // BLAS per object (pbrt scenes hold triangles only: one record per primitive, so tris[k].prim_id == k)
+    std::vector<GpuBvhResult> blas(n_obj);
+    auto free_blas = [&]() { for (auto& b : blas) { cudaFree(b.d_nodes); cudaFree(b.d_tris); b.d_nodes = nullptr; b.d_tris = nullptr; } };
+    int max_blas_depth = 0;
+    for (size_t k = 0; k < n_obj; k++) {
+        const size_t first = obj_first[k], n = obj_first[k + 1] - first;
+        std::vector<TriIn> local(s->packed.tris.begin() + (ptrdiff_t)first, s->packed.tris.begin() + (ptrdiff_t)(first + n));
+        for (auto& t : local) t.prim_id -= (uint32_t)first;             // index WITHIN the object
+        std::string berr;
+        e = build_bvh8_gpu(c->stream, local.data(), n, 3, kTraversalStack, blas[k], berr);
+        if (e != cudaSuccess) { free_blas(); return bail(fail(c, PTX_ERR_CUDA, "GPU BVH build (object) failed: " + berr)); }
+        max_blas_depth = std::max(max_blas_depth, blas[k].max_depth);
+    }
+    // instances: the world's own shapes first (identity), then the file's, in flattening order
+    std::vector<InstanceRec> recs;
+    std::vector<TriIn> boxes;
+    uint32_t prim_base = 0;
+    auto add_instance = [&](size_t obj, const float* m) -> bool {
+        InstanceRec r; memset(&r, 0, sizeof r);
+        memcpy(r.m, m, sizeof r.m);
+        if (!invert_affine(m, r.inv)) return false;
+        r.root = (uint32_t)obj;                                         // patched to the node offset below
+        r.prim_base = prim_base; r.shade_base = (uint32_t)obj_first[obj];
+        prim_base += (uint32_t)(obj_first[obj + 1] - obj_first[obj]);
+        aabb wb = aabb_empty();
+        const aabb& ob = blas[obj].bounds;
+        for (int k = 0; k < 8; k++) aabb_grow(wb, xfm_pt(m, mk3((k & 1) ? ob.hi.x : ob.lo.x, (k & 2) ? ob.hi.y : ob.lo.y, (k & 4) ? ob.hi.z : ob.lo.z)));
+        const vec3 ext = wb.hi - wb.lo;                                 // the corners were transformed in float: pad by a few ulps of the box
+        const float pad = 1e-5f * std::max(std::max(ext.x, ext.y), std::max(ext.z, 1e-3f)) + 1e-6f * std::max(std::max(std::fabs(wb.hi.x), std::fabs(wb.lo.x)), std::max(std::max(std::fabs(wb.hi.y), std::fabs(wb.lo.y)), std::max(std::fabs(wb.hi.z), std::fabs(wb.lo.z))));
+        TriIn t;
+        st3(t.v0, wb.lo - mk3(pad, pad, pad)); st3(t.v1, wb.hi + mk3(pad, pad, pad)); st3(t.v2, 0.5f * (wb.lo + wb.hi));
+        t.prim_id = (uint32_t)recs.size();
+        boxes.push_back(t); recs.push_back(r);
+        return true;
+    };
+    const float ident[12] = {1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0};
+    bool ok_inst = true;
+    if (has_world) ok_inst = add_instance(0, ident);
+    for (const auto& in : is.instances) if (ok_inst) ok_inst = add_instance((size_t)in.object + (has_world ? 1 : 0), in.m);
+    if (!ok_inst) { free_blas(); return bail(fail(c, PTX_ERR_INVALID, "an instance transform is singular")); }
+    GpuBvhResult tlas; std::string terr;
+    e = build_bvh8_gpu(c->stream, boxes.data(), boxes.size(), 1, kTraversalStack, tlas, terr);
+    if (e != cudaSuccess) { free_blas(); cudaFree(tlas.d_nodes); cudaFree(tlas.d_tris); return bail(fail(c, PTX_ERR_CUDA, "GPU BVH build (TLAS) failed: " + terr)); }
+    if (tlas.max_depth + 1 + max_blas_depth > kTraversalStack) { free_blas(); cudaFree(tlas.d_nodes); cudaFree(tlas.d_tris); return bail(fail(c, PTX_ERR_INVALID, "two-level tree deeper than the traversal stack")); }
+    // one node array, one triangle array: TLAS first, then every BLAS with its bases shifted
+    size_t n_nodes = tlas.n_nodes, n_tris = tlas.n_tris;
+    std::vector<uint32_t> node_off(n_obj), tri_off(n_obj);
+    for (size_t k = 0; k < n_obj; k++) { node_off[k] = (uint32_t)n_nodes; tri_off[k] = (uint32_t)n_tris; n_nodes += blas[k].n_nodes; n_tris += blas[k].n_tris; }
+    e = cudaMalloc(&s->d_nodes, n_nodes * kNodeQuads * sizeof(u32x4));
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_tris, std::max<size_t>(n_tris, 1) * kTriQuads * sizeof(f32x4));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(s->d_nodes, tlas.d_nodes, (size_t)tlas.n_nodes * kNodeQuads * sizeof(u32x4), cudaMemcpyDeviceToDevice, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(s->d_tris, tlas.d_tris, (size_t)tlas.n_tris * kTriQuads * sizeof(f32x4), cudaMemcpyDeviceToDevice, c->stream);
+    for (size_t k = 0; k < n_obj && e == cudaSuccess; k++) {
+        e = cudaMemcpyAsync(s->d_nodes + (size_t)node_off[k] * kNodeQuads, blas[k].d_nodes, (size_t)blas[k].n_nodes * kNodeQuads * sizeof(u32x4), cudaMemcpyDeviceToDevice, c->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(s->d_tris + (size_t)tri_off[k] * kTriQuads, blas[k].d_tris, (size_t)blas[k].n_tris * kTriQuads * sizeof(f32x4), cudaMemcpyDeviceToDevice, c->stream);
+        if (e == cudaSuccess) { launch_offset_nodes(c->stream, s->d_nodes + (size_t)node_off[k] * kNodeQuads, blas[k].n_nodes, node_off[k], tri_off[k]); e = cudaGetLastError(); }
+    }
+    for (auto& r : recs) r.root = node_off[r.root];
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_inst, recs.size() * sizeof(InstanceRec));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(s->d_inst, recs.data(), recs.size() * sizeof(InstanceRec), cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(c->ev1, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    free_blas(); cudaFree(tlas.d_nodes); cudaFree(tlas.d_tris);
+    if (e != cudaSuccess) return bail(cuda_fail(c, e, "instanced scene assembly"));
+    float ms = 0.f; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    s->view.nodes = s->d_nodes; s->view.tris = s->d_tris; s->view.prim_shade = s->d_prim_shade; s->view.materials = s->d_materials;
+    s->view.n_nodes = (uint32_t)n_nodes; s->view.n_tris = (uint32_t)n_tris;
+    s->view.n_prims = prim_base; s->view.n_mats = (uint32_t)(s->packed.materials.size() / 2);
+    s->view.inst = s->d_inst; s->view.n_inst = (uint32_t)recs.size();
+    s->stats.n_primitives = (int64_t)prim_base; s->stats.n_triangles = (int64_t)prim_base;       // what the flattened scene would hold
+    s->stats.n_nodes = (int64_t)n_nodes; s->stats.n_materials = s->view.n_mats;
+    s->stats.node_bytes = (int64_t)(n_nodes * kNodeQuads * sizeof(u32x4)); s->stats.triangle_bytes = (int64_t)(n_tris * kTriQuads * sizeof(f32x4));
+    s->stats.shading_bytes = (int64_t)((s->packed.prim_shade.size() + s->packed.materials.size()) * sizeof(f32x4) + recs.size() * sizeof(InstanceRec));
+    s->stats.sah_cost = tlas.sah_cost; s->stats.max_depth = tlas.max_depth + 1 + max_blas_depth; s->stats.builder = 0; s->stats.build_ms = ms;
+    s->stats.n_instances = (int32_t)recs.size(); s->stats.stored_triangles = (int64_t)s->packed.tris.size();
+    st3(s->stats.bounds_min, tlas.bounds.lo); st3(s->stats.bounds_max, tlas.bounds.hi);
+    *out = s;
+    return PTX_OK;
+}
+
 bool has_suffix(const std::string& s, const char* suf) {
     size_t n = strlen(suf);
     if (s.size() < n) return false;
@@ -439,6 +559,12 @@ int ptx_scene_from_triangles(ptx_ctx* c, const float* v, const float* normals, c
 int ptx_scene_load(ptx_ctx* c, const char* path, const ptx_load_opts* opts, ptx_scene** out) {
     if (!c || !path || !out) return fail(c, PTX_ERR_INVALID, "ptx_scene_load: NULL argument");
     std::vector<ptx_primitive> prims; std::string err;
+    if (opts && opts->keep_instances && has_suffix(path, ".pbrt") && !opts->convert_quads && opts->subdivision <= 0 && opts->triangle_cap <= 0) {
+        InstancedScene is;
+        if (load_pbrt_instanced(path, opts->mirror_from_mtl != 0, is, err)) return scene_from_instanced(c, is, out);
+        if (!err.empty()) return fail(c, PTX_ERR_IO, err);
+        // no instances / nested instancing: fall through to the flattened load
+    }
     const bool gpu_geometry = opts && (opts->convert_quads || opts->subdivision > 0) && !opts->host_preprocess;
     ptx_load_opts base_opts{};
     if (opts) base_opts = *opts;
@@ -451,6 +577,7 @@ int ptx_scene_load(ptx_ctx* c, const char* path, const ptx_load_opts* opts, ptx_
 
 int ptx_scene_build_accel(ptx_scene* s, const ptx_build_opts* opts) {
     if (!s) return fail(nullptr, PTX_ERR_INVALID, "ptx_scene_build_accel: scene is NULL");
+    if (s->view.inst) return fail(s->ctx, PTX_ERR_UNSUPPORTED, "ptx_scene_build_accel: a two-level scene is built once at load time");
     return build_accel(s, opts);
 }
 
@@ -472,7 +599,7 @@ void ptx_scene_destroy(ptx_scene* s) {
     cudaSetDevice(s->ctx->device);
     cudaStreamSynchronize(s->ctx->stream);
     free_accel(s);
-    cudaFree(s->d_prim_shade); cudaFree(s->d_materials); cudaFree(s->d_guide); cudaFree(s->d_quad_bits);
+    cudaFree(s->d_prim_shade); cudaFree(s->d_materials); cudaFree(s->d_guide); cudaFree(s->d_quad_bits); cudaFree(s->d_inst);
     delete s;
 }
 
@@ -756,6 +883,8 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
 #if !defined(PTX_EXPERIMENTAL)
     if (pipeline == 5) return fail(c, PTX_ERR_UNSUPPORTED, "pipeline 5 (CTA wavefront) is an experiment: build the library with -DPTX_EXPERIMENTAL");
 #endif
+    if (scene->view.inst && (pipeline != 3 || guided))
+        return fail(c, PTX_ERR_UNSUPPORTED, "two-level (instanced) scenes render with the persistent kernel and BSDF sampling only (pipeline 0 / 3)");
     const bool cta_wave = pipeline == 5;                               // CTA wavefront: same items and hand-off as the persistent kernel
     const bool flat = pipeline == 6;
     const bool persist = pipeline == 3 || cta_wave || flat;
@@ -1019,6 +1148,7 @@ int ptx_trace_rays(ptx_ctx* c, const ptx_scene* scene, const float* rays_host, s
 int ptx_trace_rays_noalloc(ptx_ctx* c, const ptx_scene* scene, const float* rays_host, size_t n, float t_min, int32_t* prim_id_host, float* t_host) {
     if (!c || !scene || (n && (!rays_host || !prim_id_host || !t_host))) return fail(c, PTX_ERR_INVALID, "ptx_trace_rays_noalloc: bad argument");
     if (scene->ctx != c) return fail(c, PTX_ERR_INVALID, "ptx_trace_rays_noalloc: the scene belongs to another context");
+    if (scene->view.inst) return fail(c, PTX_ERR_UNSUPPORTED, "ptx_trace_rays_noalloc: not implemented for two-level (instanced) scenes");
     if (n > (size_t)PTX_NOALLOC_MAX_RAYS)
         return fail(c, PTX_ERR_INVALID, "ptx_trace_rays_noalloc: at most PTX_NOALLOC_MAX_RAYS (65536) rays per call; split the batch or use ptx_trace_rays");
     if (!scene->view.nodes) return fail(c, PTX_ERR_INVALID, "ptx_trace_rays_noalloc: the scene has no acceleration structure");
@@ -1042,6 +1172,7 @@ int ptx_ctx_flush_l2(ptx_ctx* c) {
 int ptx_trace_occluded(ptx_ctx* c, const ptx_scene* scene, const float* segs_host, size_t n, uint8_t* occluded_host) {
     if (!c || !scene || (n && (!segs_host || !occluded_host))) return fail(c, PTX_ERR_INVALID, "ptx_trace_occluded: bad argument");
     if (!scene->view.nodes) return fail(c, PTX_ERR_INVALID, "ptx_trace_occluded: the scene has no acceleration structure (a rebuild failed)");
+    if (scene->view.inst) return fail(c, PTX_ERR_UNSUPPORTED, "ptx_trace_occluded: not implemented for two-level (instanced) scenes");
     if (!n) return PTX_OK;
     PTX_CUDA(c, cudaSetDevice(c->device));
     float* d_segs = nullptr; uint8_t* d_out = nullptr;
@@ -1061,6 +1192,7 @@ int ptx_render_visibility(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* 
     if (!c || !scene || !cam || !film || !rgb8_host || spp <= 0) return fail(c, PTX_ERR_INVALID, "ptx_render_visibility: bad argument");
     if (scene->ctx != c || film->ctx != c) return fail(c, PTX_ERR_INVALID, "ptx_render_visibility: scene/film belong to another context");
     if (!scene->view.nodes) return fail(c, PTX_ERR_INVALID, "ptx_render_visibility: the scene has no acceleration structure (a rebuild failed)");
+    if (scene->view.inst) return fail(c, PTX_ERR_UNSUPPORTED, "ptx_render_visibility: not implemented for two-level (instanced) scenes");
     PTX_CUDA(c, cudaSetDevice(c->device));
     const size_t npix = (size_t)film->w * film->h, nprim = scene->view.n_prims;
     float* d_rad = nullptr; uint8_t* d_img = nullptr;

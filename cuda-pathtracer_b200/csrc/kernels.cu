@@ -3,7 +3,9 @@
 #include "kernels.cuh"
 
 #include <mutex>
+#include <type_traits>
 #include "traverse.h"
+#include "traverse_inst.h"
 #include "flat.h"
 
 namespace ptx {
@@ -426,7 +428,8 @@ __global__ void __launch_bounds__(kBlock) k_build_guide(const float* __restrict_
 // ends (ncu r1h: lane efficiency 0.53 in the second launch of a 128-spp frame).  Lanes only idle in the
 // tail of the frame, when the counter has run dry.
 // ---------------------------------------------------------------------------------------------
-template <int RNG, int BLOCK, int MINB, bool GUIDED = false, bool PAIR = false>
+// INST: the scene is two-level (traverse_inst.h): the cursor is an InstTraversal, normal and material of a hit are resolved per instance.
+template <int RNG, int BLOCK, int MINB, bool GUIDED = false, bool PAIR = false, bool INST = false>
 __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, SceneView scene, FilmView film, CameraView cam, RenderParams rp) {
     constexpr unsigned kFull = 0xFFFFFFFFu;
     const int lane = (int)(threadIdx.x & 31);
@@ -446,9 +449,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
     float fx = 0.f, fy = 0.f;
     bool alive = false, pending = false, dry = rp.spp <= 0;
     bool waiting = false;                               // the lane's ray is through, its result not shaded yet
-    Traversal tr;
+    typename std::conditional<INST, InstTraversal, Traversal>::type tr;
     TravStack<24> stk;
-    tr.begin(pv.d, FLT_MAX);
+    auto restart = [&]() { if constexpr (INST) tr.begin(pv.o, pv.d, FLT_MAX); else tr.begin(pv.d, FLT_MAX); };
+    restart();
     for (;;) {
         // ---- fetch: every lane without work asks for an item; one atomic per warp
         const bool want = !alive && !pending && !dry;
@@ -472,7 +476,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
                         float ju = pr.next(), jv = pr.next();
                         start_path_xy(cam, (float)(int)(pixel % (uint32_t)cam.width), (float)(int)(pixel / (uint32_t)cam.width), ju, jv, pv);
                         L = v3(0.f, 0.f, 0.f);
-                        tr.begin(pv.d, FLT_MAX);
+                        restart();
                         alive = true;
                     }
                 } else dry = true;
@@ -499,13 +503,16 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
                 float ju = xr.next(), jv = xr.next();
                 start_path_xy(cam, fx, fy, ju, jv, pv);
                 L = v3(0.f, 0.f, 0.f);
-                tr.begin(pv.d, FLT_MAX);
+                restart();
                 pending = false; alive = true;
             }
         }
         if (!__any_sync(kFull, alive || pending)) break;
         // ---- extend: one wide-node visit (+ its triangles) per lane
-        if (alive && !waiting) waiting = tr.template step<false, 24, PAIR>(scene, stk, pv.o, pv.d, 1e-4f, nullptr);
+        if (alive && !waiting) {
+            if constexpr (INST) waiting = tr.template step<24>(scene, stk, pv.o, pv.d, 1e-4f);
+            else waiting = tr.template step<false, 24, PAIR>(scene, stk, pv.o, pv.d, 1e-4f, nullptr);
+        }
         __syncwarp();
         // ---- shade in batches: a finished ray waits until enough lanes of the warp are through.  Shading + regeneration
         //      cost about as much as a node visit and run for the whole warp whenever one lane needs them; on a scene with
@@ -518,12 +525,25 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
         waiting = false;
         bool cont = true;
         if (done) {
-            uint32_t prim = tr.bestw;      // kMiss when nothing was hit
             nseg++;
-            if (RNG == 0) cont = shade_bounce<XorwowRng, GUIDED>(scene, rp.shade, pv, prim, tr.closest, xr, L);
-            else {
-                pr.seek(((unsigned long long)sample << 32) | pixel, 1u + (uint32_t)pv.depth, rp.seed);
-                cont = shade_bounce(scene, rp.shade, pv, prim, tr.closest, pr, L);
+            if constexpr (INST) {
+                cont = false;
+                if (tr.tr.best != kMiss) {
+                    uint32_t prim, mat; vec3 n;
+                    resolve_instanced_hit(scene, tr, prim, n, mat);
+                    if (RNG == 0) cont = shade_hit<XorwowRng, false>(scene, rp.shade, pv, prim, n, mat, tr.tr.closest, xr, L);
+                    else {
+                        pr.seek(((unsigned long long)sample << 32) | pixel, 1u + (uint32_t)pv.depth, rp.seed);
+                        cont = shade_hit<PhiloxRng, false>(scene, rp.shade, pv, prim, n, mat, tr.tr.closest, pr, L);
+                    }
+                }
+            } else {
+                uint32_t prim = tr.bestw;      // kMiss when nothing was hit
+                if (RNG == 0) cont = shade_bounce<XorwowRng, GUIDED>(scene, rp.shade, pv, prim, tr.closest, xr, L);
+                else {
+                    pr.seek(((unsigned long long)sample << 32) | pixel, 1u + (uint32_t)pv.depth, rp.seed);
+                    cont = shade_bounce(scene, rp.shade, pv, prim, tr.closest, pr, L);
+                }
             }
         }
         __syncwarp();
@@ -554,7 +574,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_persist(WaveState ws, Scen
             }
         }
         __syncwarp();
-        if (done && cont) tr.begin(pv.d, FLT_MAX);
+        if (done && cont) restart();
     }
     nseg = __reduce_add_sync(kFull, nseg);
     npaths = __reduce_add_sync(kFull, npaths);
@@ -1195,6 +1215,37 @@ __global__ void __launch_bounds__(kBlock) k_trace_rays(SceneView scene, const fl
     tout[i] = tri == kMiss ? -1.0f : t;
 }
 
+// two-level scenes: the same queries through the TLAS / BLAS traversal; ids in the flattened numbering
+__global__ void __launch_bounds__(kBlock) k_primary_ids_inst(SceneView scene, CameraView cam, int w, int h, int32_t* prim, float* tout) {
+    uint32_t p = blockIdx.x * kBlock + threadIdx.x;
+    if (p >= (uint32_t)w * (uint32_t)h) return;
+    int x = (int)(p % (uint32_t)w), y = (int)(p / (uint32_t)w);
+    float u = ((float)x + 0.5f) / (float)w, v = ((float)y + 0.5f) / (float)h;
+    vec3 o, d; camera_ray(cam, u, v, o, d);
+    float t; uint32_t id;
+    uint32_t tri = trace_closest_instanced<24>(scene, o, d, 1e-4f, FLT_MAX, t, id);
+    prim[p] = tri == kMiss ? -1 : (int32_t)id;
+    tout[p] = tri == kMiss ? -1.0f : t;
+}
+__global__ void __launch_bounds__(kBlock) k_trace_rays_inst(SceneView scene, const float* __restrict__ rays, size_t n, float t_min, int32_t* prim, float* tout) {
+    size_t i = (size_t)blockIdx.x * kBlock + threadIdx.x;
+    if (i >= n) return;
+    vec3 o = v3(rays[6 * i], rays[6 * i + 1], rays[6 * i + 2]);
+    vec3 d = unit(v3(rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5]));
+    float t; uint32_t id;
+    uint32_t tri = trace_closest_instanced<24>(scene, o, d, t_min, FLT_MAX, t, id);
+    prim[i] = tri == kMiss ? -1 : (int32_t)id;
+    tout[i] = tri == kMiss ? -1.0f : t;
+}
+// a BLAS copied behind other trees in the shared node / triangle arrays: shift its child and triangle bases
+__global__ void __launch_bounds__(kBlock) k_offset_nodes(u32x4* nodes, uint32_t n_nodes, uint32_t node_off, uint32_t tri_off) {
+    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+    if (i >= n_nodes) return;
+    u32x4 q = nodes[(size_t)i * kNodeQuads + 1];
+    q.x += node_off; q.y += tri_off;
+    nodes[(size_t)i * kNodeQuads + 1] = q;
+}
+
 // Scene::occluded(from, to) (scene.h:132-149): the shadow ray starts 1e-4 along the normalised direction, is normalised
 // again by the Ray ctor, and any hit in [1e-4, dist - 1e-4) occludes.
 __global__ void __launch_bounds__(kBlock) k_occluded(SceneView scene, const float* __restrict__ segs, size_t n, uint8_t* out) {
@@ -1326,6 +1377,12 @@ void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, con
     if (min_blocks == 0 && rng_mode == 0 && (unsigned long long)rp.n_owned < 3ull * (unsigned long long)sm_count * 3ull * kBlock) per_sm = 2;
     const int block = min_blocks == 7 ? 128 : kBlock;
     unsigned g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (items + block - 1) / block);
+    if (scene.inst != nullptr) {           // two-level scene: 2 CTAs per SM (the cursor carries the object-space ray as well)
+        g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * 2, (items + kBlock - 1) / kBlock);
+        if (rng_mode == 0) k_path_persist<0, kBlock, 2, false, false, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+        else k_path_persist<1, kBlock, 2, false, false, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+        return;
+    }
     if (rng_mode == 0 && rp.shade.sampling_mode != 0 && scene.guide != nullptr) {
         // grid / MIS sampling (compat RNG only): the instantiation whose shading honours the per-primitive guide records
         g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * std::min(per_sm, 3), (items + kBlock - 1) / kBlock);
@@ -1422,11 +1479,17 @@ void launch_film_scale(cudaStream_t st, const FilmView& film, float inv_spp, flo
 void launch_primary_ids(cudaStream_t st, const SceneView& scene, const CameraView& cam, int w, int h, int32_t* prim, float* t) {
     size_t n = (size_t)w * h;
     if (!n) return;
-    k_primary_ids<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, cam, w, h, prim, t);
+    if (scene.inst) k_primary_ids_inst<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, cam, w, h, prim, t);
+    else k_primary_ids<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, cam, w, h, prim, t);
 }
 void launch_trace_rays(cudaStream_t st, const SceneView& scene, const float* rays, size_t n, float t_min, int32_t* prim, float* t) {
     if (!n) return;
-    k_trace_rays<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, rays, n, t_min, prim, t);
+    if (scene.inst) k_trace_rays_inst<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, rays, n, t_min, prim, t);
+    else k_trace_rays<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, rays, n, t_min, prim, t);
+}
+void launch_offset_nodes(cudaStream_t st, u32x4* nodes, uint32_t n_nodes, uint32_t node_off, uint32_t tri_off) {
+    if (!n_nodes) return;
+    k_offset_nodes<<<blocks_for(n_nodes, kBlock), kBlock, 0, st>>>(nodes, n_nodes, node_off, tri_off);
 }
 
 // ---------------------------------------------------------------------------------------------

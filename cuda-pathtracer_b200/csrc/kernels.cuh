@@ -20,6 +20,7 @@
 #include "flat.h"
 #include "layout.h"
 #include "shade.h"
+#include "traverse_inst.h"
 
 namespace ptx {
 
@@ -101,6 +102,7 @@ void launch_trace_rays(cudaStream_t st, const SceneView& scene, const float* ray
 constexpr size_t kNoAllocMaxRays = 65536;
 cudaError_t trace_rays_noalloc(cudaStream_t st, int device, const SceneView& scene, const float* rays_host, size_t n, float t_min,
                                int32_t* prim_host, float* t_host);
+void launch_offset_nodes(cudaStream_t st, u32x4* nodes, uint32_t n_nodes, uint32_t node_off, uint32_t tri_off);   // two-level scene assembly
 void launch_occluded(cudaStream_t st, const SceneView& scene, const float* segs, size_t n, uint8_t* out);
 void launch_visibility(cudaStream_t st, const SceneView& scene, const FilmView& film, const CameraView& cam, int spp, const float* radiosity,
                        uint8_t* rgb8);

@@ -37,6 +37,8 @@ constexpr uint32_t kNodeQuads = 5;       // uint4 per node
 constexpr uint32_t kTriQuads = 3;        // float4 per triangle
 constexpr uint32_t kMiss = 0xFFFFFFFFu;
 
+struct InstanceRec;
+
 struct SceneView {
     const u32x4* nodes;
     const f32x4* tris;
@@ -50,6 +52,9 @@ struct SceneView {
     float mis_bsdf_fraction = 0.5f;
     // one bit per reference primitive: 1 = Quad (its halves reject t == t_max in the any-hit query, trace_any); nullptr = no quads
     const uint32_t* quad_bits = nullptr;
+    // two-level scenes (traverse_inst.h): instance records, or nullptr for an ordinary (flattened) scene
+    const struct InstanceRec* inst = nullptr;
+    uint32_t n_inst = 0;
 };
 
 // Camera in the reference's Sensor terms (rendering/sensor.h:92-95): what get_ray needs.

@@ -661,4 +661,41 @@ bool load_pbrt(const std::string& path, bool mirror_ext, long long triangle_cap,
     return true;
 }
 
+bool load_pbrt_instanced(const std::string& path, bool mirror_ext, InstancedScene& out, std::string& err) {
+    Parser ps;
+    ps.mirror_ext = mirror_ext;
+    err.clear();
+    if (!ps.run(path)) { err = "PBRT: " + ps.err; return false; }
+    out.world.clear(); out.objects.clear(); out.instances.clear();
+    const Object& w = *ps.world;
+    if (w.instances.empty()) return false;
+    for (const auto& in : w.instances) if (!in.first->instances.empty()) return false;        // nested instancing: flatten
+    const Affine id = affine_identity();
+    for (const Mesh& m : w.meshes) emit_mesh(m, &id, mirror_ext, out.world);
+    std::map<const Object*, int> index;
+    for (const auto& in : w.instances) {
+        const Object* o = in.first.get();
+        auto it = index.find(o);
+        if (it == index.end()) {
+            it = index.emplace(o, (int)out.objects.size()).first;
+            out.objects.emplace_back();
+            std::vector<ptx_primitive>& prims = out.objects.back();
+            for (const Mesh& m : o->meshes) {
+                const size_t first = prims.size();
+                emit_mesh(m, nullptr, mirror_ext, prims);
+                if (m.N.size() < m.P.size())                                                 // no vertex normals: the instance's
+                    for (size_t k = first; k < prims.size(); k++) prims[k].normal[0] = prims[k].normal[1] = prims[k].normal[2] = NAN;   // geometric normal is computed in world space
+            }
+        }
+        if (out.objects[(size_t)it->second].empty()) continue;                               // an object without triangles contributes nothing
+        InstancedScene::Inst ii;
+        ii.object = it->second;
+        const Affine& a = in.second;
+        st3(ii.m + 0, a.vx); st3(ii.m + 3, a.vy); st3(ii.m + 6, a.vz); st3(ii.m + 9, a.p);
+        out.instances.push_back(ii);
+    }
+    if (out.instances.empty()) return false;
+    return true;
+}
+
 }  // namespace ptx

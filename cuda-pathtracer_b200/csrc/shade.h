@@ -247,47 +247,55 @@ PTX_HD vec3 guided_direction(const float* g, int mode, float mis_bsdf_fraction, 
 // the shading block ran 1.8x per warp iteration at 38 % lane efficiency).
 // GUIDED instantiations also honour sp.sampling_mode (grid / MIS modes when the scene carries guide records); the default
 // instantiation contains no trace of that code.
+// shade_hit: the hit is known to exist; n = the primitive's stored flat normal, mat = its material index.  shade_bounce (below)
+// looks both up for an ordinary scene; the instanced kernel computes them per instance (traverse_inst.h resolve_instanced_hit).
+template <class Rng, bool GUIDED = false>
+PTX_HD bool shade_hit(const SceneView& s, const ShadeParams& sp, PathVertex& pv, uint32_t prim, vec3 n, uint32_t mat, float t, Rng& rng,
+                      vec3& radiance) {
+    bool cont = false;
+    f32x4 m0 = ldq(s.materials + 2 * (size_t)mat), m1 = ldq(s.materials + 2 * (size_t)mat + 1);
+    vec3 Le = mk3(m1.x, m1.y, m1.z);
+    radiance = radiance + pv.beta * Le;                            // both faces emit (integrator.h:204)
+    bool survive = true;
+    if (pv.depth >= sp.rr_start_depth) {                           // integrator.h:207-212
+        float mx = fmaxf(pv.beta.x, fmaxf(pv.beta.y, pv.beta.z));
+        float rr = fminf(mx, sp.rr_cap);
+        survive = !(rng.next() > rr);
+        if (survive) pv.beta = div_scalar(pv.beta, rr);
+    }
+    if (survive) {
+        pv.beta = pv.beta * mk3(m0.x, m0.y, m0.z);
+        if (!(length(pv.beta) < 1e-5f)) {                           // integrator.h:215-218
+            vec3 ns = dot(pv.d, n) < 0 ? n : -n;
+            vec3 next;
+            const float* g = nullptr;
+            if (GUIDED && sp.sampling_mode != 0 && s.guide != nullptr) {        // initGridFromPrimitive + isValid, integrator.h:229-231
+                g = s.guide + (size_t)prim * kGuideFloats;
+                if (f2u(ldf(g + kGuideValid)) == 0u) g = nullptr;
+            }
+            if (f2u(m0.w) == 1u) next = pv.d - (2.0f * dot(pv.d, ns)) * ns;     // mirror extension: no draws consumed
+            else if (GUIDED && g != nullptr) {
+                float weight;
+                next = guided_direction(g, sp.sampling_mode, s.mis_bsdf_fraction, ns, rng, weight);
+                pv.beta = pv.beta * weight;
+            } else { float u = rng.next(); float v = rng.next(); next = cosine_hemisphere(ns, u, v); }
+            vec3 p = pv.o + t * pv.d;                              // triangle.h:90
+            pv.o = p + ns * 1e-4f;
+            pv.d = unit(next);
+            pv.depth++;
+            cont = pv.depth < sp.max_depth;
+        }
+    }
+    return cont;
+}
+
 template <class Rng, bool GUIDED = false>
 PTX_HD bool shade_bounce(const SceneView& s, const ShadeParams& sp, PathVertex& pv, uint32_t prim, float t, Rng& rng,
                          vec3& radiance) {
     bool cont = false;
     if (prim != kMiss) {                                                // miss: no environment light (integrator.h:199-201)
         f32x4 ps = ldq(s.prim_shade + prim);
-        uint32_t mat = f2u(ps.w);
-        f32x4 m0 = ldq(s.materials + 2 * (size_t)mat), m1 = ldq(s.materials + 2 * (size_t)mat + 1);
-        vec3 Le = mk3(m1.x, m1.y, m1.z);
-        radiance = radiance + pv.beta * Le;                            // both faces emit (integrator.h:204)
-        bool survive = true;
-        if (pv.depth >= sp.rr_start_depth) {                           // integrator.h:207-212
-            float mx = fmaxf(pv.beta.x, fmaxf(pv.beta.y, pv.beta.z));
-            float rr = fminf(mx, sp.rr_cap);
-            survive = !(rng.next() > rr);
-            if (survive) pv.beta = div_scalar(pv.beta, rr);
-        }
-        if (survive) {
-            pv.beta = pv.beta * mk3(m0.x, m0.y, m0.z);
-            if (!(length(pv.beta) < 1e-5f)) {                           // integrator.h:215-218
-                vec3 n = mk3(ps.x, ps.y, ps.z);
-                vec3 ns = dot(pv.d, n) < 0 ? n : -n;
-                vec3 next;
-                const float* g = nullptr;
-                if (GUIDED && sp.sampling_mode != 0 && s.guide != nullptr) {        // initGridFromPrimitive + isValid, integrator.h:229-231
-                    g = s.guide + (size_t)prim * kGuideFloats;
-                    if (f2u(ldf(g + kGuideValid)) == 0u) g = nullptr;
-                }
-                if (f2u(m0.w) == 1u) next = pv.d - (2.0f * dot(pv.d, ns)) * ns;     // mirror extension: no draws consumed
-                else if (GUIDED && g != nullptr) {
-                    float weight;
-                    next = guided_direction(g, sp.sampling_mode, s.mis_bsdf_fraction, ns, rng, weight);
-                    pv.beta = pv.beta * weight;
-                } else { float u = rng.next(); float v = rng.next(); next = cosine_hemisphere(ns, u, v); }
-                vec3 p = pv.o + t * pv.d;                              // triangle.h:90
-                pv.o = p + ns * 1e-4f;
-                pv.d = unit(next);
-                pv.depth++;
-                cont = pv.depth < sp.max_depth;
-            }
-        }
+        cont = shade_hit<Rng, GUIDED>(s, sp, pv, prim, mk3(ps.x, ps.y, ps.z), f2u(ps.w), t, rng, radiance);
     }
     return cont;
 }

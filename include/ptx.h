@@ -76,6 +76,12 @@ typedef struct {
     int32_t mirror_from_mtl;  /* extension: MTL `illum 3|5` => mirror with Kr = Ks.  0 keeps reference semantics */
     int32_t host_preprocess;  /* 1 = run convert_quads / subdivision on the host (cross-check); default 0 = CUDA kernels
                                  feeding the device BVH builder (ptx_scene_load only; ptx_parse_scene_file is host-only) */
+    int32_t keep_instances;   /* .pbrt, ptx_scene_load only: 1 = keep ObjectInstance two-level (every object stored once in object
+                                 space, a TLAS over the instances; the ray is transformed at the instance) instead of flattening
+                                 like the reference (pbrt_loader.h:197, 282-344).  Same primitive numbering; hit distances agree
+                                 with the flattened scene to rounding, not bit for bit.  Ignored (flattened) for files without
+                                 instances or with nested instancing, and with convert_quads / subdivision / triangle_cap. */
+    int32_t reserved;
 } ptx_load_opts;
 
 typedef struct {
@@ -98,6 +104,9 @@ typedef struct {
     int32_t max_depth;
     float preprocess_ms;      /* device time of convert-quads / subdivision / packing when they ran on the GPU, else 0 */
     int32_t preprocess_on_device;
+    int32_t n_instances;      /* > 0: two-level scene (keep_instances): instances in the TLAS; n_triangles is then the FLATTENED count */
+    int32_t reserved2;
+    int64_t stored_triangles; /* triangle records actually stored (two-level: every object once) */
     int32_t flat_units;       /* > 0: the scene is tiny enough for the flat unit list (<= 20 planar quads / triangle pairs):
                                  ptx_render's default pipeline then runs without a tree (pipeline 6) */
     int32_t reserved;
