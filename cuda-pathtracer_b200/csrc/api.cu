@@ -464,7 +464,8 @@ int scene_from_instanced(ptx_ctx* c, InstancedScene& is, ptx_scene** out) {
     GpuBvhResult tlas; std::string terr;
     e = build_bvh8_gpu(c->stream, boxes.data(), boxes.size(), 1, kTraversalStack, tlas, terr);
     if (e != cudaSuccess) { free_blas(); cudaFree(tlas.d_nodes); cudaFree(tlas.d_tris); return bail(fail(c, PTX_ERR_CUDA, "GPU BVH build (TLAS) failed: " + terr)); }
-    if (tlas.max_depth + 1 + max_blas_depth > kTraversalStack) { free_blas(); cudaFree(tlas.d_nodes); cudaFree(tlas.d_tris); return bail(fail(c, PTX_ERR_INVALID, "two-level tree deeper than the traversal stack")); }
+    // a TLAS level can park two stack entries: the rest of its group and its inner hits
+    if (2 * tlas.max_depth + 1 + max_blas_depth > kTraversalStack) { free_blas(); cudaFree(tlas.d_nodes); cudaFree(tlas.d_tris); return bail(fail(c, PTX_ERR_INVALID, "two-level tree deeper than the traversal stack")); }
     // one node array, one triangle array: TLAS first, then every BLAS with its bases shifted
     size_t n_nodes = tlas.n_nodes, n_tris = tlas.n_tris;
     std::vector<uint32_t> node_off(n_obj), tri_off(n_obj);

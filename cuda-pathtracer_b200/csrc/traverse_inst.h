@@ -57,6 +57,9 @@ struct InstTraversal {
     PTX_HD bool step(const SceneView& s, TravStack<STACK>& stk, vec3 ow, vec3 dw, float t_min) {
         uint32_t tg_x, tg_y;
         tr.template visit<false>(s, stk, o, d, t_min, tg_x, tg_y, nullptr);
+        // visit() leaves the node's imask in the low byte of ng_y; without a hit inner child the group is exhausted, and below a
+        // value <= 0x00FFFFFF with low bits set means "instance list": clear it
+        if (tr.ng_y <= 0x00FFFFFFu) tr.ng_y = 0u;
         if (inst == kMiss) {
             if (tg_y != 0) {                            // instances hit by this TLAS node: they become the current group
                 if (tr.ng_y > 0x00FFFFFFu) { stk.x[tr.sp] = tr.ng_x; stk.y[tr.sp] = tr.ng_y; tr.sp++; }
