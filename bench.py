@@ -381,7 +381,7 @@ def run_ours(args, w, h, spp, depth):
     sampler.join(timeout=2)
     clocks = sampler.summary()
     st_t = run.step(False, stage_timing=True)          # dominant-kernel time of one more frame (per-launch events; outside the timed regions)
-    check = run.check_against_unsharded() if world > 1 else None
+    check = run.check_against_unsharded() if world > 1 and not args.no_check else None
     roof = roofline_of(run, m, st_t, args, clocks, sm_count) if pipeline in (pkg.PIPELINE_PERSIST, pkg.PIPELINE_FLAT, pkg.PIPELINE_DEFAULT) else None
     run.close()
 
@@ -502,6 +502,7 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override spp (reduced runs are NOT the headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gpu-baseline", action="store_true")
+    ap.add_argument("--no-check", action="store_true", help="N > 1: skip the unsharded re-render that checks the combined film (a whole frame per rank: expensive on c5)")
     ap.add_argument("--no-extra", action="store_true", help="skip the secondary records (extra.philox / extra.c4 / extra.c3) of the default C2 run")
     ap.add_argument("--min-blocks", type=int, default=0, help="experiment: occupancy variant of the path-loop kernels (0 = 3x256 threads/SM, 4 = 4x256, 7 = 7x128)")
     ap.add_argument("--chunks", type=int, default=0, help="experiment: work items per pixel of the persistent kernel, compat RNG (0 = default 6, 1 = none)")
