@@ -62,3 +62,17 @@ def test_async_render_then_sync_render(pkg, ctx):
     assert st2["segments"] == ref2["segments"]
     assert np.array_equal(film.linear(), want)
     film.close(); scene.close()
+
+
+def test_cpp_multi_gpu_example_runs(built, tmp_path):
+    """examples/multi_gpu.cpp (C++ threads + the C ABI only) on as many GPUs as this box has (1 or 2 here): the combined film equals the
+    unsharded one bit for bit, every rank holds the same film, and rank 0 writes the PNG."""
+    import subprocess
+    import torch
+    exe = built.build_multi_gpu_example()
+    n = min(2, torch.cuda.device_count())
+    png = tmp_path / "out.png"
+    r = subprocess.run([exe, os.path.join(SCENES, "cbox_quads.obj"), "160", "90", "16", "8", str(n), str(png)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "IDENTICAL" in r.stdout
+    assert png.exists() and png.stat().st_size > 1000
