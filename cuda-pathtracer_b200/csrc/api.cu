@@ -8,6 +8,8 @@
 #include <dlfcn.h>
 #include <nccl.h>          // types only: the functions are resolved with dlopen (a single-GPU host needs no NCCL)
 
+#include <cub/device/device_radix_sort.cuh>
+
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -49,6 +51,7 @@ struct ptx_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, tev0 = nullptr, tev1 = nullptr;
     std::vector<cudaEvent_t> stage_events;
     ptx_render_stats stats{};
+    uint32_t* d_sort_keys[2] = {nullptr, nullptr}; void* d_sort_tmp = nullptr; size_t sort_capacity = 0, sort_tmp_bytes = 0;   // wavefront queue sorting
     bool stats_pending = false;                 // PTX_RENDER_ASYNC: the counters of the last render are still on their way
 };
 
@@ -146,7 +149,7 @@ void ptx_ctx_destroy(ptx_ctx* c) {
     cudaStreamSynchronize(c->stream);
     cudaFree(c->ws.A); cudaFree(c->ws.B); cudaFree(c->ws.C); cudaFree(c->ws.D); cudaFree(c->ws.E);
     cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]); cudaFree(c->ws.slot_pixel); cudaFree(c->ws.progress); cudaFree(c->ws.counters); cudaFree(c->d_flush);
-    cudaFree(c->d_scratch); cudaFree(c->d_jump);
+    cudaFree(c->d_scratch); cudaFree(c->d_jump); cudaFree(c->d_sort_keys[0]); cudaFree(c->d_sort_keys[1]); cudaFree(c->d_sort_tmp);
     cudaFreeHost(c->h_counters);
     for (auto ev : c->stage_events) cudaEventDestroy(ev);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -1017,9 +1020,29 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
                 if (stage_timing) cudaEventRecord(c->stage_events[3 * i + 2], c->stream);
                 st.kernel_launches++;
             } else {
+                // north_star subsystem 3: reorder the rays before extend / sort the hits by material before shade (opt-in, pipeline 4)
+                auto sort_queue = [&](bool by_material) -> int {
+                    if (qbound > c->sort_capacity) {
+                        PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+                        cudaFree(c->d_sort_keys[0]); cudaFree(c->d_sort_keys[1]); cudaFree(c->d_sort_tmp);
+                        c->d_sort_keys[0] = c->d_sort_keys[1] = nullptr; c->d_sort_tmp = nullptr; c->sort_capacity = 0;
+                        PTX_CUDA(c, cudaMalloc(&c->d_sort_keys[0], (size_t)qbound * 4)); PTX_CUDA(c, cudaMalloc(&c->d_sort_keys[1], (size_t)qbound * 4));
+                        size_t need = 0;
+                        PTX_CUDA(c, cub::DeviceRadixSort::SortPairs(nullptr, need, c->d_sort_keys[0], c->d_sort_keys[1], c->ws.queue[0], c->ws.queue[1], (int)qbound, 0, 31, c->stream));
+                        PTX_CUDA(c, cudaMalloc(&c->d_sort_tmp, need));
+                        c->sort_tmp_bytes = need; c->sort_capacity = qbound;
+                    }
+                    launch_queue_keys(c->stream, c->ws, scene->view, q, qbound, by_material, scene->stats.bounds_min, scene->stats.bounds_max, c->d_sort_keys[0]);
+                    size_t tmp = c->sort_tmp_bytes;
+                    PTX_CUDA(c, cub::DeviceRadixSort::SortPairs(c->d_sort_tmp, tmp, c->d_sort_keys[0], c->d_sort_keys[1], c->ws.queue[q], c->ws.queue[q ^ 1], (int)qbound, 0, 31, c->stream));
+                    q ^= 1; st.kernel_launches += 4;
+                    return PTX_OK;
+                };
+                if (opts->flags & PTX_RENDER_SORT_RAYS) { int src = sort_queue(false); if (src != PTX_OK) return src; }
                 if (stage_timing) cudaEventRecord(c->stage_events[3 * i], c->stream);
                 launch_extend(c->stream, c->ws, scene->view, q, qbound, count_work);
                 if (stage_timing) cudaEventRecord(c->stage_events[3 * i + 1], c->stream);
+                if (opts->flags & PTX_RENDER_SORT_MATERIAL) { int src = sort_queue(true); if (src != PTX_OK) return src; }
                 launch_shade(c->stream, rng_mode, c->ws, scene->view, fv, cv, rp, q, qbound);
                 if (stage_timing) cudaEventRecord(c->stage_events[3 * i + 2], c->stream);
                 st.kernel_launches += 2;

@@ -1062,6 +1062,46 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_cta(WaveState ws, SceneVie
 #endif  // PTX_EXPERIMENTAL
 
 // ---------------------------------------------------------------------------------------------
+// Queue sorting for the wavefront pipeline (north_star subsystem 3: ray reordering + material-sorted shading).
+//   ray key      : 15-bit Morton code of the ray origin's cell (32^3 over the scene bounds) << 3 | direction octant -- rays that start
+//                  in the same region and head the same way visit the same nodes and triangle records (L1 / L2 hits in extend)
+//   material key : material index of the primitive the ray hit (misses after every material) -- lanes of a warp take the same
+//                  branch of shade_bounce (emitter / mirror / diffuse / miss)
+// Entries past the live length and dead slots get the largest keys, so a stable sort keeps them behind the live ones.
+// The order of the queue cannot change an image: a slot's path, RNG stream and (compat) pixel are its own.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t spread5(uint32_t v) {          // 5 bits -> every third bit
+    v = (v | (v << 8)) & 0x0000F00Fu; v = (v | (v << 4)) & 0x000C30C3u; v = (v | (v << 2)) & 0x00249249u;
+    return v;
+}
+__global__ void __launch_bounds__(kBlock) k_queue_keys(WaveState ws, SceneView scene, int q, uint32_t n_bound, int by_material, float3 lo, float3 inv_ext,
+                                                       uint32_t* keys) {
+    uint32_t k = blockIdx.x * kBlock + threadIdx.x;
+    if (k >= n_bound) return;
+    uint32_t qlen = (uint32_t)ws.counters[CTR_QLEN];
+    uint32_t key = 0x7FFFFFFFu;
+    if (k < qlen) {
+        uint32_t slot = ws.queue[q][k];
+        float4 b = ws.B[slot];
+        key = 0x7FFFFFFEu;
+        if (!(__float_as_uint(b.z) & kDeadFlag)) {
+            if (by_material) {
+                uint32_t prim = __float_as_uint(ws.C[slot].w);
+                key = prim == kMiss ? 0x0000FFFFu : (f2u(ldq(scene.prim_shade + prim).w) & 0xFFFFu);
+            } else {
+                float4 a = ws.A[slot];
+                uint32_t cx = (uint32_t)fminf(fmaxf((a.x - lo.x) * inv_ext.x, 0.0f), 31.0f);
+                uint32_t cy = (uint32_t)fminf(fmaxf((a.y - lo.y) * inv_ext.y, 0.0f), 31.0f);
+                uint32_t cz = (uint32_t)fminf(fmaxf((a.z - lo.z) * inv_ext.z, 0.0f), 31.0f);
+                uint32_t oct = (a.w < 0.0f ? 4u : 0u) | (b.x < 0.0f ? 2u : 0u) | (b.y < 0.0f ? 1u : 0u);
+                key = ((spread5(cx) | (spread5(cy) << 1) | (spread5(cz) << 2)) << 3) | oct;
+            }
+        }
+    }
+    keys[k] = key;
+}
+
+// ---------------------------------------------------------------------------------------------
 // compact: stable removal of dead slots from the queue.  count -> scan -> scatter -> commit.
 // Each block owns 1024 consecutive queue entries; order is preserved so state accesses stay coalesced.
 // ---------------------------------------------------------------------------------------------
@@ -1448,6 +1488,13 @@ void launch_path_cta(cudaStream_t st, int rng_mode, const WaveState& ws, const S
 void launch_build_guide(cudaStream_t st, const float* rgb, size_t n_prims, float* out) {
     if (!n_prims) return;
     k_build_guide<<<blocks_for(n_prims, kBlock), kBlock, 0, st>>>(rgb, n_prims, out);
+}
+void launch_queue_keys(cudaStream_t st, const WaveState& ws, const SceneView& scene, int q, uint32_t n_bound, bool by_material, const float lo[3],
+                       const float hi[3], uint32_t* keys) {
+    if (!n_bound) return;
+    float3 l = make_float3(lo[0], lo[1], lo[2]);
+    float3 ie = make_float3(32.0f / fmaxf(hi[0] - lo[0], 1e-20f), 32.0f / fmaxf(hi[1] - lo[1], 1e-20f), 32.0f / fmaxf(hi[2] - lo[2], 1e-20f));
+    k_queue_keys<<<blocks_for(n_bound, kBlock), kBlock, 0, st>>>(ws, scene, q, n_bound, by_material ? 1 : 0, l, ie, keys);
 }
 void launch_compact(cudaStream_t st, const WaveState& ws, int q, uint32_t qlen_bound, uint32_t* scratch) {
     if (!qlen_bound) return;

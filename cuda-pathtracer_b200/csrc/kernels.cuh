@@ -88,6 +88,9 @@ void launch_path_cta(cudaStream_t st, int rng_mode, const WaveState& ws, const S
 #endif
 // guide records (kGuideFloats floats per primitive, shade.h) from n_prims x 256 x 3 device floats of radiosity
 void launch_build_guide(cudaStream_t st, const float* rgb, size_t n_prims, float* out);
+// sort keys of queue[q][0, n_bound): ray keys (origin cell + direction octant) or material keys (after extend); kernels.cu
+void launch_queue_keys(cudaStream_t st, const WaveState& ws, const SceneView& scene, int q, uint32_t n_bound, bool by_material, const float lo[3],
+                       const float hi[3], uint32_t* keys);
 // compacts queue[q] -> queue[q^1]; scratch holds per-block counts (>= ceil(qlen_bound/1024)+1 words)
 void launch_compact(cudaStream_t st, const WaveState& ws, int q, uint32_t qlen_bound, uint32_t* scratch);
 void launch_resolve(cudaStream_t st, const FilmView& film, float inv_spp, uint8_t* rgb8, int flip_y);

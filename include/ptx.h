@@ -217,6 +217,9 @@ typedef struct {
 enum {
     PTX_RENDER_STAGE_TIMING = 1,   /* fill ptx_render_stats.extend_ms / shade_ms (pipelines 1, 2, 4) */
     PTX_RENDER_COUNT_WORK = 2,     /* pipeline 4: instrumented extend kernel, fills node_visits / tri_tests */
+    PTX_RENDER_SORT_RAYS = 8,      /* pipeline 4: sort the queue by (origin cell, direction octant) before every extend (ray reordering) */
+    PTX_RENDER_SORT_MATERIAL = 16, /* pipeline 4: sort the queue by the material of the hit before every shade (material-sorted shading).
+                                      Neither changes an image (a slot's path, stream and pixel are its own); measured in DESIGN.md */
     PTX_RENDER_ASYNC = 4           /* pipelines 3 / 6: ptx_render returns without waiting for the GPU (nothing between the render
                                       and a following ptx_film_combine / resolve synchronises the host); the statistics are
                                       completed by the next ptx_render_stats_get, ptx_sync or ptx_render on this context */
