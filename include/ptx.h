@@ -256,7 +256,9 @@ int ptx_render_stats_get(const ptx_ctx* ctx, ptx_render_stats* out);
  *   PTX_SHARD_SAMPLES (counter RNG): in-place ncclAllReduce(sum) of the running sums; the sample count becomes the total.
  * No host synchronisation happens in ptx_film_combine; with PTX_RENDER_ASYNC none happens between render and combine either.
  * NCCL is loaded at run time (dlopen of $PTX_NCCL_LIB, libnccl.so.2): rank 0 calls ptx_comm_unique_id, ships the 128 bytes to
- * the other ranks by any means (MPI, a file, torch.distributed ...), then every rank calls ptx_comm_create -- collectively. */
+ * the other ranks by any means (MPI, a file, torch.distributed ...), then every rank calls ptx_comm_create -- collectively.
+ * A process that also loads another copy of NCCL under the same soname (PyTorch bundles its own libnccl.so.2) must load THAT first
+ * (import torch before the first ptx_comm_* call) or point PTX_NCCL_LIB at it: the dynamic loader keeps one libnccl.so.2 per process. */
 typedef struct ptx_comm ptx_comm;
 #define PTX_COMM_ID_BYTES 128
 int ptx_comm_unique_id(uint8_t* id_out, size_t bytes);
