@@ -86,3 +86,23 @@ def test_shard_arithmetic_single_process(pkg):
             assert f == tot
             tot += c
         assert tot == spp
+
+
+@pytest.mark.parametrize("w,h,world", [(50, 23, 2), (64, 36, 3), (333, 77, 8), (1920, 1080, 8), (17, 4, 5)])
+def test_combine_slice_layout_is_the_inverse_of_the_owner_map(pkg, w, h, world):
+    """ptx_film_combine, tiles: rank r packs its owned pixels in slot order into slice r of the gather buffer (per_rank = what rank 0
+    owns, the largest share), and k_film_unpack_all reads pixel p back from (owner, local slot) = (band % world, (band / world) * band_px
+    + p - band * band_px) with bands of 4 rows.  That formula must invert ptx_shard_owned_pixels for every rank -- checked here on
+    the host, the kernel itself runs in tests/test_gpu_combine.py and in every N > 1 bench run."""
+    import numpy as np
+    band_px = 4 * w
+    per_rank = len(pkg.shard_owned_pixels(w, h, pkg.SHARD_TILES, 0, world))
+    gathered = np.full(per_rank * world, -1, np.int64)
+    for r in range(world):
+        owned = pkg.shard_owned_pixels(w, h, pkg.SHARD_TILES, r, world)
+        assert len(owned) <= per_rank
+        gathered[r * per_rank: r * per_rank + len(owned)] = owned          # what k_film_pack_owned writes: slot i <- pixel owned[i]
+    p = np.arange(w * h)
+    band = p // band_px
+    src = (band % world) * per_rank + (band // world) * band_px + (p - band * band_px)
+    assert np.array_equal(gathered[src], p)
