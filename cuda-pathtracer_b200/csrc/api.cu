@@ -48,6 +48,9 @@ struct ptx_ctx {
     uint32_t pixmap_capacity = 0, progress_capacity = 0;   // entries allocated in ws.slot_pixel / ws.progress
     unsigned long long* h_counters = nullptr;   // pinned
     int slot_key[5] = {-1, -1, -1, -1, -1};     // (w, h, shard_mode, rank, world) the slot map was built for
+    // ws.slot_pixel points at d_slot_base (canonical order: what ptx_film_combine packs by) or at d_slot_sorted (cost order)
+    uint32_t* d_slot_base = nullptr; uint32_t* d_slot_sorted = nullptr; uint32_t* d_cost_keys[2] = {nullptr, nullptr}; uint32_t* d_cost_vals = nullptr;
+    void* d_cost_tmp = nullptr; size_t cost_tmp_bytes = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, tev0 = nullptr, tev1 = nullptr;
     std::vector<cudaEvent_t> stage_events;
     ptx_render_stats stats{};
@@ -148,7 +151,8 @@ void ptx_ctx_destroy(ptx_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     cudaFree(c->ws.A); cudaFree(c->ws.B); cudaFree(c->ws.C); cudaFree(c->ws.D); cudaFree(c->ws.E);
-    cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]); cudaFree(c->ws.slot_pixel); cudaFree(c->ws.progress); cudaFree(c->ws.counters); cudaFree(c->d_flush);
+    cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]); cudaFree(c->d_slot_base); cudaFree(c->d_slot_sorted); cudaFree(c->d_cost_keys[0]); cudaFree(c->d_cost_keys[1]);
+    cudaFree(c->d_cost_vals); cudaFree(c->d_cost_tmp); cudaFree(c->ws.progress); cudaFree(c->ws.counters); cudaFree(c->d_flush);
     cudaFree(c->d_scratch); cudaFree(c->d_jump); cudaFree(c->d_sort_keys[0]); cudaFree(c->d_sort_keys[1]); cudaFree(c->d_sort_tmp);
     cudaFreeHost(c->h_counters);
     for (auto ev : c->stage_events) cudaEventDestroy(ev);
@@ -818,9 +822,17 @@ int ensure_wave_capacity(ptx_ctx* c, uint32_t slots, uint32_t owned) {
 // slot -> pixel map and per-pixel chunk progress: all the persistent kernel needs besides the film
 int ensure_pixmap(ptx_ctx* c, uint32_t owned, uint32_t film_pixels) {
     if (owned > c->pixmap_capacity) {
-        cudaFree(c->ws.slot_pixel);
+        PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_slot_base); cudaFree(c->d_slot_sorted); cudaFree(c->d_cost_keys[0]); cudaFree(c->d_cost_keys[1]); cudaFree(c->d_cost_vals); cudaFree(c->d_cost_tmp);
+        c->d_slot_base = c->d_slot_sorted = c->d_cost_keys[0] = c->d_cost_keys[1] = c->d_cost_vals = nullptr; c->d_cost_tmp = nullptr;
         c->ws.slot_pixel = nullptr; c->pixmap_capacity = 0; c->slot_key[0] = -1;
-        PTX_CUDA(c, cudaMalloc(&c->ws.slot_pixel, (size_t)owned * sizeof(uint32_t)));
+        const size_t bytes = (size_t)owned * sizeof(uint32_t);
+        PTX_CUDA(c, cudaMalloc(&c->d_slot_base, bytes)); PTX_CUDA(c, cudaMalloc(&c->d_slot_sorted, bytes));
+        PTX_CUDA(c, cudaMalloc(&c->d_cost_keys[0], bytes)); PTX_CUDA(c, cudaMalloc(&c->d_cost_keys[1], bytes)); PTX_CUDA(c, cudaMalloc(&c->d_cost_vals, bytes));
+        size_t need = 0;
+        PTX_CUDA(c, cub::DeviceRadixSort::SortPairs(nullptr, need, c->d_cost_keys[0], c->d_cost_keys[1], c->d_cost_vals, c->d_slot_sorted, (int)owned, 0, 8, c->stream));
+        PTX_CUDA(c, cudaMalloc(&c->d_cost_tmp, need));
+        c->cost_tmp_bytes = need;
         c->pixmap_capacity = owned;
     }
     if (film_pixels > c->progress_capacity) {
@@ -932,12 +944,32 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     rp.shade_batch = opts->shade_batch > 0 ? opts->shade_batch : 12;      // lanes of a warp that must be waiting before it shades
     int key[5] = {w, h, shard_mode, rank, world};
     if (memcmp(key, c->slot_key, sizeof key) != 0) {
-        launch_slot_pixels(c->stream, c->ws.slot_pixel, w, h, shard_mode, rank, world, rp.n_owned);
+        launch_slot_pixels(c->stream, c->d_slot_base, w, h, shard_mode, rank, world, rp.n_owned);
         memcpy(c->slot_key, key, sizeof key);
     }
+    c->ws.slot_pixel = c->d_slot_base;
     if (!opts->accumulate) { rc = ptx_film_clear(film); if (rc != PTX_OK) return rc; }
 
     CameraView cv = camera_view(*cam, w, h);
+    FlatScene fs{};
+    if (flat) {
+        for (size_t k = 0; k < scene->flat.units.size(); k++) flat_set_unit(fs, (int)k, scene->flat.units[k]);
+        fs.recs = scene->d_flat_recs;
+        fs.n_units = (uint32_t)scene->flat.units.size();
+        float scale = scene->flat.scale;                               // rays start at the camera or on the scene
+        for (int k = 0; k < 3; k++) scale = std::max(scale, std::fabs(cam->origin[k]));
+        flat_margins(scale, fs.m0, fs.m1);
+        fs.key_mask = kFlatKeyMask;
+    }
+    // Work order, sequential RNG: the longest-expected pixels first (kernels.cu k_pixel_cost), so that no long sample chain starts late.
+    // Costs 2 probe paths per pixel (0.2 % of a 1 024-spp frame) + an 8-bit radix sort; only the order of the work changes.
+    if (persist && !cta_wave && rng_mode == PTX_RNG_XORWOW_COMPAT && rp.spp >= 64 && rp.n_owned > 0 && !scene->view.inst && !(opts->flags & PTX_RENDER_NO_COST_ORDER)) {
+        launch_pixel_cost(c->stream, scene->view, flat ? &fs : nullptr, cv, rp.shade, c->d_slot_base, rp.n_owned, c->d_cost_keys[0], c->d_cost_vals);
+        PTX_CUDA(c, cudaGetLastError());
+        size_t tmp = c->cost_tmp_bytes;
+        PTX_CUDA(c, cub::DeviceRadixSort::SortPairs(c->d_cost_tmp, tmp, c->d_cost_keys[0], c->d_cost_keys[1], c->d_cost_vals, c->d_slot_sorted, (int)rp.n_owned, 0, 8, c->stream));
+        c->ws.slot_pixel = c->d_slot_sorted;
+    }
     FilmView fv = film->view();
     const bool fused = pipeline == 1;
     const bool path_loop = pipeline == 2;
@@ -960,14 +992,6 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     if (persist) {      // one launch for the whole frame: items are pulled from CTR_NEXT_PATH, nothing else to drive
         if (rng_mode == PTX_RNG_XORWOW_COMPAT && rp.n_owned) PTX_CUDA(c, cudaMemsetAsync(c->ws.progress, 0, (size_t)w * h * sizeof(uint32_t), c->stream));
         if (flat) {
-            FlatScene fs{};
-            for (size_t k = 0; k < scene->flat.units.size(); k++) flat_set_unit(fs, (int)k, scene->flat.units[k]);
-            fs.recs = scene->d_flat_recs;
-            fs.n_units = (uint32_t)scene->flat.units.size();
-            float scale = scene->flat.scale;                               // rays start at the camera or on the scene
-            for (int k = 0; k < 3; k++) scale = std::max(scale, std::fabs(cam->origin[k]));
-            flat_margins(scale, fs.m0, fs.m1);
-            fs.key_mask = kFlatKeyMask;
             int per_sm = opts->ctas_per_sm & 15;
             if (per_sm == 0) {
                 // Resident CTAs per SM (256 threads each).  Bulk throughput is best with 4 (64 registers; C2 28.6 against 27.0 G
@@ -1349,11 +1373,11 @@ int ptx_film_combine(ptx_film* f, ptx_comm* m, int shard_mode) {
         if (rc != PTX_OK) return rc;
         int key[5] = {w, h, PTX_SHARD_TILES, m->rank, m->world};
         if (memcmp(key, c->slot_key, sizeof key) != 0) {
-            launch_slot_pixels(c->stream, c->ws.slot_pixel, w, h, PTX_SHARD_TILES, m->rank, m->world, mine);
+            launch_slot_pixels(c->stream, c->d_slot_base, w, h, PTX_SHARD_TILES, m->rank, m->world, mine);
             memcpy(c->slot_key, key, sizeof key);
         }
         float4* my_slice = m->d_gather + (size_t)m->rank * per_rank;
-        launch_film_pack_owned(c->stream, fv, c->ws.slot_pixel, mine, my_slice);
+        launch_film_pack_owned(c->stream, fv, c->d_slot_base, mine, my_slice);       // canonical slot order (the render may have used the cost order)
         PTX_CUDA(c, cudaGetLastError());
         r = n->AllGather(my_slice, m->d_gather, (size_t)per_rank * 4, ncclFloat32, m->comm, c->stream);     // in place
         if (r != ncclSuccess) return fail(c, PTX_ERR_CUDA, std::string("ncclAllGather: ") + n->GetErrorString(r));

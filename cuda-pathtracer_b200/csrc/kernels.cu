@@ -1062,6 +1062,46 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_path_cta(WaveState ws, SceneVie
 #endif  // PTX_EXPERIMENTAL
 
 // ---------------------------------------------------------------------------------------------
+// Work ORDER of the persistent kernels, compat RNG (longest-expected pixels first).  A pixel's samples are one sequential chain, and
+// the work items are handed out in slot order: a pixel with long paths (the interior of the box) whose first chunk is fetched late
+// finishes after everything else and stretches the frame's tail (one rank of eight on C2: 20.7 ms for 16.9 ms of work).  This probe
+// traces kProbePaths paths per owned pixel with a counter RNG of its own -- it never touches the film's XORWOW streams -- and counts
+// their segments; the slots are then sorted by that cost, descending.  Only the ORDER of the work changes: the film is identical.
+// ---------------------------------------------------------------------------------------------
+constexpr int kProbePaths = 2;
+template <bool FLAT>
+__global__ void __launch_bounds__(kBlock) k_pixel_cost(SceneView scene, const __grid_constant__ FlatScene fs, CameraView cam, ShadeParams sp,
+                                                       const uint32_t* __restrict__ slot_base, uint32_t n_owned, uint32_t* keys, uint32_t* vals) {
+    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+    if (i >= n_owned) return;
+    const uint32_t pixel = slot_base[i];
+    const float fx = (float)(int)(pixel % (uint32_t)cam.width), fy = (float)(int)(pixel / (uint32_t)cam.width);
+    uint32_t nseg = 0;
+    for (int k = 0; k < kProbePaths; k++) {
+        PhiloxRng pr;
+        pr.seek(((unsigned long long)(0xC0570000u + (uint32_t)k) << 32) | pixel, 0u, 0x9E3779B97F4A7C15ull);
+        PathVertex pv;
+        float ju = pr.next(), jv = pr.next();
+        start_path_xy(cam, fx, fy, ju, jv, pv);
+        vec3 L = v3(0.f, 0.f, 0.f);
+        bool cont = true;
+        while (cont) {
+            float t; uint32_t prim;
+            if (FLAT) flat_closest<false>(fs, pv.o, pv.d, 1e-4f, t, prim, nullptr);
+            else {
+                uint32_t tri = trace_closest<24, false>(scene, pv.o, pv.d, 1e-4f, FLT_MAX, t, nullptr);
+                prim = tri == kMiss ? kMiss : __float_as_uint(ldq(scene.tris + (size_t)tri * kTriQuads).w);
+            }
+            nseg++;
+            pr.seek(((unsigned long long)(0xC0570000u + (uint32_t)k) << 32) | pixel, 1u + (uint32_t)pv.depth, 0x9E3779B97F4A7C15ull);
+            cont = shade_bounce(scene, sp, pv, prim, t, pr, L);
+        }
+    }
+    keys[i] = 255u - min(nseg, 255u);          // ascending sort of this key = descending cost; stable: equal costs keep slot order
+    vals[i] = pixel;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Queue sorting for the wavefront pipeline (north_star subsystem 3: ray reordering + material-sorted shading).
 //   ray key      : 15-bit Morton code of the ray origin's cell (32^3 over the scene bounds) << 3 | direction octant -- rays that start
 //                  in the same region and head the same way visit the same nodes and triangle records (L1 / L2 hits in extend)
@@ -1488,6 +1528,12 @@ void launch_path_cta(cudaStream_t st, int rng_mode, const WaveState& ws, const S
 void launch_build_guide(cudaStream_t st, const float* rgb, size_t n_prims, float* out) {
     if (!n_prims) return;
     k_build_guide<<<blocks_for(n_prims, kBlock), kBlock, 0, st>>>(rgb, n_prims, out);
+}
+void launch_pixel_cost(cudaStream_t st, const SceneView& scene, const FlatScene* fs, const CameraView& cam, const ShadeParams& sp, const uint32_t* slot_base,
+                       uint32_t n_owned, uint32_t* keys, uint32_t* vals) {
+    if (!n_owned) return;
+    if (fs) k_pixel_cost<true><<<blocks_for(n_owned, kBlock), kBlock, 0, st>>>(scene, *fs, cam, sp, slot_base, n_owned, keys, vals);
+    else { FlatScene none{}; k_pixel_cost<false><<<blocks_for(n_owned, kBlock), kBlock, 0, st>>>(scene, none, cam, sp, slot_base, n_owned, keys, vals); }
 }
 void launch_queue_keys(cudaStream_t st, const WaveState& ws, const SceneView& scene, int q, uint32_t n_bound, bool by_material, const float lo[3],
                        const float hi[3], uint32_t* keys) {

@@ -88,6 +88,10 @@ void launch_path_cta(cudaStream_t st, int rng_mode, const WaveState& ws, const S
 #endif
 // guide records (kGuideFloats floats per primitive, shade.h) from n_prims x 256 x 3 device floats of radiosity
 void launch_build_guide(cudaStream_t st, const float* rgb, size_t n_prims, float* out);
+// cost probe for the work order of the persistent kernels (kernels.cu k_pixel_cost): keys[i] = 255 - segments of 2 probe paths of
+// pixel slot_base[i], vals[i] = that pixel; fs = the flat unit list or nullptr (BVH8)
+void launch_pixel_cost(cudaStream_t st, const SceneView& scene, const FlatScene* fs, const CameraView& cam, const ShadeParams& sp, const uint32_t* slot_base,
+                       uint32_t n_owned, uint32_t* keys, uint32_t* vals);
 // sort keys of queue[q][0, n_bound): ray keys (origin cell + direction octant) or material keys (after extend); kernels.cu
 void launch_queue_keys(cudaStream_t st, const WaveState& ws, const SceneView& scene, int q, uint32_t n_bound, bool by_material, const float lo[3],
                        const float hi[3], uint32_t* keys);

@@ -220,6 +220,9 @@ enum {
     PTX_RENDER_SORT_RAYS = 8,      /* pipeline 4: sort the queue by (origin cell, direction octant) before every extend (ray reordering) */
     PTX_RENDER_SORT_MATERIAL = 16, /* pipeline 4: sort the queue by the material of the hit before every shade (material-sorted shading).
                                       Neither changes an image (a slot's path, stream and pixel are its own); measured in DESIGN.md */
+    PTX_RENDER_NO_COST_ORDER = 32, /* pipelines 3 / 6, compat RNG: keep the work items in pixel order instead of handing out the
+                                      longest-expected pixels first (a 2-path probe per pixel + a radix sort per frame); images are the
+                                      same either way, only the frame's tail differs (A/B measurements) */
     PTX_RENDER_ASYNC = 4           /* pipelines 3 / 6: ptx_render returns without waiting for the GPU (nothing between the render
                                       and a following ptx_film_combine / resolve synchronises the host); the statistics are
                                       completed by the next ptx_render_stats_get, ptx_sync or ptx_render on this context */

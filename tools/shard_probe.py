@@ -26,8 +26,8 @@ with pkg.Context(0) as ctx:
     for n in worlds:
         mode = pkg.SHARD_NONE if n == 1 else (pkg.SHARD_TILES if rng == 0 else pkg.SHARD_SAMPLES)
         for rep in range(2):
-            st = ctx.render(scene, cam, film, spp=spp, max_depth=depth, pipeline=pipe, chunks=chunks, rng_mode=rng, loop_min_blocks=min_blocks,
+            st = ctx.render(scene, cam, film, spp=spp, max_depth=depth, pipeline=pipe, cost_order=os.environ.get("COST_ORDER", "1") == "1", chunks=chunks, rng_mode=rng, loop_min_blocks=min_blocks,
                             shard_mode=mode, shard_rank=0, shard_world=n)
         t1 = t1 or st["render_ms"]
-        print(json.dumps({"workload": wl, "chunks": chunks, "rng": rng, "min_blocks": min_blocks, "pipeline": pipe, "world": n, "render_ms": round(st["render_ms"], 2), "ideal_ms": round(t1 / n, 2),
+        print(json.dumps({"workload": wl, "chunks": chunks, "rng": rng, "min_blocks": min_blocks, "pipeline": pipe, "cost_order": os.environ.get("COST_ORDER", "1"), "world": n, "render_ms": round(st["render_ms"], 2), "ideal_ms": round(t1 / n, 2),
                           "efficiency": round(t1 / n / st["render_ms"], 3), "Gseg_s": round(st["segments"] / st["render_ms"] / 1e6, 2)}))
