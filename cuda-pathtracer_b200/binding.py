@@ -53,7 +53,7 @@ class SceneStats(C.Structure):
                 ("node_bytes", C.c_int64), ("triangle_bytes", C.c_int64), ("shading_bytes", C.c_int64),
                 ("bounds_min", C.c_float * 3), ("bounds_max", C.c_float * 3), ("sah_cost", C.c_float), ("build_ms", C.c_float),
                 ("builder", C.c_int32), ("max_depth", C.c_int32), ("preprocess_ms", C.c_float), ("preprocess_on_device", C.c_int32),
-                ("n_instances", C.c_int32), ("reserved2", C.c_int32), ("stored_triangles", C.c_int64),
+                ("n_instances", C.c_int32), ("reserved2", C.c_int32), ("stored_triangles", C.c_int64), ("build_stage_ms", C.c_float * 4),
                 ("flat_units", C.c_int32), ("reserved", C.c_int32)]
 
 
@@ -376,6 +376,7 @@ class Scene:
         _check(lib().ptx_scene_stats_get(self._h, C.byref(st)))
         d = {k: getattr(st, k) for k, _ in SceneStats._fields_}
         d["bounds_min"], d["bounds_max"] = list(st.bounds_min), list(st.bounds_max)
+        d["build_stage_ms"] = list(st.build_stage_ms)
         return d
 
     def rebuild(self, builder=0, sah_bins=0, max_leaf=0):

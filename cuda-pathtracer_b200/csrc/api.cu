@@ -302,6 +302,7 @@ int build_accel(ptx_scene* s, const ptx_build_opts* bo, const TriIn* d_tris_in =
         s->view.n_nodes = g.n_nodes; s->view.n_tris = g.n_tris;
         node_bytes = (size_t)g.n_nodes * kNodeQuads * sizeof(u32x4); tri_bytes = (size_t)g.n_tris * kTriQuads * sizeof(f32x4);
         sah = g.sah_cost; depth = g.max_depth; bounds = g.bounds;
+        memcpy(s->stats.build_stage_ms, g.stage_ms, sizeof g.stage_ms);
     } else {
         Bvh8Result r;
         Bvh2 b2;

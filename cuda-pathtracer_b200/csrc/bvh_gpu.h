@@ -18,6 +18,7 @@ struct GpuBvhResult {
     int max_depth = 0;             // BVH8 depth
     float sah_cost = 0.f;
     aabb bounds;
+    float stage_ms[4] = {0.f, 0.f, 0.f, 0.f};   // upload + boxes + Morton sort | binned-SAH levels | leaf order | BVH8 collapse
 };
 
 // tris: n input triangles, on the host (uploaded here) or already on the device (tris_on_device; read in place, e.g. the

@@ -107,6 +107,7 @@ typedef struct {
     int32_t n_instances;      /* > 0: two-level scene (keep_instances): instances in the TLAS; n_triangles is then the FLATTENED count */
     int32_t reserved2;
     int64_t stored_triangles; /* triangle records actually stored (two-level: every object once) */
+    float build_stage_ms[4];  /* device builder: upload + boxes + Morton sort | binned-SAH levels | leaf order | BVH8 collapse */
     int32_t flat_units;       /* > 0: the scene is tiny enough for the flat unit list (<= 20 planar quads / triangle pairs):
                                  ptx_render's default pipeline then runs without a tree (pipeline 6) */
     int32_t reserved;
