@@ -24,6 +24,7 @@
 #include "kernels.cuh"
 #include "geometry_gpu.h"
 #include "image_io.h"
+#include "instancing_host.h"
 #include "loader.h"
 #include "rng.h"
 #include "scene_pack.h"
@@ -390,20 +391,6 @@ int scene_from_base_gpu(ptx_ctx* c, const std::vector<ptx_primitive>& base, bool
     return rc;
 }
 
-// 3 x 4 affine inverse in double precision (columns vx, vy, vz, translation)
-bool invert_affine(const float* m, float* inv) {
-    const double a = m[0], b = m[3], c = m[6], d = m[1], e = m[4], f = m[7], g = m[2], h = m[5], i = m[8];
-    const double det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
-    if (!(std::fabs(det) > 1e-30)) return false;
-    const double r[9] = {(e * i - f * h) / det, (c * h - b * i) / det, (b * f - c * e) / det,
-                         (f * g - d * i) / det, (a * i - c * g) / det, (c * d - a * f) / det,
-                         (d * h - e * g) / det, (b * g - a * h) / det, (a * e - b * d) / det};      // row-major inverse of the linear part
-    // store as columns: inv[0..2] = first column = (r[0], r[3], r[6]) ...
-    for (int col = 0; col < 3; col++) for (int row = 0; row < 3; row++) inv[3 * col + row] = (float)r[3 * row + col];
-    for (int row = 0; row < 3; row++) inv[9 + row] = (float)(-(r[3 * row + 0] * m[9] + r[3 * row + 1] * m[10] + r[3 * row + 2] * m[11]));
-    return true;
-}
-
 // Two-level scene: one BLAS per object (the world's own shapes are object 0 under the identity), a TLAS over the instances' world
 // boxes, all in ONE node array and ONE triangle array (TLAS first).  Every tree comes from the device builder; the TLAS is built
 // from one placeholder triangle per instance whose bounding box is the instance's box and whose prim id is the instance index.
@@ -447,20 +434,9 @@ int scene_from_instanced(ptx_ctx* c, InstancedScene& is, ptx_scene** out) {
     std::vector<TriIn> boxes;
     uint32_t prim_base = 0;
     auto add_instance = [&](size_t obj, const float* m) -> bool {
-        InstanceRec r; memset(&r, 0, sizeof r);
-        memcpy(r.m, m, sizeof r.m);
-        if (!invert_affine(m, r.inv)) return false;
-        r.root = (uint32_t)obj;                                         // patched to the node offset below
-        r.prim_base = prim_base; r.shade_base = (uint32_t)obj_first[obj];
+        InstanceRec r; TriIn t;
+        if (!make_instance(m, blas[obj].bounds, (uint32_t)obj, prim_base, (uint32_t)obj_first[obj], (uint32_t)recs.size(), r, t)) return false;
         prim_base += (uint32_t)(obj_first[obj + 1] - obj_first[obj]);
-        aabb wb = aabb_empty();
-        const aabb& ob = blas[obj].bounds;
-        for (int k = 0; k < 8; k++) aabb_grow(wb, xfm_pt(m, mk3((k & 1) ? ob.hi.x : ob.lo.x, (k & 2) ? ob.hi.y : ob.lo.y, (k & 4) ? ob.hi.z : ob.lo.z)));
-        const vec3 ext = wb.hi - wb.lo;                                 // the corners were transformed in float: pad by a few ulps of the box
-        const float pad = 1e-5f * std::max(std::max(ext.x, ext.y), std::max(ext.z, 1e-3f)) + 1e-6f * std::max(std::max(std::fabs(wb.hi.x), std::fabs(wb.lo.x)), std::max(std::max(std::fabs(wb.hi.y), std::fabs(wb.lo.y)), std::max(std::fabs(wb.hi.z), std::fabs(wb.lo.z))));
-        TriIn t;
-        st3(t.v0, wb.lo - mk3(pad, pad, pad)); st3(t.v1, wb.hi + mk3(pad, pad, pad)); st3(t.v2, 0.5f * (wb.lo + wb.hi));
-        t.prim_id = (uint32_t)recs.size();
         boxes.push_back(t); recs.push_back(r);
         return true;
     };

@@ -11,6 +11,7 @@
 
 #include "../cuda-pathtracer_b200/csrc/bvh_host.h"
 #include "../cuda-pathtracer_b200/csrc/flat_host.h"
+#include "../cuda-pathtracer_b200/csrc/instancing_host.h"
 #include "../cuda-pathtracer_b200/csrc/loader.h"
 #include "../cuda-pathtracer_b200/csrc/rng.h"
 #include "../cuda-pathtracer_b200/csrc/scene_pack.h"
@@ -132,6 +133,100 @@ void emu_occluded(const EmuScene* s, const float* segs, int64_t n, uint8_t* out)
         vec3 o = from + 1e-4f * dir;
         vec3 d = unit(dir);
         out[i] = trace_any<32>(s->view, o, d, 1e-4f, dist - 1e-4f) ? 1 : 0;
+    }
+}
+
+// ---- two-level scenes on the CPU: the assembly of api.cu scene_from_instanced with the HOST builder in place of the device builder ----
+struct EmuInstScene {
+    PackedScene packed;
+    std::vector<u32x4> nodes;
+    std::vector<f32x4> tris;
+    std::vector<InstanceRec> inst;
+    SceneView view;
+    int64_t flattened_prims = 0;
+    int depth_tlas = 0, depth_blas = 0;
+};
+EmuInstScene* emu_inst_load(const char* path, int mirror_ext) {
+    InstancedScene is; std::string err;
+    if (!load_pbrt_instanced(path, mirror_ext != 0, is, err)) return nullptr;
+    EmuInstScene* s = new EmuInstScene();
+    std::vector<size_t> obj_first;
+    std::vector<ptx_primitive> all;
+    const bool has_world = !is.world.empty();
+    if (has_world) { obj_first.push_back(0); all.insert(all.end(), is.world.begin(), is.world.end()); }
+    for (auto& o : is.objects) { obj_first.push_back(all.size()); all.insert(all.end(), o.begin(), o.end()); }
+    obj_first.push_back(all.size());
+    const size_t n_obj = obj_first.size() - 1;
+    pack_primitives(all.data(), all.size(), s->packed);
+    std::vector<Bvh8Result> blas(n_obj);
+    for (size_t k = 0; k < n_obj; k++) {
+        const size_t first = obj_first[k], n = obj_first[k + 1] - first;
+        std::vector<TriIn> local(s->packed.tris.begin() + (ptrdiff_t)first, s->packed.tris.begin() + (ptrdiff_t)(first + n));
+        for (auto& t : local) t.prim_id -= (uint32_t)first;
+        Bvh2 b2;
+        build_bvh2_sah(local.data(), n, 16, 3, b2);
+        collapse_bvh8(b2, local.data(), n, blas[k]);
+        s->depth_blas = std::max(s->depth_blas, blas[k].max_depth);
+    }
+    std::vector<TriIn> boxes;
+    uint32_t prim_base = 0;
+    auto add = [&](size_t obj, const float* m) {
+        InstanceRec r; TriIn t;
+        if (!make_instance(m, blas[obj].bounds, (uint32_t)obj, prim_base, (uint32_t)obj_first[obj], (uint32_t)s->inst.size(), r, t)) return false;
+        prim_base += (uint32_t)(obj_first[obj + 1] - obj_first[obj]);
+        boxes.push_back(t); s->inst.push_back(r);
+        return true;
+    };
+    const float ident[12] = {1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0};
+    bool ok = true;
+    if (has_world) ok = add(0, ident);
+    for (const auto& in : is.instances) if (ok) ok = add((size_t)in.object + (has_world ? 1 : 0), in.m);
+    if (!ok) { delete s; return nullptr; }
+    Bvh2 t2; Bvh8Result tlas;
+    build_bvh2_sah(boxes.data(), boxes.size(), 16, 1, t2);
+    collapse_bvh8(t2, boxes.data(), boxes.size(), tlas);
+    s->depth_tlas = tlas.max_depth;
+    s->nodes = tlas.nodes; s->tris = tlas.tris;
+    std::vector<uint32_t> node_off(n_obj);
+    for (size_t k = 0; k < n_obj; k++) {
+        const uint32_t noff = (uint32_t)(s->nodes.size() / kNodeQuads), toff = (uint32_t)(s->tris.size() / kTriQuads);
+        node_off[k] = noff;
+        for (size_t i = 0; i < blas[k].nodes.size(); i++) {
+            u32x4 q = blas[k].nodes[i];
+            if (i % kNodeQuads == 1) { q.x += noff; q.y += toff; }                  // k_offset_nodes
+            s->nodes.push_back(q);
+        }
+        s->tris.insert(s->tris.end(), blas[k].tris.begin(), blas[k].tris.end());
+    }
+    for (auto& r : s->inst) r.root = node_off[r.root];
+    s->flattened_prims = prim_base;
+    s->view.nodes = s->nodes.data(); s->view.tris = s->tris.data();
+    s->view.prim_shade = s->packed.prim_shade.data(); s->view.materials = s->packed.materials.data();
+    s->view.n_nodes = (uint32_t)(s->nodes.size() / kNodeQuads); s->view.n_tris = (uint32_t)(s->tris.size() / kTriQuads);
+    s->view.n_prims = prim_base; s->view.n_mats = (uint32_t)(s->packed.materials.size() / 2);
+    s->view.inst = s->inst.data(); s->view.n_inst = (uint32_t)s->inst.size();
+    return s;
+}
+void emu_inst_free(EmuInstScene* s) { delete s; }
+int64_t emu_inst_counts(const EmuInstScene* s, int64_t* n_inst, int64_t* stored_tris, int* depth_tlas, int* depth_blas) {
+    *n_inst = (int64_t)s->inst.size(); *stored_tris = (int64_t)s->packed.tris.size(); *depth_tlas = s->depth_tlas; *depth_blas = s->depth_blas;
+    return s->flattened_prims;
+}
+// closest hits through the two-level traversal; prim = flattened numbering; normals_out (optional, 3 floats per ray) = the world-space
+// shading normal resolve_instanced_hit computes
+void emu_inst_trace(const EmuInstScene* s, const float* rays, int64_t n, float t_min, int32_t* prim, float* t, float* normals_out) {
+    for (int64_t i = 0; i < n; i++) {
+        vec3 o = ld3(rays + 6 * i), d = unit(ld3(rays + 6 * i + 3));
+        InstTraversal it; TravStack<32> stk;
+        it.begin(o, d, FLT_MAX);
+        while (!it.template step<32>(s->view, stk, o, d, t_min)) {}
+        prim[i] = -1; t[i] = -1.0f;
+        if (it.tr.best != kMiss) {
+            uint32_t p, mat; vec3 nn;
+            resolve_instanced_hit(s->view, it, p, nn, mat);
+            prim[i] = (int32_t)p; t[i] = it.tr.closest;
+            if (normals_out) st3(normals_out + 3 * i, nn);
+        }
     }
 }
 

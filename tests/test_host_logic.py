@@ -37,6 +37,12 @@ def emu(built):
     L.emu_parse_obj.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_int64]
     L.emu_xorwow_init.argtypes = [C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]
     L.emu_occluded.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+    L.emu_inst_load.restype = C.c_void_p
+    L.emu_inst_load.argtypes = [C.c_char_p, C.c_int]
+    L.emu_inst_free.argtypes = [C.c_void_p]
+    L.emu_inst_counts.restype = C.c_int64
+    L.emu_inst_counts.argtypes = [C.c_void_p] * 5
+    L.emu_inst_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
     L.emu_flat_units.argtypes = [C.c_void_p, C.c_void_p]
     L.emu_trace_flat.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
     L.emu_render_flat.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -329,6 +335,42 @@ def test_mirror_extension_core_vs_oracle(pkg, emu, oracle):
     assert seg.value == ostats[0]
     assert np.array_equal(bits(lin), bits(olin))
     emu.emu_scene_free(s); oracle.free(osc)
+
+
+# ---- two-level instancing (traverse_inst.h, instancing_host.h) ------------------------------------
+def test_two_level_traversal_matches_flattened_scene(pkg, emu, tmp_path):
+    """keep_instances on the CPU: the product's instanced loader, instance records (instancing_host.h) and InstTraversal compiled for
+    the host, trees from the host builder -- against the FLATTENED load of the same file (what the reference's loadPBRT produces,
+    pinned bit for bit by pbrt_vectors.npz) traversed single-level.  Same primitive numbering, distances equal to rounding, and the
+    shading normal resolved per instance equals the flattened primitive's stored normal."""
+    from cuda_pathtracer_b200 import scenegen
+    path = str(tmp_path / "inst.pbrt")
+    n = scenegen.write_c5_pbrt(path, instances=20, level=3, n_lights=4)
+    flat_prims = pkg.parse_scene_file(path, mirror_from_mtl=True)
+    assert len(flat_prims) == n
+    sf = emu.emu_scene_from_prims(P(flat_prims), len(flat_prims), 3)
+    si = emu.emu_inst_load(path.encode(), 1)
+    assert si
+    ni, stored, dt, db = C.c_int64(), C.c_int64(), C.c_int(), C.c_int()
+    assert emu.emu_inst_counts(si, C.byref(ni), C.byref(stored), C.byref(dt), C.byref(db)) == n
+    assert ni.value == 21 and stored.value == 2 * 20 * 4 ** 3 + 10 + 2 * 4
+    assert 2 * dt.value + 1 + db.value <= 24                                    # fits the kernels' traversal stack
+    rng = np.random.default_rng(9)
+    o = rng.uniform(0.5, 11.5, (4000, 3)); d = rng.normal(size=(4000, 3))
+    rays = np.concatenate([o, d], 1).astype(np.float32)
+    idf = np.zeros(4000, np.int32); tf = np.zeros(4000, np.float32)
+    idi = np.zeros(4000, np.int32); ti = np.zeros(4000, np.float32); nrm = np.zeros((4000, 3), np.float32)
+    emu.emu_trace(sf, P(rays), 4000, C.c_float(1e-4), P(idf), P(tf), None)
+    emu.emu_inst_trace(si, P(rays), 4000, C.c_float(1e-4), P(idi), P(ti), P(nrm))
+    assert (idf >= 0).mean() > 0.8                                               # the room is open at the front
+    same = idf == idi
+    assert same.mean() >= 0.999, float(same.mean())
+    close = np.isclose(ti[same], tf[same], rtol=1e-4, atol=1e-4)
+    assert close.mean() >= 0.999
+    hit = same & (idf >= 0)
+    want = flat_prims["normal"][idf[hit]]
+    assert np.abs(nrm[hit] - want).max() < 2e-3                                  # unit(L e1 x L e2) against the flattened unit((v1 - v0) x (v2 - v0))
+    emu.emu_scene_free(sf); emu.emu_inst_free(si)
 
 
 # ---- any-hit end-point rule (traverse.h trace_any) -------------------------------------------------
