@@ -26,6 +26,12 @@ struct WideChild {
     uint32_t tri_offset;     // leaf only: offset from the node's tri_base
 };
 
+// Padding of every primitive's box before the build.  The reference pads its BVH2 boxes by 1e-6 (rendering/bvh.h:110-150,
+// restated at oracle/pt_oracle.c:181): a ray aimed exactly at a vertex or an edge that lies on a box face is then still inside
+// the box when the exact triangle test -- which alone decides a hit -- accepts it within rounding.  The relative term
+// (4 ulp of the coordinate) keeps that true for scenes far from the origin, where 1e-6 is below one ulp.
+PTX_HD float box_pad(float lo, float hi) { return fmaxf(1e-6f, 4.76837158e-7f * fmaxf(fabsf(lo), fabsf(hi))); }
+
 constexpr float kTravCost = 1.0f;   // cost of visiting one wide-node child box relative to one triangle test
 
 PTX_HD void pack_triangle(const TriIn& t, f32x4 out[3]) {

@@ -89,6 +89,8 @@ __global__ void __launch_bounds__(kThreads) k_prim_setup(const TriIn* __restrict
             lo[a] = fminf(t.v0[a], fminf(t.v1[a], t.v2[a]));
             hi[a] = fmaxf(t.v0[a], fmaxf(t.v1[a], t.v2[a]));
             c[a] = 0.5f * (lo[a] + hi[a]);
+            float pad = box_pad(lo[a], hi[a]);                 // bvh_common.h: the reference's 1e-6 box padding
+            lo[a] -= pad; hi[a] += pad;
         }
         PrimBox pb;
         for (int a = 0; a < 3; a++) { pb.lo[a] = lo[a]; pb.hi[a] = hi[a]; }

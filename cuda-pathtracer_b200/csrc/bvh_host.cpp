@@ -20,6 +20,13 @@ inline aabb tri_box(const TriIn& t) {
     return b;
 }
 inline vec3 box_center(const aabb& b) { return mk3(0.5f * (b.lo.x + b.hi.x), 0.5f * (b.lo.y + b.hi.y), 0.5f * (b.lo.z + b.hi.z)); }
+inline aabb padded(const aabb& b) {     // bvh_common.h box_pad; the centroid is taken from the unpadded box (as k_prim_setup does)
+    float px = box_pad(b.lo.x, b.hi.x), py = box_pad(b.lo.y, b.hi.y), pz = box_pad(b.lo.z, b.hi.z);
+    aabb r;
+    r.lo = mk3(b.lo.x - px, b.lo.y - py, b.lo.z - pz);
+    r.hi = mk3(b.hi.x + px, b.hi.y + py, b.hi.z + pz);
+    return r;
+}
 
 
 }  // namespace
@@ -30,7 +37,7 @@ void build_bvh2_sah(const TriIn* tris, size_t n, int bins, int max_leaf, Bvh2& o
     out.nodes.clear(); out.order.resize(n);
     std::vector<aabb> boxes(n);
     std::vector<vec3> cents(n);
-    for (size_t i = 0; i < n; i++) { out.order[i] = (uint32_t)i; boxes[i] = tri_box(tris[i]); cents[i] = box_center(boxes[i]); }
+    for (size_t i = 0; i < n; i++) { out.order[i] = (uint32_t)i; aabb tb = tri_box(tris[i]); cents[i] = box_center(tb); boxes[i] = padded(tb); }
     out.nodes.reserve(n ? 2 * n : 1);
     out.nodes.push_back(Bvh2Node{aabb_empty(), 0, 0, 0});
     if (n == 0) return;
