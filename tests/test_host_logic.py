@@ -319,6 +319,36 @@ def test_flat_and_bvh8_agree_on_adversarial_tiny_scenes(pkg, emu, oracle):
     assert total >= 100000 and lin_checked >= 2400
 
 
+def test_bvh8_adversarial_rays_on_clustered_soups(pkg, emu, oracle):
+    """Deeper trees: 50..600 primitives in clusters plus an axis-aligned grid of quads (shared edges lying ON box faces), rays aimed
+    at edges and vertices.  The padded BVH8 boxes must keep every hit of the reference's linear scan, bit for bit."""
+    import fuzz_scenes
+    rng = np.random.default_rng(99)
+    for it in range(4):
+        parts = []
+        for _ in range(int(rng.integers(8, 50))):
+            p, off, size = fuzz_scenes.tiny_scene(rng, pkg.PRIM_DTYPE)
+            p["v"] += (rng.normal(size=3) * 5).astype(np.float32) - off
+            parts.append(p)
+        g = int(rng.integers(2, 8))
+        q = np.zeros(g * g, pkg.PRIM_DTYPE); q["type"] = 1; q["bsdf"] = 0.5; q["normal"] = [0, 1, 0]
+        for i in range(g):
+            for j in range(g):
+                q["v"][i * g + j] = [[i, 0, j], [i + 1, 0, j], [i + 1, 0, j + 1], [i, 0, j + 1]]
+        prims = np.concatenate(parts + [q])
+        s = emu.emu_scene_from_prims(P(prims), len(prims), 1 + it % 3)
+        m = 700
+        rays = fuzz_scenes.adversarial_rays(rng, prims, np.zeros(3, np.float32), 3.0, m)
+        ia = np.zeros(m, np.int32); ta = np.zeros(m, np.float32)
+        emu.emu_trace(s, P(rays), m, C.c_float(1e-4), P(ia), P(ta), None)
+        osc = oracle.scene_from_prims(prims)
+        il, tl = oracle.intersect(osc, rays, mode=1)
+        tl = np.where(il >= 0, tl, -1.0).astype(np.float32)
+        assert np.array_equal(bits(ta), bits(tl)), (it, np.nonzero(bits(ta) != bits(tl))[0][:5])
+        assert (ia != il).mean() < 0.03                  # same distance to the bit, another primitive: shared edges of the grid
+        oracle.free(osc); emu.emu_scene_free(s)
+
+
 def test_flat_units_reject_large_or_degenerate(pkg, emu):
     prims = pkg.parse_scene_file(os.path.join(SCENES, "cbox.obj"), subdivision=1)      # 128 triangles
     s = emu.emu_scene_from_prims(P(prims), len(prims), 3)
