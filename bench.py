@@ -199,7 +199,8 @@ class Run:
         self.film = ctx.create_film(self.w, self.h)
         self.rgb_host = np.empty((self.h, self.w, 3), np.uint8)
         self.kw = dict(spp=spp, max_depth=depth, rng_mode=self.rng_mode, pipeline=pipeline, shard_mode=self.shard_mode, shard_rank=rank, shard_world=world,
-                       loop_min_blocks=args.min_blocks, chunks=args.chunks, shade_batch=args.shade_batch)
+                       loop_min_blocks=args.min_blocks, chunks=args.chunks, shade_batch=args.shade_batch,
+                       cost_order=not getattr(args, "no_cost_order", False))
 
     def barrier(self):
         self.ctx.sync()
@@ -507,6 +508,7 @@ def main():
     ap.add_argument("--min-blocks", type=int, default=0, help="experiment: occupancy variant of the path-loop kernels (0 = 3x256 threads/SM, 4 = 4x256, 7 = 7x128)")
     ap.add_argument("--chunks", type=int, default=0, help="experiment: work items per pixel of the persistent kernel, compat RNG (0 = default 6, 1 = none)")
     ap.add_argument("--shade-batch", type=int, default=0, help="experiment: waiting lanes per warp that trigger a shading round (0 = default 12, 1 = at once)")
+    ap.add_argument("--no-cost-order", action="store_true", help="experiment: hand out the work items in film order instead of longest-expected first")
     ap.add_argument("--max-leaf", type=int, default=0, help="experiment: triangles per BVH8 leaf slot (1..3; 0 = library default)")
     args = ap.parse_args()
     scene, w, h, spp, depth = WORKLOADS[args.workload]
