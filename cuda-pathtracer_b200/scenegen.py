@@ -8,6 +8,8 @@ Everything is float32 and deterministic (hash-based value noise, fixed seeds).  
 produced by subdividing triangles directly: a shared edge midpoint is computed from the same two floats
 in both triangles ((a + b) is commutative in IEEE arithmetic), so the meshes are watertight.
 """
+import os
+
 import numpy as np
 
 _PHI = (1.0 + 5.0 ** 0.5) / 2.0
@@ -203,3 +205,40 @@ def write_c5_pbrt(path, instances=4883, level=5, n_lights=64, seed=7):
             n += len(f)
         fp.write("WorldEnd\n")
     return n + 10 + 2 * n_lights
+
+
+def write_tree_obj(path, prims, level=5, seed=1234):
+    """A mid-size scene the REFERENCE can load (parity tests): the enclosure of scenes/cbox_quads.obj (its first six faces, as
+    quads) plus two displaced icospheres of 20 * 4^level triangles each, written as .obj + .mtl with unshared vertices, no `vn`
+    (both loaders then store the geometric normal) and 9 significant digits (float32 round-trips).  Lambertian materials only.
+    `prims` = binding.parse_scene_file(cbox_quads.obj).  Returns the primitive count."""
+    mats = [("Khaki", CORNELL_MATS[0]), ("BloodyRed", CORNELL_MATS[1]), ("DarkGreen", CORNELL_MATS[2]), ("Light", CORNELL_MATS[3]),
+            ("Blob", CORNELL_MATS[4]), ("Blob2", {"bsdf": (0.3, 0.4, 0.75), "Le": (0, 0, 0), "type": 0})]
+    mtl = os.path.splitext(path)[0] + ".mtl"
+    with open(mtl, "w") as fp:
+        for name, m in mats:
+            fp.write(f"newmtl {name}\nKd {m['bsdf'][0]:.9g} {m['bsdf'][1]:.9g} {m['bsdf'][2]:.9g}\nKe {m['Le'][0]:.9g} {m['Le'][1]:.9g} {m['Le'][2]:.9g}\n\n")
+    n_v = n_p = 0
+    with open(path, "w") as fp:
+        fp.write(f"# generated by cuda-pathtracer_b200/scenegen.py: write_tree_obj(level={level}, seed={seed})\nmtllib {os.path.basename(mtl)}\n")
+        for p in prims[:6]:
+            k = 4 if p["type"] == 1 else 3
+            emissive = float(np.max(p["Le"])) > 0
+            m = 3 if emissive else int(np.argmin([np.abs(np.asarray(mm["bsdf"], np.float32) - p["bsdf"]).sum() for _, mm in mats[:3]]))
+            fp.write(f"usemtl {mats[m][0]}\n")
+            for v in p["v"][:k]:
+                fp.write("v %.9g %.9g %.9g\n" % tuple(float(x) for x in v))
+            fp.write("f " + " ".join(str(n_v + 1 + i) for i in range(k)) + "\n")
+            n_v += k; n_p += 1
+        for name, radius, centre in (("Blob", 1.0, (-1.2, 1.2, -3.0)), ("Blob2", 0.8, (1.0, 0.9, -2.0))):
+            tris = displaced_icosphere(level, radius, centre, seed=seed)
+            fp.write(f"usemtl {name}\n")
+            lines = []
+            for t in tris:
+                for v in t:
+                    lines.append("v %.9g %.9g %.9g\n" % (float(v[0]), float(v[1]), float(v[2])))
+                lines.append(f"f {n_v + 1} {n_v + 2} {n_v + 3}\n")
+                n_v += 3
+            fp.write("".join(lines))
+            n_p += len(tris)
+    return n_p

@@ -35,7 +35,7 @@ def run_ref_cuda(tmp_path, scene, w, h, spp, depth, orig=False):
     if not os.path.exists(REF_CUDA):
         pytest.skip("oracle/_ref/ref_cuda not built (needs /root/reference at build time)")
     prefix = str(tmp_path / f"ref_{w}x{h}_{spp}_{depth}_{int(orig)}")
-    r = subprocess.run([REF_CUDA, "render", os.path.join(SCENES, scene), str(w), str(h), str(spp), str(depth), "1", prefix, "0", "0", "1" if orig else "0"],
+    r = subprocess.run([REF_CUDA, "render", scene if os.path.isabs(scene) else os.path.join(SCENES, scene), str(w), str(h), str(spp), str(depth), "1", prefix, "0", "0", "1" if orig else "0"],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-500:]
     info = json.loads(r.stdout.strip().splitlines()[-1])
@@ -103,6 +103,40 @@ def test_unmodified_render_kernel_rgb8(pkg, ctx, tmp_path, scene, w, h, spp):
     report(f"render() {scene}", rgb8_max_diff=int(d8.max()), rgb8_identical=float((d8 == 0).mean()), bytes_differing=int((d8 != 0).sum()))
     # a pixel one of whose paths diverged can move by more than 1 LSB at 64 spp: bound the count of such bytes instead
     assert (d8 <= 1).mean() >= 0.9999 and (d8 == 0).mean() >= 0.99
+    film.close(); sc.close()
+
+
+@pytest.mark.parametrize("level,w,h,spp,depth", [(5, 512, 512, 16, 8), (6, 960, 540, 8, 8)])
+def test_tree_scene_vs_reference_cuda_kernels(pkg, ctx, tmp_path, level, w, h, spp, depth):
+    """A scene with a real tree (the Cornell enclosure + two displaced icospheres: 40 966 / 163 846 primitives, written as .obj by
+    scenegen.write_tree_obj so that the REFERENCE loads it): the reference's own loadOBJ + BVHBuilder + CUDA kernels against the
+    product's loader, device-built BVH8 and k_path_persist (two-records-per-round instantiation) on the same GPU.  The Cornell
+    scenes of the other full-size tests take the flat unit list; this one is the traversal the large configurations (C3, C5) use."""
+    from cuda_pathtracer_b200 import scenegen
+    path = str(tmp_path / "tree.obj")
+    n = scenegen.write_tree_obj(path, pkg.parse_scene_file(os.path.join(SCENES, "cbox_quads.obj")), level=level)
+    rlin, rrgb, info = run_ref_cuda(tmp_path, path, w, h, spp, depth)
+    assert info["prims"] == n
+    sc = ctx.load_scene(path)
+    assert sc.stats()["flat_units"] == 0 and sc.stats()["n_triangles"] == n + 6
+    cam = pkg.default_camera(w, h)
+    film = ctx.create_film(w, h)
+    st = ctx.render(sc, cam, film, spp=spp, max_depth=depth)
+    lin, rgb = film.linear(), film.rgb8()
+    err = mean_rel_err(lin, rlin)
+    d8 = np.abs(rgb.astype(int) - rrgb.astype(int))
+    differ = int((lin != rlin).any(-1).sum())
+    report(f"tree level {level} ({n} primitives)", mean_rel_err=err, pixels_differing=differ, pixels=w * h, rgb8_identical=float((d8 == 0).mean()),
+           ref_ms=info["ms_per_frame"], ours_ms=st["render_ms"], segments=st["segments"], ref_nodes=info["nodes"], bvh8_nodes=sc.stats()["n_nodes"])
+    assert err <= TOL_IMAGE, err
+    same = (np.abs(lin.astype(np.float64) - rlin) <= 1e-5 * np.maximum(rlin, 1e-3)).all(-1)
+    assert d8[same].max() <= 1 and (d8 == 0).mean() >= 0.99
+    assert (~same).sum() <= 2e-3 * w * h, int((~same).sum())
+    film.reset(2023)
+    st2 = ctx.render(sc, cam, film, spp=spp, max_depth=depth, pipeline=pkg.PIPELINE_WAVEFRONT)
+    nd = int((film.linear() != lin).any(-1).sum())
+    report(f"tree level {level}: wavefront vs persistent", pixels_differing=nd, segments=st2["segments"])
+    assert nd <= 1e-4 * w * h + 2
     film.close(); sc.close()
 
 

@@ -349,6 +349,38 @@ def test_bvh8_adversarial_rays_on_clustered_soups(pkg, emu, oracle):
         oracle.free(osc); emu.emu_scene_free(s)
 
 
+def test_tree_scene_bvh8_vs_reference_goldens(pkg, emu, tmp_path):
+    """A 2 566-primitive scene (tests/golden/make_golden_tree.py): the product's .obj loader equals the reference's dump bit for bit on
+    a generated file; the BVH8 traversal (host build of the device code) returns the reference's LINEAR-scan hit for every one of
+    6 000 adversarial rays (distances bit for bit; ids but for equal-distance ties) -- i.e. also on the 11 rays where the
+    reference's own BVH2 disagrees with its linear scan; primary ids equal its BVH's; and the integrator core gives the reference's
+    fixed-seed image bit for bit."""
+    from cuda_pathtracer_b200 import scenegen
+    g = np.load(os.path.join(GOLDEN, "tree_vectors.npz"))
+    path = os.path.join(tmp_path, "tree.obj")
+    scenegen.write_tree_obj(path, pkg.parse_scene_file(os.path.join(SCENES, "cbox_quads.obj")), level=int(g["level"]))
+    prims = pkg.parse_scene_file(path)
+    _assert_prims_equal_reference_dump(prims, g["prims"])
+    for max_leaf in (1, 3):
+        s = emu.emu_scene_from_prims(P(prims), len(prims), max_leaf)
+        assert emu.emu_flat_units(s, None) == 0
+        rays = np.ascontiguousarray(g["rays"])
+        ids = np.zeros(len(rays), np.int32); ts = np.zeros(len(rays), np.float32)
+        emu.emu_trace(s, P(rays), len(rays), C.c_float(1e-4), P(ids), P(ts), None)
+        assert np.array_equal(bits(ts), bits(g["rays_lin_t"]))
+        assert (ids != g["rays_lin"]).sum() <= 30            # same distance to the bit, the neighbouring triangle across a shared edge
+        w = h = 160
+        v = cam_view(pkg, w, h)
+        pid = np.zeros((h, w), np.int32); pt = np.zeros((h, w), np.float32)
+        emu.emu_primary_ids(s, C.byref(v), P(pid), P(pt))
+        assert np.array_equal(bits(pt), bits(g["ids_t"])) and (pid != g["ids"]).sum() <= 4
+        v = cam_view(pkg, 48, 48)
+        lin = np.zeros((48, 48, 3), np.float32); seg = C.c_uint64()
+        emu.emu_render(s, C.byref(v), 4, 8, 2023, P(lin), None, C.byref(seg))
+        assert np.array_equal(bits(lin), bits(g["render_48x48_4spp_d8"]))
+        emu.emu_scene_free(s)
+
+
 def test_flat_units_reject_large_or_degenerate(pkg, emu):
     prims = pkg.parse_scene_file(os.path.join(SCENES, "cbox.obj"), subdivision=1)      # 128 triangles
     s = emu.emu_scene_from_prims(P(prims), len(prims), 3)

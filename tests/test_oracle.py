@@ -177,3 +177,41 @@ def test_guided_modes_without_grids_equal_bsdf_sampling(oracle):
     lin, _, _ = oracle.render_guided(s, 24, 20, 4, 5, 3)
     assert np.array_equal(bits(lin), bits(ref))
     oracle.free(s)
+
+
+# ---- a scene with a real tree: 2 566 primitives, goldens from the reference's host build (tests/golden/make_golden_tree.py) ----
+@pytest.fixture(scope="module")
+def tree(pkg, tmp_path_factory):
+    from cuda_pathtracer_b200 import scenegen
+    g = np.load(os.path.join(GOLDEN, "tree_vectors.npz"))
+    path = os.path.join(tmp_path_factory.mktemp("tree"), "tree.obj")
+    n = scenegen.write_tree_obj(path, pkg.parse_scene_file(os.path.join(SCENES, "cbox_quads.obj")), level=int(g["level"]))
+    assert n == len(g["prims"]) == 2566
+    return path, g
+
+
+def test_tree_scene_oracle_pinned_on_a_deep_bvh(oracle, tree):
+    """The oracle's loadOBJ, BVHBuilder (median split, padded boxes), Scene::intersect through the BVH2 AND the linear scan, and the
+    integrator on a 1 681-node tree: bit for bit what the reference's own code returns, including the 11 of 6 000 adversarial rays
+    where the reference's BVH and its linear scan disagree with each other."""
+    path, g = tree
+    s = oracle.load_obj(path)
+    prims, ref = oracle.prims(s), g["prims"]
+    assert np.array_equal(prims["type"], ref[:, 0].view(np.int32))
+    tri = prims["type"] == 0
+    v = prims["v"].reshape(len(prims), 12)
+    assert np.array_equal(bits(v[tri, :9]), bits(ref[tri, 1:10])) and np.array_equal(bits(v[~tri]), bits(ref[~tri, 1:13]))
+    assert np.array_equal(bits(prims["n"]), bits(ref[:, 13:16])) and np.array_equal(bits(prims["bsdf"]), bits(ref[:, 16:19]))
+    assert len(oracle.nodes(s)) == 1681
+    ids, ts = oracle.primary_ids(s, 160, 160)
+    assert np.array_equal(ids, g["ids"]) and np.array_equal(bits(ts), bits(g["ids_t"]))
+    rays = g["rays"][:2500]
+    for mode, key in ((0, "bvh"), (1, "lin")):
+        i, t = oracle.intersect(s, rays, mode=mode)
+        assert np.array_equal(i, g["rays_" + key][:2500])
+        hit = i >= 0
+        assert np.array_equal(bits(t[hit]), bits(g["rays_" + key + "_t"][:2500][hit]))
+    assert (g["rays_bvh"] != g["rays_lin"]).sum() == 11
+    lin, _, stats = oracle.render(s, 48, 48, 4, 8)
+    assert np.array_equal(bits(lin), bits(g["render_48x48_4spp_d8"]))
+    oracle.free(s)
