@@ -1457,7 +1457,16 @@ void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, con
     if (min_blocks == 0 && rng_mode == 0 && (unsigned long long)rp.n_owned < 3ull * (unsigned long long)sm_count * 3ull * kBlock) per_sm = 2;
     const int block = min_blocks == 7 ? 128 : kBlock;
     unsigned g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (items + block - 1) / block);
-    if (scene.inst != nullptr) {           // two-level scene: 2 CTAs per SM (the cursor carries the object-space ray as well)
+    if (scene.inst != nullptr) {
+        // two-level scene: the cursor carries the object-space ray as well.  3 CTAs per SM at 80 registers (66 bytes of spills in the
+        // compat build) beat 2 CTAs at 110: the kernel is latency-bound (ncu r2x on C5: issue slots 52 % busy at 16 warps per SM);
+        // C5 on one GPU 1 163 -> 1 292 M segments/s, counter RNG 1 201 -> 1 422 (profiles/r2y_c5_ab.log).  ctas_per_sm = 2 keeps the old form.
+        if (min_blocks != 2) {
+            g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * 3, (items + kBlock - 1) / kBlock);
+            if (rng_mode == 0) k_path_persist<0, kBlock, 3, false, false, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+            else k_path_persist<1, kBlock, 3, false, false, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+            return;
+        }
         g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * 2, (items + kBlock - 1) / kBlock);
         if (rng_mode == 0) k_path_persist<0, kBlock, 2, false, false, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
         else k_path_persist<1, kBlock, 2, false, false, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);

@@ -9,7 +9,14 @@ which = sys.argv[1]
 w, h, spp, depth, pipe, rng, minb = [int(x) for x in sys.argv[2:9]]
 frames = int(sys.argv[9]) if len(sys.argv) > 9 else 2
 with pkg.Context(0) as ctx:
-    if which.startswith("c3") or which == "c4":
+    cam = None
+    if which == "c5":                     # SURVEY 8(d) C5 as bench.py builds it: 305 instances x 327 680 triangles, two-level
+        from cuda_pathtracer_b200 import scenegen
+        scenegen.write_c5_pbrt("/tmp/c5_ncu.pbrt", instances=305, level=7)
+        scene = ctx.load_scene("/tmp/c5_ncu.pbrt", mirror_from_mtl=True, keep_instances=True)
+        room = 28.0
+        cam = pkg.look_at_camera((room / 2, room / 2, room * 1.9), (room / 2, room / 2, 0.0), (0.0, 1.0, 0.0), 40.0, w, h)
+    elif which.startswith("c3") or which == "c4":
         from cuda_pathtracer_b200 import scenegen
         base = pkg.parse_scene_file(os.path.join(ROOT, "scenes", "cbox_quads.obj"))
         if which == "c4":
@@ -19,7 +26,7 @@ with pkg.Context(0) as ctx:
             scene = ctx.scene_from_triangles(tris, mat, mats, builder=0)
     else:
         scene = ctx.load_scene(os.path.join(ROOT, "scenes", "cbox.obj" if which == "c1" else "cbox_quads.obj"))
-    cam = pkg.default_camera(w, h)
+    cam = cam or pkg.default_camera(w, h)
     film = ctx.create_film(w, h)
     for rep in range(frames):
         st = ctx.render(scene, cam, film, spp=spp, max_depth=depth, pipeline=pipe, rng_mode=rng, loop_min_blocks=minb)
