@@ -1455,12 +1455,25 @@ void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, con
     // default: with the sequential RNG and fewer than ~3 pixels per resident lane the frame is bounded by its longest pixel
     // chain, not by throughput -- two CTAs per SM finish such a frame sooner (C2, 1/8 of the film: 38 vs 43 ms)
     if (min_blocks == 0 && rng_mode == 0 && (unsigned long long)rp.n_owned < 3ull * (unsigned long long)sm_count * 3ull * kBlock) per_sm = 2;
+    // counter RNG on a large scene: its build fits 64 registers without spills, and the latency-bound traversal gains from 32 warps
+    // per SM (C3: 7 505 -> 8 046 M segments/s; the compat build spills 158 bytes at 64 registers and loses 7.5 %: profiles/r2y3_c3_minb4_pair.log)
+    if (min_blocks == 0 && rng_mode != 0 && pair) per_sm = 4;
     const int block = min_blocks == 7 ? 128 : kBlock;
     unsigned g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (items + block - 1) / block);
     if (scene.inst != nullptr) {
         // two-level scene: the cursor carries the object-space ray as well.  3 CTAs per SM at 80 registers (66 bytes of spills in the
         // compat build) beat 2 CTAs at 110: the kernel is latency-bound (ncu r2x on C5: issue slots 52 % busy at 16 warps per SM);
         // C5 on one GPU 1 163 -> 1 292 M segments/s, counter RNG 1 201 -> 1 422 (profiles/r2y_c5_ab.log).  ctas_per_sm = 2 keeps the old form.
+        if (min_blocks == 0 || min_blocks == 4) {
+            // default: 4 CTAs per SM at 64 registers (260 bytes of spills in the compat build, 74 with the counter RNG): C5 on one GPU
+            // 1 293 -> 1 338 M segments/s, counter RNG 1 423 -> 1 440 (profiles/r2y2_c5_ab.log); ctas_per_sm = 3 / 2 keep the other forms.
+            // (Keeping the cold per-pixel state -- running sum, pixel coordinates, counters: 8 registers -- in shared memory instead cut
+            //  the spills to 196 bytes but gave 1 288: the 32 KB carve-out comes out of L1.  profiles/r2y4_c5_cold.log)
+            g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * 4, (items + kBlock - 1) / kBlock);
+            if (rng_mode == 0) k_path_persist<0, kBlock, 4, false, false, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+            else k_path_persist<1, kBlock, 4, false, false, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+            return;
+        }
         if (min_blocks != 2) {
             g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * 3, (items + kBlock - 1) / kBlock);
             if (rng_mode == 0) k_path_persist<0, kBlock, 3, false, false, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
@@ -1478,7 +1491,10 @@ void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, con
         k_path_persist<0, kBlock, 3, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
         return;
     }
-    if (per_sm == 4) {
+    if (per_sm == 4 && pair) {
+        if (rng_mode == 0) k_path_persist<0, kBlock, 4, false, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+        else k_path_persist<1, kBlock, 4, false, true><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
+    } else if (per_sm == 4) {
         if (rng_mode == 0) k_path_persist<0, kBlock, 4><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
         else k_path_persist<1, kBlock, 4><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
     } else if (per_sm == 7) {
