@@ -1512,7 +1512,7 @@ void launch_path_flat(cudaStream_t st, int rng_mode, const WaveState& ws, const 
                       const CameraView& cam, const RenderParams& rp, int sm_count, int per_sm) {
     if (rp.spp <= 0 || !rp.n_owned) return;
     const unsigned long long items = rng_mode == 0 ? (unsigned long long)rp.n_owned : rp.total_paths;
-    if (per_sm != 2 && per_sm != 4) per_sm = 3;
+    if (per_sm != 1 && per_sm != 2 && per_sm != 4) per_sm = 3;      // 1: probe only (how fast does a lone sample chain run?)
     // few pixels per resident lane (a tile-sharded frame on many GPUs): fewer warps per SM, so every pixel's sequential
     // sample chain advances faster (see launch_path_persist)
     unsigned g = (unsigned)std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (items + kBlock - 1) / kBlock);
