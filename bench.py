@@ -200,7 +200,7 @@ class Run:
         self.rgb_host = np.empty((self.h, self.w, 3), np.uint8)
         self.kw = dict(spp=spp, max_depth=depth, rng_mode=self.rng_mode, pipeline=pipeline, shard_mode=self.shard_mode, shard_rank=rank, shard_world=world,
                        loop_min_blocks=args.min_blocks, chunks=args.chunks, shade_batch=args.shade_batch,
-                       cost_order=not getattr(args, "no_cost_order", False))
+                       cost_order=not getattr(args, "no_cost_order", False), bounds_cull=not getattr(args, "no_cull", False))
 
     def barrier(self):
         self.ctx.sync()
@@ -229,14 +229,15 @@ class Run:
         # ---- timed region A: inputs resident in HBM, device events on the launching stream
         self.barrier()
         self.ctx.timer_start()
-        seg = launches = 0
+        seg = launches = culled = 0
         for _ in range(steps):
             st = self.step(False)
+            culled += st.get("culled_paths", 0)
             seg += st["segments"]; launches += st["kernel_launches"] + 1 + (3 if self.shard_mode == pkg.SHARD_TILES else (1 if self.world > 1 else 0))
         ms_dev = self.ctx.timer_stop()
         self.barrier()
         # ---- timed region B: end to end through the C ABI with host buffers
-        seg_e2e, ms_e2e = 0, 0.0
+        seg_e2e, ms_e2e, culled_e2e = 0, 0.0, 0
         if e2e:
             self.barrier()
             t0 = time.perf_counter()
@@ -244,20 +245,28 @@ class Run:
                 if self.default_cam:
                     self.cam = pkg.default_camera(self.w, self.h)    # host camera update + by-value upload, like renderFrame (application.h:161-164)
                 st = self.step(True)
-                seg_e2e += st["segments"]
+                seg_e2e += st["segments"]; culled_e2e += st.get("culled_paths", 0)
             self.ctx.sync()
             ms_e2e = (time.perf_counter() - t0) * 1e3
             self.barrier()
-        out = dict(seg=seg, seg_e2e=seg_e2e, ms_dev=ms_dev, ms_e2e=ms_e2e, launches=launches)
+        out = dict(seg=seg, seg_e2e=seg_e2e, ms_dev=ms_dev, ms_e2e=ms_e2e, launches=launches, culled=culled)
         if self.world > 1:
-            t = self.torch.tensor([float(seg), float(seg_e2e)], dtype=self.torch.float64, device="cuda")
+            t = self.torch.tensor([float(seg), float(seg_e2e), float(culled), float(culled_e2e)], dtype=self.torch.float64, device="cuda")
             self.dist.all_reduce(t)
+            out.update(culled=t[2].item())
+            culled_e2e = t[3].item()
             m = self.torch.tensor([ms_dev, ms_e2e], dtype=self.torch.float64, device="cuda")
             self.dist.all_reduce(m, op=self.dist.ReduceOp.MAX)
             out.update(seg=t[0].item(), seg_e2e=t[1].item(), ms_dev=m[0].item(), ms_e2e=m[1].item())
         out["value"] = out["seg"] / (out["ms_dev"] * 1e-3) * 1e-6
         out["e2e_value"] = out["seg_e2e"] / (out["ms_e2e"] * 1e-3) * 1e-6 if e2e else None
         out["ms_per_step"] = out["ms_dev"] / steps
+        # whole-pixel culling (ptx_render): the frame's paths whose every ray misses the scene's bounds are resolved without tracing;
+        # `value` counts the WORKLOAD's segments (what the reference traces for this frame), value_traced only the traced ones
+        out["value_traced"] = (out["seg"] - out["culled"]) / (out["ms_dev"] * 1e-3) * 1e-6
+        out["e2e_value_traced"] = (out["seg_e2e"] - culled_e2e) / (out["ms_e2e"] * 1e-3) * 1e-6 if e2e else None
+        out["culled_per_step"] = out["culled"] / steps
+        out["seg_per_step"] = out["seg"] / steps
         return out
 
     def check_against_unsharded(self):
@@ -307,8 +316,9 @@ def roofline_of(run, m, st_t, args, clocks, sm_count):
     n_chunks = compat_chunk_count(run.spp, args.chunks, n_px / (sm_count * 768.0))
     # per owned pixel and sample chunk: pixel id 4 + RNG state 24 + 24 + pixel sum 16 + 16 + progress flag 4 + 4; counter RNG: pixel id 4 + three float atomics 12 per path
     per_item = 92.0 * n_chunks * n_px if run.rng_mode == pkg.RNG_XORWOW_COMPAT else 16.0 * st_t["paths"]
-    bytes_per_seg = per_item / max(st_t["segments"], 1)
-    seg_per_s = st_t["segments"] / (k_ms * 1e-3) if k_ms > 0 else 0.0
+    bytes_per_seg = per_item / max(st_t["segments"] - st_t.get("culled_paths", 0), 1)
+    traced = st_t["segments"] - st_t.get("culled_paths", 0)          # the roofline is about what the kernel executes: traced segments only
+    seg_per_s = traced / (k_ms * 1e-3) if k_ms > 0 else 0.0
     tkey = f"{run.workload}/{'philox' if run.rng_mode == pkg.RNG_PHILOX else 'compat'}/{'flat' if is_flat else 'persist'}"
     ent = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
@@ -321,8 +331,14 @@ def roofline_of(run, m, st_t, args, clocks, sm_count):
         st_c = ctx.render(run.scene, run.cam, run.film, count_work=True, **kwc)
         n_node, n_tri = st_c["node_visits"] / max(st_c["segments"], 1), st_c["tri_tests"] / max(st_c["segments"], 1)
         bps = n_node * 80 + n_tri * 48
-        achieved = seg_per_s * bps * 1e-9
+        # the instrumented run traces EVERY segment of the frame; the timed kernel does not trace the culled ones (whole-pixel culling),
+        # each of which would have cost exactly one node visit (the root, all children missed): take those 80 bytes out
+        f_culled = st_t.get("culled_paths", 0) / max(st_t["segments"], 1)
+        all_per_s = st_t["segments"] / (k_ms * 1e-3) if k_ms > 0 else 0.0
+        bps_exec = bps - f_culled * 80.0
+        achieved = all_per_s * bps_exec * 1e-9
         return dict(common, bound="hbm", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak, peak_source=peak_src, bytes_per_segment=bps,
+                    bytes_per_segment_executed=bps_exec, culled_fraction_of_segments=f_culled,
                     traversal={"nodes_per_segment": n_node, "tris_per_segment": n_tri, "node_bytes": 80, "tri_bytes": 48})
     hbm = {"achieved": seg_per_s * bytes_per_seg * 1e-9, "peak": peak, "unit": "GB/s", "frac": seg_per_s * bytes_per_seg * 1e-9 / peak, "peak_source": peak_src,
            "bytes_per_segment": bytes_per_seg, "note": "algorithmic HBM bytes of a kernel that keeps all path state in registers: not the bound"}
@@ -424,6 +440,14 @@ def run_ours(args, w, h, spp, depth):
             "e2e": {"value": m["e2e_value"], "unit": METRIC, "h2d_bytes_per_step": ctypes.sizeof(pkg.Camera), "d2h_bytes_per_step": w * h * 3,
                     "ms_per_step": m["ms_e2e"] / args.steps},
             "gpu_launches": m["launches"],
+            "culling": {"what": "whole-pixel culling in ptx_render (on by default): pixels none of whose camera rays can reach the scene's bounding box are not traced; "
+                                "their XORWOW streams are advanced by 2 * spp draws and their film sums left alone, so film and RNG state equal the traced frame's bit for bit "
+                                "(tests: test_whole_pixel_culling_keeps_film_and_rng_state, the full-size comparisons with the reference's CUDA kernels). "
+                                "`value` and `e2e.value` count the WORKLOAD's path segments (what the reference traces for this frame: its kernels trace every one); "
+                                "value_traced_only counts only the segments this build traced; the roofline is computed from the traced ones",
+                        "segments_per_step": m["seg_per_step"], "culled_paths_per_step": m["culled_per_step"],
+                        "traced_segments_per_step": m["seg_per_step"] - m["culled_per_step"],
+                        "value_traced_only": m["value_traced"], "e2e_value_traced_only": m["e2e_value_traced"]},
             "roofline": roof,
             "scene": {k: scene_stats[k] for k in ("n_triangles", "n_nodes", "node_bytes", "triangle_bytes", "build_ms", "builder", "max_depth", "sah_cost", "flat_units")},
         }
@@ -508,6 +532,7 @@ def main():
     ap.add_argument("--min-blocks", type=int, default=0, help="experiment: occupancy variant of the path-loop kernels (0 = 3x256 threads/SM, 4 = 4x256, 7 = 7x128)")
     ap.add_argument("--chunks", type=int, default=0, help="experiment: work items per pixel of the persistent kernel, compat RNG (0 = default 6, 1 = none)")
     ap.add_argument("--shade-batch", type=int, default=0, help="experiment: waiting lanes per warp that trigger a shading round (0 = default 12, 1 = at once)")
+    ap.add_argument("--no-cull", action="store_true", help="experiment: trace every pixel (PTX_RENDER_NO_BOUNDS_CULL)")
     ap.add_argument("--no-cost-order", action="store_true", help="experiment: hand out the work items in film order instead of longest-expected first")
     ap.add_argument("--max-leaf", type=int, default=0, help="experiment: triangles per BVH8 leaf slot (1..3; 0 = library default)")
     args = ap.parse_args()

@@ -15,7 +15,7 @@ LIB_PATH = os.environ.get("PTX_LIB") or os.path.join(HERE, "libptx.so")      # P
 RNG_XORWOW_COMPAT, RNG_PHILOX = 0, 1
 SHARD_NONE, SHARD_TILES, SHARD_SAMPLES = 0, 1, 2
 NOALLOC_MAX_RAYS = 65536
-RENDER_STAGE_TIMING, RENDER_COUNT_WORK, RENDER_ASYNC, RENDER_SORT_RAYS, RENDER_SORT_MATERIAL, RENDER_NO_COST_ORDER = 1, 2, 4, 8, 16, 32
+RENDER_STAGE_TIMING, RENDER_COUNT_WORK, RENDER_ASYNC, RENDER_SORT_RAYS, RENDER_SORT_MATERIAL, RENDER_NO_COST_ORDER, RENDER_NO_BOUNDS_CULL = 1, 2, 4, 8, 16, 32, 64
 PIPELINE_DEFAULT, PIPELINE_FUSED, PIPELINE_LOOP, PIPELINE_PERSIST, PIPELINE_WAVEFRONT, PIPELINE_CTA, PIPELINE_FLAT = 0, 1, 2, 3, 4, 5, 6
 SAMPLING_BSDF, SAMPLING_FORMFACTOR, SAMPLING_RADIOSITY, SAMPLING_MIS, SAMPLING_TOPK = 0, 1, 2, 3, 4
 
@@ -74,7 +74,7 @@ class RenderOpts(C.Structure):
 class RenderStats(C.Structure):
     _fields_ = [("segments", C.c_uint64), ("paths", C.c_uint64), ("iterations", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("compactions", C.c_uint64), ("render_ms", C.c_float), ("extend_ms", C.c_float), ("shade_ms", C.c_float),
-                ("other_ms", C.c_float), ("node_visits", C.c_uint64), ("tri_tests", C.c_uint64), ("slot_launches", C.c_uint64)]
+                ("other_ms", C.c_float), ("node_visits", C.c_uint64), ("tri_tests", C.c_uint64), ("slot_launches", C.c_uint64), ("culled_paths", C.c_uint64)]
 
 
 EXPORTS = [
@@ -282,12 +282,12 @@ class Context:
 
     # -- rendering ----------------------------------------------------------------------------
     def render(self, scene, camera, film, spp, max_depth=5, rng_mode=RNG_XORWOW_COMPAT, accumulate=False, shard_mode=SHARD_NONE,
-               shard_rank=0, shard_world=1, pipeline=PIPELINE_DEFAULT, stage_timing=False, count_work=False, sampling_mode=0, loop_iters=0, loop_min_blocks=0, chunks=0, shade_batch=0, async_=False, sort_rays=False, sort_material=False, cost_order=True):
+               shard_rank=0, shard_world=1, pipeline=PIPELINE_DEFAULT, stage_timing=False, count_work=False, sampling_mode=0, loop_iters=0, loop_min_blocks=0, chunks=0, shade_batch=0, async_=False, sort_rays=False, sort_material=False, cost_order=True, bounds_cull=True):
         o = RenderOpts()
         o.spp, o.max_depth, o.rng_mode, o.sampling_mode = int(spp), int(max_depth), int(rng_mode), int(sampling_mode)
         o.accumulate, o.shard_mode, o.shard_rank, o.shard_world = int(accumulate), int(shard_mode), int(shard_rank), int(shard_world)
         o.pipeline = int(pipeline)
-        o.flags = (RENDER_STAGE_TIMING if stage_timing else 0) | (RENDER_COUNT_WORK if count_work else 0) | (RENDER_ASYNC if async_ else 0) | (RENDER_SORT_RAYS if sort_rays else 0) | (RENDER_SORT_MATERIAL if sort_material else 0) | (0 if cost_order else RENDER_NO_COST_ORDER)
+        o.flags = (RENDER_STAGE_TIMING if stage_timing else 0) | (RENDER_COUNT_WORK if count_work else 0) | (RENDER_ASYNC if async_ else 0) | (RENDER_SORT_RAYS if sort_rays else 0) | (RENDER_SORT_MATERIAL if sort_material else 0) | (0 if cost_order else RENDER_NO_COST_ORDER) | (0 if bounds_cull else RENDER_NO_BOUNDS_CULL)
         o.loop_iters = int(loop_iters)
         o.ctas_per_sm = int(loop_min_blocks)
         o.chunks = int(chunks)

@@ -52,6 +52,11 @@ struct ptx_ctx {
     // ws.slot_pixel points at d_slot_base (canonical order: what ptx_film_combine packs by) or at d_slot_sorted (cost order)
     uint32_t* d_slot_base = nullptr; uint32_t* d_slot_sorted = nullptr; uint32_t* d_cost_keys[2] = {nullptr, nullptr}; uint32_t* d_cost_vals = nullptr;
     void* d_cost_tmp = nullptr; size_t cost_tmp_bytes = 0;
+    // whole-pixel culling (ptx_render): compacted list of the pixels that can see the scene, owned rows before each row, T^n
+    uint32_t* d_slot_active = nullptr; uint32_t* d_cull_rows = nullptr; uint32_t cull_rows_capacity = 0;
+    uint32_t* d_skip = nullptr; uint64_t skip_n = 0;
+    std::vector<uint32_t> h_cull_rows;
+    unsigned long long culled_paths = 0;        // paths (= segments) of the last render that were resolved by culling
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, tev0 = nullptr, tev1 = nullptr;
     std::vector<cudaEvent_t> stage_events;
     ptx_render_stats stats{};
@@ -152,9 +157,9 @@ void ptx_ctx_destroy(ptx_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     cudaFree(c->ws.A); cudaFree(c->ws.B); cudaFree(c->ws.C); cudaFree(c->ws.D); cudaFree(c->ws.E);
-    cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]); cudaFree(c->d_slot_base); cudaFree(c->d_slot_sorted); cudaFree(c->d_cost_keys[0]); cudaFree(c->d_cost_keys[1]);
+    cudaFree(c->ws.queue[0]); cudaFree(c->ws.queue[1]); cudaFree(c->d_slot_base); cudaFree(c->d_slot_sorted); cudaFree(c->d_slot_active); cudaFree(c->d_cost_keys[0]); cudaFree(c->d_cost_keys[1]);
     cudaFree(c->d_cost_vals); cudaFree(c->d_cost_tmp); cudaFree(c->ws.progress); cudaFree(c->ws.counters); cudaFree(c->d_flush);
-    cudaFree(c->d_scratch); cudaFree(c->d_jump); cudaFree(c->d_sort_keys[0]); cudaFree(c->d_sort_keys[1]); cudaFree(c->d_sort_tmp);
+    cudaFree(c->d_scratch); cudaFree(c->d_jump); cudaFree(c->d_cull_rows); cudaFree(c->d_skip); cudaFree(c->d_sort_keys[0]); cudaFree(c->d_sort_keys[1]); cudaFree(c->d_sort_tmp);
     cudaFreeHost(c->h_counters);
     for (auto ev : c->stage_events) cudaEventDestroy(ev);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -173,7 +178,8 @@ static int finalize_pending(ptx_ctx* c) {
     const unsigned long long* hc = c->h_counters;
     cudaEventElapsedTime(&c->stats.render_ms, c->ev0, c->ev1);
     c->stats.shade_ms = c->stats.render_ms;
-    c->stats.segments = hc[CTR_SEGMENTS]; c->stats.paths = hc[CTR_PATHS];
+    c->stats.segments = hc[CTR_SEGMENTS] + c->culled_paths; c->stats.paths = hc[CTR_PATHS] + c->culled_paths;
+    c->stats.culled_paths = c->culled_paths;
     return PTX_OK;
 }
 
@@ -800,11 +806,11 @@ int ensure_wave_capacity(ptx_ctx* c, uint32_t slots, uint32_t owned) {
 int ensure_pixmap(ptx_ctx* c, uint32_t owned, uint32_t film_pixels) {
     if (owned > c->pixmap_capacity) {
         PTX_CUDA(c, cudaStreamSynchronize(c->stream));
-        cudaFree(c->d_slot_base); cudaFree(c->d_slot_sorted); cudaFree(c->d_cost_keys[0]); cudaFree(c->d_cost_keys[1]); cudaFree(c->d_cost_vals); cudaFree(c->d_cost_tmp);
-        c->d_slot_base = c->d_slot_sorted = c->d_cost_keys[0] = c->d_cost_keys[1] = c->d_cost_vals = nullptr; c->d_cost_tmp = nullptr;
+        cudaFree(c->d_slot_base); cudaFree(c->d_slot_sorted); cudaFree(c->d_slot_active); cudaFree(c->d_cost_keys[0]); cudaFree(c->d_cost_keys[1]); cudaFree(c->d_cost_vals); cudaFree(c->d_cost_tmp);
+        c->d_slot_base = c->d_slot_sorted = c->d_slot_active = c->d_cost_keys[0] = c->d_cost_keys[1] = c->d_cost_vals = nullptr; c->d_cost_tmp = nullptr;
         c->ws.slot_pixel = nullptr; c->pixmap_capacity = 0; c->slot_key[0] = -1;
         const size_t bytes = (size_t)owned * sizeof(uint32_t);
-        PTX_CUDA(c, cudaMalloc(&c->d_slot_base, bytes)); PTX_CUDA(c, cudaMalloc(&c->d_slot_sorted, bytes));
+        PTX_CUDA(c, cudaMalloc(&c->d_slot_base, bytes)); PTX_CUDA(c, cudaMalloc(&c->d_slot_sorted, bytes)); PTX_CUDA(c, cudaMalloc(&c->d_slot_active, bytes));
         PTX_CUDA(c, cudaMalloc(&c->d_cost_keys[0], bytes)); PTX_CUDA(c, cudaMalloc(&c->d_cost_keys[1], bytes)); PTX_CUDA(c, cudaMalloc(&c->d_cost_vals, bytes));
         size_t need = 0;
         PTX_CUDA(c, cub::DeviceRadixSort::SortPairs(nullptr, need, c->d_cost_keys[0], c->d_cost_keys[1], c->d_cost_vals, c->d_slot_sorted, (int)owned, 0, 8, c->stream));
@@ -938,17 +944,67 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
         flat_margins(scale, fs.m0, fs.m1);
         fs.key_mask = kFlatKeyMask;
     }
+    // Whole-pixel culling (persistent pipelines).  A pixel all of whose camera rays miss the scene's bounding box contributes nothing:
+    // each of its samples draws the two jitter numbers, misses and ends (integrator.h:384-385, 199-201).  Such pixels are taken off
+    // the work list; with the sequential RNG their streams are advanced by 2 * spp draws (k_cull_pixels), so the film AND the RNG state
+    // after the frame are what tracing them leaves, bit for bit.  Their paths / segments are counted in the statistics (and
+    // separately in culled_paths).  The test is conservative: the screen rectangle of the projected bounds, 2 pixels of margin; any
+    // corner behind the camera turns it off (cull.h).
+    PTX_CUDA(c, cudaEventRecord(c->ev0, c->stream));       // render_ms covers the cull, the cost probe + sort and the path kernel
+    c->culled_paths = 0;
+    int pre_launches = 0;                                  // own kernels launched before the path kernel (cull, cost probe)
+    CullRect cull{0, 0, w, h};
+    if (persist && rp.spp > 0 && rp.n_owned > 0 && !(opts->flags & PTX_RENDER_NO_BOUNDS_CULL) && cull_rect(*cam, scene->stats.bounds_min, scene->stats.bounds_max, w, h, cull)) {
+        const int rw = cull.x1 - cull.x0;
+        c->h_cull_rows.assign((size_t)h, 0u);
+        uint32_t rows = 0;
+        for (int y = 0; y < h; y++) {
+            c->h_cull_rows[(size_t)y] = rows;
+            const bool owned = shard_mode != PTX_SHARD_TILES || world <= 1 || (y / kBandRows) % world == rank;
+            if (owned && y >= cull.y0 && y < cull.y1) rows++;
+        }
+        const uint32_t n_active = rows * (uint32_t)rw;
+        if ((unsigned long long)n_active * 16ull < (unsigned long long)rp.n_owned * 15ull) {      // worth it: more than 1/16 of the pixels go
+            if ((uint32_t)h > c->cull_rows_capacity) {
+                cudaFree(c->d_cull_rows); c->d_cull_rows = nullptr; c->cull_rows_capacity = 0;
+                PTX_CUDA(c, cudaMalloc(&c->d_cull_rows, (size_t)h * sizeof(uint32_t)));
+                c->cull_rows_capacity = (uint32_t)h;
+            }
+            PTX_CUDA(c, cudaMemcpyAsync(c->d_cull_rows, c->h_cull_rows.data(), (size_t)h * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+            const uint32_t* skip = nullptr; uint32_t weyl = 0;
+            if (rng_mode == PTX_RNG_XORWOW_COMPAT) {
+                const uint64_t n = 2ull * (uint64_t)rp.spp;
+                if (!c->d_skip) PTX_CUDA(c, cudaMalloc(&c->d_skip, sizeof(uint32_t) * kXorwowJumpWords));
+                if (c->skip_n != n) {
+                    std::vector<uint32_t> m((size_t)kXorwowJumpWords);
+                    xorwow_build_skip_matrix(n, m.data());
+                    PTX_CUDA(c, cudaStreamSynchronize(c->stream));       // an earlier frame may still read the old matrix
+                    PTX_CUDA(c, cudaMemcpy(c->d_skip, m.data(), sizeof(uint32_t) * kXorwowJumpWords, cudaMemcpyHostToDevice));
+                    c->skip_n = n;
+                }
+                skip = c->d_skip; weyl = (uint32_t)(362437ull * n);
+            }
+            launch_cull_pixels(c->stream, film->view(), c->d_slot_base, rp.n_owned, cull, c->d_cull_rows, skip, weyl, c->d_slot_active);
+            PTX_CUDA(c, cudaGetLastError());
+            pre_launches++;
+            c->culled_paths = (unsigned long long)(rp.n_owned - n_active) * (unsigned long long)rp.spp;
+            c->ws.slot_pixel = c->d_slot_active;
+            rp.n_owned = n_active;
+            rp.total_paths = (unsigned long long)n_active * (unsigned long long)rp.spp;
+        }
+    }
     // Work order, sequential RNG: the longest-expected pixels first (kernels.cu k_pixel_cost), so that no long sample chain starts late.
     // Costs 2 probe paths per pixel (0.2 % of a 1 024-spp frame) + an 8-bit radix sort; only the order of the work changes.
     // On a tree (not the flat list) consecutive pixels share nodes in L1 / L2, which the cost order breaks up: C3 at 1080p is 0.9 % faster in
     // film order (profiles/r2s_cost_order_c3.log), so there the order is only used when a lane gets few pixels (sharded / small frames).
     const bool order_pays = flat || (unsigned long long)rp.n_owned < 8ull * (unsigned long long)c->prop.multiProcessorCount * 3ull * 256ull;
     if (persist && !cta_wave && rng_mode == PTX_RNG_XORWOW_COMPAT && rp.spp >= 64 && rp.n_owned > 0 && !scene->view.inst && order_pays && !(opts->flags & PTX_RENDER_NO_COST_ORDER)) {
-        launch_pixel_cost(c->stream, scene->view, flat ? &fs : nullptr, cv, rp.shade, c->d_slot_base, rp.n_owned, c->d_cost_keys[0], c->d_cost_vals);
+        launch_pixel_cost(c->stream, scene->view, flat ? &fs : nullptr, cv, rp.shade, c->ws.slot_pixel, rp.n_owned, c->d_cost_keys[0], c->d_cost_vals);
         PTX_CUDA(c, cudaGetLastError());
         size_t tmp = c->cost_tmp_bytes;
         PTX_CUDA(c, cub::DeviceRadixSort::SortPairs(c->d_cost_tmp, tmp, c->d_cost_keys[0], c->d_cost_keys[1], c->d_cost_vals, c->d_slot_sorted, (int)rp.n_owned, 0, 8, c->stream));
         c->ws.slot_pixel = c->d_slot_sorted;
+        pre_launches++;                                    // k_pixel_cost (the radix sort's kernels are cub's, not counted)
     }
     FilmView fv = film->view();
     const bool fused = pipeline == 1;
@@ -968,7 +1024,7 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     const bool async = persist && (opts->flags & PTX_RENDER_ASYNC) != 0;
 
     ptx_render_stats st{};
-    PTX_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    st.kernel_launches = (uint64_t)pre_launches;
     if (persist) {      // one launch for the whole frame: items are pulled from CTR_NEXT_PATH, nothing else to drive
         if (rng_mode == PTX_RNG_XORWOW_COMPAT && rp.n_owned) PTX_CUDA(c, cudaMemsetAsync(c->ws.progress, 0, (size_t)w * h * sizeof(uint32_t), c->stream));
         if (flat) {
@@ -979,9 +1035,12 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
                 // faster the fewer warps share its SM: when a rank owns few pixels per resident lane AND the chains are long
                 // (spp >= 512: a tile-sharded 1080p frame on 8 GPUs) 2 CTAs finish sooner; short chains (C1: 64 spp, 2.3
                 // pixels per lane) are throughput-bound again and want 3 (23.5 against 19.7 G with 2, 20.5 with 4).
+                // With whole-pixel culling n_owned counts only the pixels that can see the scene -- all of them long chains on the Cornell
+                // frames -- and the thresholds were re-measured on one rank of 1 / 2 / 4 / 8 (7.7 / 3.8 / 1.9 / 0.96 such pixels per lane;
+                // profiles/r2ad_shard_probe_cull.log): 4 CTAs 99.0 / 53.0 / 32.2 / 19.4 ms, 3 CTAs 101.1 / 50.8 / 26.3 / 19.1, 2 CTAs - / 56.9 / 29.3 / 15.3.
                 const double px_per_lane = (double)rp.n_owned / ((double)c->prop.multiProcessorCount * 768.0);
-                if (rng_mode == 0 && px_per_lane < 3.0) per_sm = rp.spp >= 512 ? 2 : 3;
-                else per_sm = px_per_lane >= 8.0 ? 4 : 3;
+                if (rng_mode == 0 && px_per_lane < 1.5 && rp.spp >= 512) per_sm = 2;
+                else per_sm = px_per_lane >= 6.0 ? 4 : 3;
             }
             launch_path_flat(c->stream, rng_mode, c->ws, scene->view, fs, fv, cv, rp, c->prop.multiProcessorCount, per_sm);
         }
@@ -1088,7 +1147,8 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     PTX_CUDA(c, cudaGetLastError());
     cudaEventElapsedTime(&st.render_ms, c->ev0, c->ev1);
     if (persist) st.shade_ms = st.render_ms;               // the one kernel is the whole render
-    st.segments = hc[CTR_SEGMENTS]; st.paths = hc[CTR_PATHS];
+    st.segments = hc[CTR_SEGMENTS] + c->culled_paths; st.paths = hc[CTR_PATHS] + c->culled_paths;
+    st.culled_paths = c->culled_paths;
     st.other_ms = st.render_ms - st.extend_ms - st.shade_ms;
     st.node_visits = hc[CTR_NODE_VISITS]; st.tri_tests = hc[CTR_TRI_TESTS]; st.slot_launches = hc[CTR_SLOT_LAUNCHES];
     c->stats = st;

@@ -85,6 +85,30 @@ __global__ void __launch_bounds__(kBlock) k_slot_pixels(uint32_t* slot_pixel, in
     slot_pixel[i] = band * band_px + within;
 }
 
+// Whole-pixel culling: see launch_cull_pixels (kernels.cuh).  A culled pixel's samples all miss the scene (its rays lie outside the
+// projection of the scene's bounds: api.cu cull_rect), so each consumes exactly the two jitter draws (integrator.h:384-385) and adds
+// nothing to the film: the pixel's stream is advanced by 2 * spp draws with one GF(2) matrix product and its running sum is left alone
+// -- the film and the RNG state are what tracing the pixel leaves behind, bit for bit.
+__global__ void __launch_bounds__(kBlock) k_cull_pixels(FilmView film, const uint32_t* __restrict__ slot_base, uint32_t n_owned, CullRect r,
+                                                        const uint32_t* __restrict__ row_prefix, const uint32_t* __restrict__ skip, uint32_t weyl_add,
+                                                        uint32_t* __restrict__ slot_active) {
+    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+    if (i >= n_owned) return;
+    const uint32_t p = slot_base[i];
+    const int x = (int)(p % (uint32_t)film.width), y = (int)(p / (uint32_t)film.width);
+    if (x >= r.x0 && x < r.x1 && y >= r.y0 && y < r.y1) {
+        slot_active[row_prefix[y] * (uint32_t)(r.x1 - r.x0) + (uint32_t)(x - r.x0)] = p;
+        return;
+    }
+    if (skip == nullptr) return;
+    uint4 a = film.rngA[p]; uint2 b = film.rngB[p];
+    Xorwow s{a.x, a.y, a.z, a.w, b.x, b.y};
+    xorwow_apply(s, skip);
+    s.d += weyl_add;
+    film.rngA[p] = make_uint4(s.v0, s.v1, s.v2, s.v3);
+    film.rngB[p] = make_uint2(s.v4, s.d);
+}
+
 __device__ __forceinline__ void store_vertex(const WaveState& ws, uint32_t slot, const PathVertex& pv, uint32_t flags) {
     ws.A[slot] = make_float4(pv.o.x, pv.o.y, pv.o.z, pv.d.x);
     ws.B[slot] = make_float4(pv.d.y, pv.d.z, __uint_as_float((uint32_t)pv.depth | flags), pv.beta.x);
@@ -1507,6 +1531,11 @@ void launch_path_persist(cudaStream_t st, int rng_mode, const WaveState& ws, con
         if (rng_mode == 0) k_path_persist<0, kBlock, 3><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
         else k_path_persist<1, kBlock, 3><<<g, kBlock, 0, st>>>(ws, scene, film, cam, rp);
     }
+}
+void launch_cull_pixels(cudaStream_t st, FilmView film, const uint32_t* slot_base, uint32_t n_owned, CullRect rect, const uint32_t* row_prefix,
+                        const uint32_t* skip, uint32_t weyl_add, uint32_t* slot_active) {
+    if (!n_owned) return;
+    k_cull_pixels<<<(n_owned + kBlock - 1) / kBlock, kBlock, 0, st>>>(film, slot_base, n_owned, rect, row_prefix, skip, weyl_add, slot_active);
 }
 void launch_path_flat(cudaStream_t st, int rng_mode, const WaveState& ws, const SceneView& scene, const FlatScene& fs, const FilmView& film,
                       const CameraView& cam, const RenderParams& rp, int sm_count, int per_sm) {

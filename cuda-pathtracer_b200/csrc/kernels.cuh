@@ -15,6 +15,7 @@
 // load/store per lane:
 //   A = { o.x, o.y, o.z, d.x }   B = { d.y, d.z, depth|flags, beta.r }   C = { beta.g, beta.b, hit_t, hit_prim }
 #pragma once
+#include "cull.h"
 #include <cuda_runtime.h>
 
 #include "flat.h"
@@ -114,6 +115,12 @@ void launch_occluded(cudaStream_t st, const SceneView& scene, const float* segs,
 void launch_visibility(cudaStream_t st, const SceneView& scene, const FilmView& film, const CameraView& cam, int spp, const float* radiosity,
                        uint8_t* rgb8);
 void launch_slot_pixels(cudaStream_t st, uint32_t* slot_pixel, int w, int h, int shard_mode, int rank, int world, uint32_t n_owned);
+// Empty-space culling of whole pixels (api.cu, ptx_render): the owned pixels inside the screen rectangle [x0, x1) x [y0, y1) are
+// compacted, in slot order, into slot_active (position = row_prefix[y] * (x1 - x0) + x - x0, row_prefix = owned rows in [y0, y));
+// every pixel outside has its XORWOW stream advanced by the draws its samples would have consumed (skip = T^n as 800 words, the
+// Weyl counter by weyl_add), or nothing when skip is NULL (counter RNG).
+void launch_cull_pixels(cudaStream_t st, FilmView film, const uint32_t* slot_base, uint32_t n_owned, CullRect rect, const uint32_t* row_prefix,
+                        const uint32_t* skip, uint32_t weyl_add, uint32_t* slot_active);
 
 // pixels owned by `rank` under tile sharding: rows are dealt in bands of kBandRows
 constexpr int kBandRows = 4;

@@ -68,6 +68,8 @@ PTX_HD void xorwow_apply(Xorwow& s, const uint32_t* m) {
 
 // host: fill `out` (kXorwowJumps * kXorwowJumpWords words) -- see rng.cpp
 void xorwow_build_jump_tables(uint32_t* out);
+// host: `out` (kXorwowJumpWords words) = T^n, the transition of n draws (the Weyl counter advances by 362437 * n besides); rng.cpp
+void xorwow_build_skip_matrix(uint64_t n, uint32_t* out);
 
 // ---------------------------------------------------------------------------------------------
 // Philox4x32-10 (Salmon et al., "Parallel random numbers: as easy as 1, 2, 3", SC11)

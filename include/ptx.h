@@ -224,6 +224,12 @@ enum {
     PTX_RENDER_NO_COST_ORDER = 32, /* pipelines 3 / 6, compat RNG: keep the work items in pixel order instead of handing out the
                                       longest-expected pixels first (a 2-path probe per pixel + a radix sort per frame); images are the
                                       same either way, only the frame's tail differs (A/B measurements) */
+    PTX_RENDER_NO_BOUNDS_CULL = 64, /* pipelines 3 / 6: trace every pixel.  By default the pixels none of whose camera rays can reach the
+                                      scene's bounding box (outside the screen rectangle of its projection, 2 pixels of margin) are not
+                                      traced: every sample of such a pixel draws its two jitter numbers, misses and ends, so the pixel's
+                                      XORWOW stream is advanced by 2 * spp draws (one GF(2) matrix product) and its film sum left alone --
+                                      film and RNG state equal those of the traced frame bit for bit.  The culled paths are counted in
+                                      ptx_render_stats.paths / segments and reported in culled_paths */
     PTX_RENDER_ASYNC = 4           /* pipelines 3 / 6: ptx_render returns without waiting for the GPU (nothing between the render
                                       and a following ptx_film_combine / resolve synchronises the host); the statistics are
                                       completed by the next ptx_render_stats_get, ptx_sync or ptx_render on this context */
@@ -239,6 +245,7 @@ typedef struct {
     float extend_ms, shade_ms, other_ms;   /* filled with PTX_RENDER_STAGE_TIMING */
     uint64_t node_visits, tri_tests;       /* filled with PTX_RENDER_COUNT_WORK */
     uint64_t slot_launches;                /* path loop: sum over launches of the live slots that entered the kernel */
+    uint64_t culled_paths;                 /* of `paths` (and of `segments`: one each): resolved by whole-pixel culling, not traced */
 } ptx_render_stats;
 
 /* Host-side sharding arithmetic (no device work; what a multi-process driver and the CPU tests use to check that the

@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "../cuda-pathtracer_b200/csrc/bvh_host.h"
+#include "../cuda-pathtracer_b200/csrc/cull.h"
 #include "../cuda-pathtracer_b200/csrc/flat_host.h"
 #include "../cuda-pathtracer_b200/csrc/instancing_host.h"
 #include "../cuda-pathtracer_b200/csrc/loader.h"
@@ -236,6 +237,26 @@ void emu_xorwow_init(uint64_t seed, uint64_t subsequence, const uint32_t* tables
     for (int b = 0; b < kXorwowJumps; b++)
         if ((subsequence >> b) & 1ull) xorwow_apply(s, tables + (size_t)b * kXorwowJumpWords);
     out6[0] = s.v0; out6[1] = s.v1; out6[2] = s.v2; out6[3] = s.v3; out6[4] = s.v4; out6[5] = s.d;
+}
+// whole-pixel culling (api.cu ptx_render): the stream skip and the screen rectangle
+void emu_xorwow_skip(uint32_t* st6, uint64_t n) {               // T^n + the Weyl counter: what k_cull_pixels applies
+    std::vector<uint32_t> m((size_t)kXorwowJumpWords);
+    xorwow_build_skip_matrix(n, m.data());
+    Xorwow s{st6[0], st6[1], st6[2], st6[3], st6[4], st6[5]};
+    xorwow_apply(s, m.data());
+    s.d += (uint32_t)(362437ull * n);
+    st6[0] = s.v0; st6[1] = s.v1; st6[2] = s.v2; st6[3] = s.v3; st6[4] = s.v4; st6[5] = s.d;
+}
+void emu_xorwow_steps(uint32_t* st6, uint64_t n) {              // n draws one at a time
+    Xorwow s{st6[0], st6[1], st6[2], st6[3], st6[4], st6[5]};
+    for (uint64_t i = 0; i < n; i++) xorwow_next(s);
+    st6[0] = s.v0; st6[1] = s.v1; st6[2] = s.v2; st6[3] = s.v3; st6[4] = s.v4; st6[5] = s.d;
+}
+int emu_cull_rect(const ptx_camera* cam, const float* bmin, const float* bmax, int w, int h, int* out4) {
+    CullRect r{0, 0, w, h};
+    bool ok = cull_rect(*cam, bmin, bmax, w, h, r);
+    out4[0] = r.x0; out4[1] = r.y0; out4[2] = r.x1; out4[3] = r.y1;
+    return ok ? 1 : 0;
 }
 void emu_philox(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out4) {
     Philox4 p = philox4x32_10(c0, c1, c2, c3, k0, k1);

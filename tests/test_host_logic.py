@@ -43,6 +43,9 @@ def emu(built):
     L.emu_inst_counts.restype = C.c_int64
     L.emu_inst_counts.argtypes = [C.c_void_p] * 5
     L.emu_inst_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.emu_xorwow_skip.argtypes = [C.c_void_p, C.c_uint64]
+    L.emu_xorwow_steps.argtypes = [C.c_void_p, C.c_uint64]
+    L.emu_cull_rect.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     L.emu_flat_units.argtypes = [C.c_void_p, C.c_void_p]
     L.emu_trace_flat.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
     L.emu_render_flat.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -379,6 +382,60 @@ def test_tree_scene_bvh8_vs_reference_goldens(pkg, emu, tmp_path):
         emu.emu_render(s, C.byref(v), 4, 8, 2023, P(lin), None, C.byref(seg))
         assert np.array_equal(bits(lin), bits(g["render_48x48_4spp_d8"]))
         emu.emu_scene_free(s)
+
+
+def test_xorwow_skip_matrix_equals_stepping(emu):
+    """Whole-pixel culling advances a culled pixel's XORWOW stream by 2 * spp draws with T^n (rng.cpp xorwow_build_skip_matrix): the
+    state must be the one n single draws leave, for the n of real frames and for awkward ones."""
+    rng = np.random.default_rng(3)
+    for n in (0, 1, 2, 3, 7, 128, 129, 2 * 64, 2 * 1024, 2 * 4096, 2 * 65535, 1000003):
+        a = rng.integers(0, 2**32, 6, dtype=np.uint64).astype(np.uint32)
+        b = a.copy()
+        emu.emu_xorwow_skip(P(a), n)
+        emu.emu_xorwow_steps(P(b), n)
+        assert np.array_equal(a, b), n
+
+
+def test_cull_rectangle_is_conservative(pkg, emu):
+    """cull.h: no camera ray through a pixel OUTSIDE the rectangle may hit the box -- checked with the product's own ray generation
+    arithmetic (float32, Sensor::get_ray) at the pixel corners and at random jitter, for random cameras and boxes; a camera inside
+    or beside the box (a corner behind it) must turn the culling off."""
+    rng = np.random.default_rng(11)
+    n_rect = n_off = 0
+    for it in range(300):
+        lo = rng.normal(size=3) * 3
+        hi = lo + rng.uniform(0.05, 4.0, 3)
+        eye = rng.normal(size=3) * 8 if it % 4 else lo + (hi - lo) * rng.uniform(-0.3, 1.3, 3)       # every fourth camera in or right beside the box
+        at = (lo + hi) / 2 + rng.normal(size=3) * rng.choice([0.2, 3.0])
+        w, h = int(rng.integers(16, 200)), int(rng.integers(16, 200))
+        cam = pkg.look_at_camera(eye, at, [0, 1, 0], float(rng.uniform(15, 80)), w, h)
+        out = np.zeros(4, np.int32)
+        bmin, bmax = lo.astype(np.float32), hi.astype(np.float32)
+        ok = emu.emu_cull_rect(C.byref(cam), P(bmin), P(bmax), w, h, P(out))
+        inside = np.all(eye > lo) and np.all(eye < hi)
+        if inside:
+            assert not ok
+        if not ok:
+            n_off += 1
+            continue
+        n_rect += 1
+        x0, y0, x1, y1 = out
+        assert 0 <= x0 <= x1 <= w and 0 <= y0 <= y1 <= h
+        ys, xs = np.mgrid[0:h, 0:w]
+        outside = (xs < x0) | (xs >= x1) | (ys < y0) | (ys >= y1)
+        px, py = xs[outside].astype(np.float32), ys[outside].astype(np.float32)
+        if len(px) == 0:
+            continue
+        O = np.float32(cam.origin[:]); llc = np.float32(cam.lower_left_corner[:]); hor = np.float32(cam.horizontal[:]); ver = np.float32(cam.vertical[:])
+        for ju, jv in [(0, 0), (1, 0), (0, 1), (1, 1)] + [tuple(rng.uniform(0, 1, 2)) for _ in range(4)]:
+            u = ((px + np.float32(ju)) / np.float32(w)).astype(np.float32); v = ((py + np.float32(jv)) / np.float32(h)).astype(np.float32)
+            d = (llc[None] + u[:, None] * hor[None] + v[:, None] * ver[None] - O[None]).astype(np.float64)
+            with np.errstate(divide="ignore", invalid="ignore"):
+                t0 = (bmin.astype(np.float64)[None] - O[None]) / d; t1 = (bmax.astype(np.float64)[None] - O[None]) / d
+            tn = np.nanmax(np.minimum(t0, t1), axis=1); tf = np.nanmin(np.maximum(t0, t1), axis=1)
+            hit = (tn <= tf) & (tf > 0)
+            assert not hit.any(), (it, out, np.nonzero(hit)[0][:4])
+    assert n_rect > 100 and n_off > 20, (n_rect, n_off)
 
 
 def test_flat_units_reject_large_or_degenerate(pkg, emu):
