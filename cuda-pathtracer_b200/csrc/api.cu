@@ -998,7 +998,8 @@ int ptx_render(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* cam, ptx_fi
     // On a tree (not the flat list) consecutive pixels share nodes in L1 / L2, which the cost order breaks up: C3 at 1080p is 0.9 % faster in
     // film order (profiles/r2s_cost_order_c3.log), so there the order is only used when a lane gets few pixels (sharded / small frames).
     const bool order_pays = flat || (unsigned long long)rp.n_owned < 8ull * (unsigned long long)c->prop.multiProcessorCount * 3ull * 256ull;
-    if (persist && !cta_wave && rng_mode == PTX_RNG_XORWOW_COMPAT && rp.spp >= 64 && rp.n_owned > 0 && !scene->view.inst && order_pays && !(opts->flags & PTX_RENDER_NO_COST_ORDER)) {
+    // (from 256 spp: the two probe paths per pixel are 3 % of a 64-spp frame -- C1 2.04 ms with, 1.87 ms without the ordering: profiles/r2ag_c1_ab.log)
+    if (persist && !cta_wave && rng_mode == PTX_RNG_XORWOW_COMPAT && rp.spp >= 256 && rp.n_owned > 0 && !scene->view.inst && order_pays && !(opts->flags & PTX_RENDER_NO_COST_ORDER)) {
         launch_pixel_cost(c->stream, scene->view, flat ? &fs : nullptr, cv, rp.shade, c->ws.slot_pixel, rp.n_owned, c->d_cost_keys[0], c->d_cost_vals);
         PTX_CUDA(c, cudaGetLastError());
         size_t tmp = c->cost_tmp_bytes;
