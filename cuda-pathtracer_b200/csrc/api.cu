@@ -1237,7 +1237,6 @@ int ptx_trace_rays(ptx_ctx* c, const ptx_scene* scene, const float* rays_host, s
 int ptx_trace_rays_noalloc(ptx_ctx* c, const ptx_scene* scene, const float* rays_host, size_t n, float t_min, int32_t* prim_id_host, float* t_host) {
     if (!c || !scene || (n && (!rays_host || !prim_id_host || !t_host))) return fail(c, PTX_ERR_INVALID, "ptx_trace_rays_noalloc: bad argument");
     if (scene->ctx != c) return fail(c, PTX_ERR_INVALID, "ptx_trace_rays_noalloc: the scene belongs to another context");
-    if (scene->view.inst) return fail(c, PTX_ERR_UNSUPPORTED, "ptx_trace_rays_noalloc: not implemented for two-level (instanced) scenes");
     if (n > (size_t)PTX_NOALLOC_MAX_RAYS)
         return fail(c, PTX_ERR_INVALID, "ptx_trace_rays_noalloc: at most PTX_NOALLOC_MAX_RAYS (65536) rays per call; split the batch or use ptx_trace_rays");
     if (!scene->view.nodes) return fail(c, PTX_ERR_INVALID, "ptx_trace_rays_noalloc: the scene has no acceleration structure");
@@ -1261,7 +1260,6 @@ int ptx_ctx_flush_l2(ptx_ctx* c) {
 int ptx_trace_occluded(ptx_ctx* c, const ptx_scene* scene, const float* segs_host, size_t n, uint8_t* occluded_host) {
     if (!c || !scene || (n && (!segs_host || !occluded_host))) return fail(c, PTX_ERR_INVALID, "ptx_trace_occluded: bad argument");
     if (!scene->view.nodes) return fail(c, PTX_ERR_INVALID, "ptx_trace_occluded: the scene has no acceleration structure (a rebuild failed)");
-    if (scene->view.inst) return fail(c, PTX_ERR_UNSUPPORTED, "ptx_trace_occluded: not implemented for two-level (instanced) scenes");
     if (!n) return PTX_OK;
     PTX_CUDA(c, cudaSetDevice(c->device));
     float* d_segs = nullptr; uint8_t* d_out = nullptr;
@@ -1281,7 +1279,6 @@ int ptx_render_visibility(ptx_ctx* c, const ptx_scene* scene, const ptx_camera* 
     if (!c || !scene || !cam || !film || !rgb8_host || spp <= 0) return fail(c, PTX_ERR_INVALID, "ptx_render_visibility: bad argument");
     if (scene->ctx != c || film->ctx != c) return fail(c, PTX_ERR_INVALID, "ptx_render_visibility: scene/film belong to another context");
     if (!scene->view.nodes) return fail(c, PTX_ERR_INVALID, "ptx_render_visibility: the scene has no acceleration structure (a rebuild failed)");
-    if (scene->view.inst) return fail(c, PTX_ERR_UNSUPPORTED, "ptx_render_visibility: not implemented for two-level (instanced) scenes");
     PTX_CUDA(c, cudaSetDevice(c->device));
     const size_t npix = (size_t)film->w * film->h, nprim = scene->view.n_prims;
     float* d_rad = nullptr; uint8_t* d_img = nullptr;

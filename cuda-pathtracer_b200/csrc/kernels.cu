@@ -1364,9 +1364,22 @@ __global__ void __launch_bounds__(kBlock) k_occluded(SceneView scene, const floa
     out[i] = trace_any<24>(scene, o, d, 1e-4f, dist - 1e-4f) ? 1 : 0;
 }
 
+__global__ void __launch_bounds__(kBlock) k_occluded_inst(SceneView scene, const float* __restrict__ segs, size_t n, uint8_t* out) {
+    size_t i = (size_t)blockIdx.x * kBlock + threadIdx.x;
+    if (i >= n) return;
+    vec3 from = v3(segs[6 * i], segs[6 * i + 1], segs[6 * i + 2]);
+    vec3 dir = v3(segs[6 * i + 3], segs[6 * i + 4], segs[6 * i + 5]) - from;
+    float dist = length(dir);
+    dir = div_scalar(dir, dist);
+    vec3 o = from + 1e-4f * dir;
+    vec3 d = unit(dir);
+    out[i] = trace_any_instanced<24>(scene, o, d, 1e-4f, dist - 1e-4f) ? 1 : 0;
+}
+
 // render_radiosity (integrator.h:460-504): per pixel, spp jittered primary rays; colour = Le + the radiosity stored for
 // the hit primitive (input of this kernel: the solver that produces it is out of scope); sqrt "gamma", clamp to 1.
 // Continues and writes back the pixel's XORWOW stream like the reference kernel.
+template <bool INST>
 __global__ void __launch_bounds__(kBlock) k_visibility(SceneView scene, FilmView film, CameraView cam, int spp, const float* __restrict__ radiosity,
                                                        uint8_t* rgb8) {
     uint32_t p = blockIdx.x * kBlock + threadIdx.x;
@@ -1380,10 +1393,22 @@ __global__ void __launch_bounds__(kBlock) k_visibility(SceneView scene, FilmView
         float v = (fy + xr.next()) / (float)cam.height;
         vec3 o, d; camera_ray(cam, u, v, o, d);
         float t;
-        uint32_t tri = trace_closest<24, false>(scene, o, d, 1e-4f, FLT_MAX, t, nullptr);
+        uint32_t tri, prim = kMiss, mat = 0;
+        if constexpr (INST) {
+            InstTraversal it;
+            TravStack<24> stk;
+            it.begin(o, d, FLT_MAX);
+            while (!it.template step<24>(scene, stk, o, d, 1e-4f)) {}
+            tri = it.tr.best; t = it.tr.closest;
+            if (tri != kMiss) { vec3 n; resolve_instanced_hit(scene, it, prim, n, mat); }
+        } else {
+            tri = trace_closest<24, false>(scene, o, d, 1e-4f, FLT_MAX, t, nullptr);
+            if (tri != kMiss) {
+                prim = __float_as_uint(ldq(scene.tris + (size_t)tri * kTriQuads).w);
+                mat = f2u(ldq(scene.prim_shade + prim).w);
+            }
+        }
         if (tri != kMiss) {
-            uint32_t prim = __float_as_uint(ldq(scene.tris + (size_t)tri * kTriQuads).w);
-            uint32_t mat = f2u(ldq(scene.prim_shade + prim).w);
             f32x4 ke = ldq(scene.materials + 2 * (size_t)mat + 1);
             color = color + v3(ke.x, ke.y, ke.z);
             if (radiosity) color = color + v3(radiosity[3 * (size_t)prim], radiosity[3 * (size_t)prim + 1], radiosity[3 * (size_t)prim + 2]);
@@ -1688,7 +1713,8 @@ cudaError_t trace_rays_noalloc(cudaStream_t st, int device, const SceneView& sce
     float* d_t = reinterpret_cast<float*>(static_cast<unsigned char*>(base) + kNoAllocMaxRays * 7 * sizeof(float));
     e = cudaMemcpyAsync(d_rays, rays_host, n * 6 * sizeof(float), cudaMemcpyHostToDevice, st);
     if (e != cudaSuccess) return e;
-    k_trace_rays<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, d_rays, n, t_min, d_ids, d_t);
+    if (scene.inst) k_trace_rays_inst<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, d_rays, n, t_min, d_ids, d_t);
+    else k_trace_rays<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, d_rays, n, t_min, d_ids, d_t);
     e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(prim_host, d_ids, n * sizeof(int32_t), cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(t_host, d_t, n * sizeof(float), cudaMemcpyDeviceToHost, st);
@@ -1698,12 +1724,14 @@ cudaError_t trace_rays_noalloc(cudaStream_t st, int device, const SceneView& sce
 
 void launch_occluded(cudaStream_t st, const SceneView& scene, const float* segs, size_t n, uint8_t* out) {
     if (!n) return;
-    k_occluded<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, segs, n, out);
+    if (scene.inst) k_occluded_inst<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, segs, n, out);
+    else k_occluded<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, segs, n, out);
 }
 void launch_visibility(cudaStream_t st, const SceneView& scene, const FilmView& film, const CameraView& cam, int spp, const float* radiosity, uint8_t* rgb8) {
     size_t n = (size_t)cam.width * cam.height;
     if (!n || spp <= 0) return;
-    k_visibility<<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, film, cam, spp, radiosity, rgb8);
+    if (scene.inst) k_visibility<true><<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, film, cam, spp, radiosity, rgb8);
+    else k_visibility<false><<<blocks_for(n, kBlock), kBlock, 0, st>>>(scene, film, cam, spp, radiosity, rgb8);
 }
 
 }  // namespace ptx

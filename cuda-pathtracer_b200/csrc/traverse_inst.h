@@ -146,4 +146,25 @@ PTX_HD uint32_t trace_closest_instanced(const SceneView& s, vec3 o, vec3 d, floa
     return it.tr.best;
 }
 
+// Any hit along (o, d) in [t_min, t_max] through the two-level structure (Scene::occluded; trace_any in traverse.h has the end-point
+// rule: a triangle accepts t == t_max, the halves of a quad do not -- quad_bits is indexed by the flattened primitive id).
+template <int STACK>
+PTX_HD bool trace_any_instanced(const SceneView& s, vec3 o, vec3 d, float t_min, float t_max) {
+    if (!(t_max >= t_min) || !(t_max > 0.0f)) return false;
+    const float bound = u2f(f2u(t_max) + 1u);
+    InstTraversal it;
+    TravStack<STACK> stk;
+    it.begin(o, d, bound);
+    for (;;) {
+        const bool done = it.template step<STACK>(s, stk, o, d, t_min);
+        if (it.tr.best != kMiss) {                         // a record accepted a hit below `bound`
+            if (it.tr.closest < t_max || s.quad_bits == nullptr) return true;
+            const uint32_t prim = f2u(ldq(reinterpret_cast<const f32x4*>(s.inst + it.best_inst) + 6).y) + it.tr.bestw;
+            if (!((s.quad_bits[prim >> 5] >> (prim & 31u)) & 1u)) return true;
+            it.tr.best = kMiss; it.tr.closest = bound;     // a quad half exactly at t_max does not count: keep looking
+        }
+        if (done) return false;
+    }
+}
+
 }  // namespace ptx

@@ -80,7 +80,10 @@ typedef struct {
                                  space, a TLAS over the instances; the ray is transformed at the instance) instead of flattening
                                  like the reference (pbrt_loader.h:197, 282-344).  Same primitive numbering; hit distances agree
                                  with the flattened scene to rounding, not bit for bit.  Ignored (flattened) for files without
-                                 instances or with nested instancing, and with convert_quads / subdivision / triangle_cap. */
+                                 instances or with nested instancing, and with convert_quads / subdivision / triangle_cap.
+                                 A two-level scene renders with BSDF sampling (pipeline 0 / 3) and answers ptx_trace_primary_ids,
+                                 ptx_trace_rays(_noalloc), ptx_trace_occluded and ptx_render_visibility; grid / MIS sampling and
+                                 ptx_scene_build_accel are not available for it. */
     int32_t reserved;
 } ptx_load_opts;
 

@@ -215,6 +215,17 @@ int64_t emu_inst_counts(const EmuInstScene* s, int64_t* n_inst, int64_t* stored_
 }
 // closest hits through the two-level traversal; prim = flattened numbering; normals_out (optional, 3 floats per ray) = the world-space
 // shading normal resolve_instanced_hit computes
+void emu_inst_occluded(const EmuInstScene* s, const float* segs, int64_t n, uint8_t* out) {      // k_occluded_inst on the host
+    for (int64_t i = 0; i < n; i++) {
+        vec3 from = ld3(segs + 6 * i);
+        vec3 dir = ld3(segs + 6 * i + 3) - from;
+        float dist = length(dir);
+        dir = div_scalar(dir, dist);
+        vec3 o = from + 1e-4f * dir;
+        vec3 d = unit(dir);
+        out[i] = trace_any_instanced<32>(s->view, o, d, 1e-4f, dist - 1e-4f) ? 1 : 0;
+    }
+}
 void emu_inst_trace(const EmuInstScene* s, const float* rays, int64_t n, float t_min, int32_t* prim, float* t, float* normals_out) {
     for (int64_t i = 0; i < n; i++) {
         vec3 o = ld3(rays + 6 * i), d = unit(ld3(rays + 6 * i + 3));

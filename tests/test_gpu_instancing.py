@@ -77,10 +77,37 @@ def test_instanced_render_close_to_flattened(pkg, ctx, scenes, rng_mode):
     assert abs(float(a.mean()) - float(b.mean())) <= 2e-2 * float(a.mean())
 
 
+def test_instanced_shadow_queries_and_visibility_view(pkg, ctx, scenes):
+    """Scene::occluded and the render_radiosity view through the two-level structure (trace_any_instanced, k_visibility<INST>) and the
+    allocation-free ray query: the same answers as the flattened scene, but for rays that graze within rounding."""
+    flat, inst, n, cam_args = scenes
+    rng = np.random.default_rng(12)
+    segs = np.concatenate([rng.uniform(1.0, 15.0, (30000, 3)), rng.uniform(1.0, 15.0, (30000, 3))], 1).astype(np.float32)
+    of, oi = ctx.trace_occluded(flat, segs), ctx.trace_occluded(inst, segs)
+    assert 0.2 < of.mean() < 0.98
+    assert (of != oi).mean() < 5e-4, float((of != oi).mean())
+    w, h, spp = 160, 120, 4
+    cam = pkg.look_at_camera(*cam_args, w, h)
+    film = ctx.create_film(w, h)
+    rad = rng.uniform(0.0, 0.6, (n, 3)).astype(np.float32)
+    out = []
+    for sc in (flat, inst):
+        film.reset(2023)
+        img = ctx.render_visibility(sc, cam, film, spp, radiosity=rad)
+        out.append((img, film.rng_state()))
+    assert np.array_equal(out[0][1], out[1][1])                                 # the same streams, the same number of draws
+    differ = (out[0][0] != out[1][0]).any(-1).mean()
+    assert differ < 5e-3, float(differ)                                          # a pixel differs where one of its 4 rays ties to rounding
+    assert out[0][0].mean() > 20
+    film.close()
+    rays = np.concatenate([rng.uniform(1.0, 15.0, (5000, 3)), rng.normal(size=(5000, 3))], 1).astype(np.float32)
+    ia, ta = ctx.trace_rays(inst, rays)
+    ib, tb = ctx.trace_rays_noalloc(inst, rays)
+    assert np.array_equal(ia, ib) and np.array_equal(ta.view(np.uint32), tb.view(np.uint32))
+
+
 def test_instanced_scene_unsupported_calls(pkg, ctx, scenes):
     flat, inst, n, cam_args = scenes
-    with pytest.raises(pkg.PtxError):
-        ctx.trace_occluded(inst, np.zeros((1, 6), np.float32))
     with pytest.raises(pkg.PtxError):
         inst.rebuild(builder=0)
     cam = pkg.look_at_camera(*cam_args, 32, 32)

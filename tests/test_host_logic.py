@@ -43,6 +43,7 @@ def emu(built):
     L.emu_inst_counts.restype = C.c_int64
     L.emu_inst_counts.argtypes = [C.c_void_p] * 5
     L.emu_inst_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.emu_inst_occluded.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
     L.emu_xorwow_skip.argtypes = [C.c_void_p, C.c_uint64]
     L.emu_xorwow_steps.argtypes = [C.c_void_p, C.c_uint64]
     L.emu_cull_rect.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
@@ -526,6 +527,17 @@ def test_two_level_traversal_matches_flattened_scene(pkg, emu, tmp_path):
     hit = same & (idf >= 0)
     want = flat_prims["normal"][idf[hit]]
     assert np.abs(nrm[hit] - want).max() < 2e-3                                  # unit(L e1 x L e2) against the flattened unit((v1 - v0) x (v2 - v0))
+    # any-hit (Scene::occluded) through the two-level structure: the same booleans as the flattened scene, but for segments whose
+    # end point lies within rounding of a surface (object-space arithmetic)
+    a = rng.uniform(0.5, 11.5, (6000, 3)); b = rng.uniform(0.5, 11.5, (6000, 3))
+    hitp = rays[hit][:1500, :3] + rays[hit][:1500, 3:] / np.linalg.norm(rays[hit][:1500, 3:], axis=1, keepdims=True) * tf[hit][:1500, None]
+    segs = np.concatenate([np.concatenate([a, b], 1), np.concatenate([rays[hit][:1500, :3], hitp], 1)], 0).astype(np.float32)    # the last 1500 end ON a surface
+    of = np.zeros(len(segs), np.uint8); oi = np.zeros(len(segs), np.uint8)
+    emu.emu_occluded(sf, P(segs), len(segs), P(of))
+    emu.emu_inst_occluded(si, P(segs), len(segs), P(oi))
+    assert 0.2 < of[:6000].mean() < 0.98
+    assert (of[:6000] != oi[:6000]).mean() < 1e-3
+    assert (of[6000:] != oi[6000:]).mean() < 0.2                                  # borderline by construction: rounding decides
     emu.emu_scene_free(sf); emu.emu_inst_free(si)
 
 
