@@ -1,6 +1,8 @@
+"""Per-pixel mean path length of C2 on the CPU (host build of the product's flat-kernel core, tests/_build/libptx_hostemu.so): a 48 x 27 grid of
+sampled pixels, 256 spp each, through a one-pixel sub-window camera.  Output: profiles/r2aa_c2_cost_map.txt.  python tools/cost_map_cpu.py"""
 import ctypes as C, os, sys, time
 import numpy as np
-ROOT='/root/repo'; sys.path.insert(0, ROOT); sys.path.insert(0, ROOT+'/tests')
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import __graft_entry__ as ge
 ge.build_host_emu(); pkg = ge.load_package()
 L = C.CDLL(os.path.join(ROOT, "tests", "_build", "libptx_hostemu.so"))
