@@ -85,7 +85,7 @@ EXPORTS = [
     "ptx_scene_set_radiosity_grids", "ptx_scene_get_guide_records",
     "ptx_camera_set", "ptx_camera_update", "ptx_camera_orbit", "ptx_camera_default",
     "ptx_film_create", "ptx_film_reset", "ptx_film_clear", "ptx_film_resolve_rgb8", "ptx_film_read_linear", "ptx_film_write", "ptx_write_png_rgb8",
-    "ptx_film_device_buffer", "ptx_film_set_sample_count", "ptx_film_destroy",
+    "ptx_film_device_buffer", "ptx_film_set_sample_count", "ptx_film_destroy", "ptx_film_save", "ptx_film_load",
     "ptx_shard_pixel_count", "ptx_shard_owned_pixels", "ptx_shard_sample_range",
     "ptx_render", "ptx_render_stats_get", "ptx_comm_unique_id", "ptx_comm_create", "ptx_comm_destroy", "ptx_film_combine",
     "ptx_trace_primary_ids", "ptx_trace_rays", "ptx_trace_rays_noalloc", "ptx_trace_occluded", "ptx_render_visibility", "ptx_film_rng_state",
@@ -129,6 +129,8 @@ def lib():
         L.ptx_scene_load.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_void_p]
         L.ptx_parse_scene_file.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ptx_film_write.argtypes = [C.c_void_p, C.c_char_p]
+        L.ptx_film_save.argtypes = [C.c_void_p, C.c_char_p]
+        L.ptx_film_load.argtypes = [C.c_void_p, C.c_char_p]
         L.ptx_write_png_rgb8.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
         L.ptx_film_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.ptx_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -435,6 +437,13 @@ class Film:
 
     def write(self, path):
         _check(lib().ptx_film_write(self._h, os.fspath(path).encode()), self.ctx._h)
+
+    def save(self, path):
+        """Checkpoint: running sums, RNG streams and sample counters (ptx_film_save)."""
+        _check(lib().ptx_film_save(self._h, os.fspath(path).encode()), self.ctx._h)
+
+    def load(self, path):
+        _check(lib().ptx_film_load(self._h, os.fspath(path).encode()), self.ctx._h)
 
     def device_buffer(self):
         p, n = C.c_void_p(), C.c_size_t()

@@ -726,6 +726,73 @@ int ptx_film_write(ptx_film* f, const char* path) {
     return PTX_OK;
 }
 
+// Checkpoint / resume of a progressive render (no counterpart in the reference, whose RNG state and image live in device memory
+// only: SURVEY.md 5.4).  File: magic, version, width, height, seed base, sample counters, then the running sums (float4 per pixel)
+// and the XORWOW streams (uint4 + uint2 per pixel) exactly as the kernels hold them.
+namespace {
+struct FilmFileHeader {
+    char magic[8];                 // "PTXFILM\0"
+    uint32_t version, width, height, sample_base;
+    uint64_t seed_base;
+    float total_spp, frame_spp;
+};
+}  // namespace
+
+int ptx_film_save(ptx_film* f, const char* path) {
+    if (!f || !path) return fail(nullptr, PTX_ERR_INVALID, "ptx_film_save: NULL argument");
+    ptx_ctx* c = f->ctx;
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    { int frc = finalize_pending(c); if (frc != PTX_OK) return frc; }
+    const size_t npix = (size_t)f->w * f->h;
+    std::vector<float4> acc(npix); std::vector<uint4> ra(npix); std::vector<uint2> rb(npix);
+    PTX_CUDA(c, cudaMemcpyAsync(acc.data(), f->d_accum, npix * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    PTX_CUDA(c, cudaMemcpyAsync(ra.data(), f->d_rngA, npix * sizeof(uint4), cudaMemcpyDeviceToHost, c->stream));
+    PTX_CUDA(c, cudaMemcpyAsync(rb.data(), f->d_rngB, npix * sizeof(uint2), cudaMemcpyDeviceToHost, c->stream));
+    PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+    FilmFileHeader hd{};
+    memcpy(hd.magic, "PTXFILM", 8);
+    hd.version = 1; hd.width = (uint32_t)f->w; hd.height = (uint32_t)f->h; hd.sample_base = f->sample_base;
+    hd.seed_base = f->seed_base; hd.total_spp = f->total_spp; hd.frame_spp = f->frame_spp;
+    FILE* fp = fopen(path, "wb");
+    if (!fp) return fail(c, PTX_ERR_IO, std::string("cannot write ") + path);
+    bool ok = fwrite(&hd, sizeof hd, 1, fp) == 1 && fwrite(acc.data(), sizeof(float4), npix, fp) == npix &&
+              fwrite(ra.data(), sizeof(uint4), npix, fp) == npix && fwrite(rb.data(), sizeof(uint2), npix, fp) == npix;
+    ok = (fclose(fp) == 0) && ok;
+    if (!ok) return fail(c, PTX_ERR_IO, std::string("short write to ") + path);
+    return PTX_OK;
+}
+
+int ptx_film_load(ptx_film* f, const char* path) {
+    if (!f || !path) return fail(nullptr, PTX_ERR_INVALID, "ptx_film_load: NULL argument");
+    ptx_ctx* c = f->ctx;
+    PTX_CUDA(c, cudaSetDevice(c->device));
+    { int frc = finalize_pending(c); if (frc != PTX_OK) return frc; }
+    FILE* fp = fopen(path, "rb");
+    if (!fp) return fail(c, PTX_ERR_IO, std::string("cannot open ") + path);
+    FilmFileHeader hd{};
+    if (fread(&hd, sizeof hd, 1, fp) != 1 || memcmp(hd.magic, "PTXFILM", 8) != 0 || hd.version != 1) {
+        fclose(fp);
+        return fail(c, PTX_ERR_IO, std::string(path) + ": not a film checkpoint (magic / version)");
+    }
+    if (hd.width != (uint32_t)f->w || hd.height != (uint32_t)f->h) {
+        fclose(fp);
+        return fail(c, PTX_ERR_INVALID, std::string(path) + ": the checkpoint is " + std::to_string(hd.width) + " x " + std::to_string(hd.height) +
+                                         ", the film " + std::to_string(f->w) + " x " + std::to_string(f->h));
+    }
+    const size_t npix = (size_t)f->w * f->h;
+    std::vector<float4> acc(npix); std::vector<uint4> ra(npix); std::vector<uint2> rb(npix);
+    const bool ok = fread(acc.data(), sizeof(float4), npix, fp) == npix && fread(ra.data(), sizeof(uint4), npix, fp) == npix &&
+                    fread(rb.data(), sizeof(uint2), npix, fp) == npix;
+    fclose(fp);
+    if (!ok) return fail(c, PTX_ERR_IO, std::string(path) + ": truncated film checkpoint");
+    PTX_CUDA(c, cudaMemcpyAsync(f->d_accum, acc.data(), npix * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    PTX_CUDA(c, cudaMemcpyAsync(f->d_rngA, ra.data(), npix * sizeof(uint4), cudaMemcpyHostToDevice, c->stream));
+    PTX_CUDA(c, cudaMemcpyAsync(f->d_rngB, rb.data(), npix * sizeof(uint2), cudaMemcpyHostToDevice, c->stream));
+    PTX_CUDA(c, cudaStreamSynchronize(c->stream));
+    f->seed_base = hd.seed_base; f->sample_base = hd.sample_base; f->total_spp = hd.total_spp; f->frame_spp = hd.frame_spp;
+    return PTX_OK;
+}
+
 int ptx_write_png_rgb8(const char* path, int width, int height, const uint8_t* rgb_host, int flip_y) {
     if (!path || !rgb_host || width <= 0 || height <= 0) return fail(nullptr, PTX_ERR_INVALID, "ptx_write_png_rgb8: bad argument");
     if (!write_png_rgb8(path, width, height, rgb_host, flip_y != 0)) return fail(nullptr, PTX_ERR_IO, std::string("cannot write ") + path);

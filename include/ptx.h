@@ -176,6 +176,12 @@ int ptx_film_write(ptx_film* film, const char* path);                        /* 
  * stbi_flip_vertically_on_write(1) + stbi_write_png, ui_windows.h:205-208).  Needs no GPU. */
 int ptx_write_png_rgb8(const char* path, int width, int height, const uint8_t* rgb_host, int flip_y);
 /* raw accumulation buffer (float4 per pixel: sum r,g,b + sample count) for NCCL film combine */
+/* Checkpoint / resume (no counterpart in the reference: its image and curandState array live in device memory only).
+ * ptx_film_save writes the running sums, the per-pixel XORWOW streams and the sample counters; ptx_film_load restores them into a film
+ * of the same size, after which ptx_render(accumulate = 1) continues the progressive render exactly where it stopped (same film,
+ * same streams, bit for bit).  PTX_ERR_IO (missing, not a checkpoint, truncated) / PTX_ERR_INVALID (size mismatch) on failure; the film is untouched then. */
+int ptx_film_save(ptx_film* film, const char* path);
+int ptx_film_load(ptx_film* film, const char* path);
 int ptx_film_device_buffer(ptx_film* film, void** dev_ptr, size_t* bytes);
 int ptx_film_set_sample_count(ptx_film* film, float spp_total);             /* after an external reduce */
 void ptx_film_destroy(ptx_film* film);
