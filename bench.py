@@ -468,9 +468,13 @@ def run_ours(args, w, h, spp, depth):
                 cb_spp = 2
                 spp_ratio = segments_per_path_estimate(scene_path, w, h, depth)
                 j = ref_host_run(scene_path, w, h, cb_spp, depth, 1)
-                j1 = ref_host_run(scene_path, w, h, 1, depth, 1, threads=1)          # the same build on ONE thread as well
+                # the same build on ONE thread as well -- on a 1/4-scale frame (render_init = curand_init with a per-pixel
+                # subsequence jump costs 12 us per pixel on the host: 25 s for 1080p on one thread), 8 spp
+                w1, h1, spp1 = max(w // 4, 1), max(h // 4, 1), 8
+                j1 = ref_host_run(scene_path, w1, h1, spp1, depth, 1, threads=1)
                 out["cpu_baseline"] = {"value": w * h * cb_spp * spp_ratio / (j["ms_per_frame"] * 1e-3) * 1e-6, "unit": METRIC, "cores": j["threads"],
-                                       "single_thread_value": w * h * 1 * spp_ratio / (j1["ms_per_frame"] * 1e-3) * 1e-6,
+                                       "single_thread_value": w1 * h1 * spp1 * spp_ratio / (j1["ms_per_frame"] * 1e-3) * 1e-6,
+                                       "single_thread_sample": f"{w1}x{h1}, {spp1} spp, one thread",
                                        "kind": "reference", "sample": f"{w}x{h}, {cb_spp} of {spp} spp, depth {depth}, oracle/_ref/ref_host (reference headers, host build, OpenMP rows)",
                                        "segments_per_path_source": "C oracle on a 1/8-scale frame at 4 spp (same streams), not counted on the timed frame"}
             except Exception as e:       # noqa: BLE001
